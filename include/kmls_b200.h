@@ -1,0 +1,157 @@
+/* kmls_b200 — C ABI of the B200-native rule-generation hot path.
+ *
+ * Drop-in boundary for the hot path of diogoneiss/kubernetes-machine-learning-server:
+ * machine-learning/main.py:262-313 (calculate_and_save_fp_growth_fast), i.e. the work that
+ * the reference delegates to mlxtend 0.23.3's TransactionEncoder and fpgrowth
+ * (main.py:267-272) plus its own dict fold (main.py:282-296). The reference has no FFI of
+ * its own (it is two Python scripts); the binding a maintainer adds is the ctypes stub in
+ * INTEGRATION.md, which is what kubernetes-machine-learning-server_b200/_lib.py implements.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; `d_` pointers are device memory of the current CUDA
+ *    device, everything else is host memory; buffers are owned by the caller, inputs are
+ *    never written;
+ *  - no entry point allocates or frees device memory: scratch is passed in;
+ *  - work is enqueued on `stream` (a cudaStream_t passed as void*), nothing synchronises;
+ *  - return 0 = ok, > 0 = cudaError_t, < 0 = argument/capacity error (text from
+ *    kmls_last_error()); an output that would not fit is an error, never a truncation;
+ *  - "row" = a kept track of the vertical bitmap (bit p of row r = playlist p contains
+ *    track r); rows are `row_words` 32-bit words long, see kmls_bitmap_row_words().
+ */
+#ifndef KMLS_B200_H_
+#define KMLS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#define KMLS_B200_VERSION 100
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* kmls_stream_t; /* cudaStream_t */
+
+const char* kmls_last_error(void);
+int kmls_version(void);
+
+/* ---- level 1: TransactionEncoder + column sums (main.py:267-269; mlxtend
+ *      TransactionEncoder.fit/transform, fpcommon.setup_fptree's np.sum(axis=0)) ---------- */
+
+/* d_occ[t] = occurrences of track id t in d_items (an upper bound of its support; exact
+ * when no playlist repeats a track). d_occ is zeroed here. d_items 16-byte aligned. */
+int kmls_item_histogram(const int32_t* d_items, int64_t nnz, int32_t n_items, int32_t* d_occ,
+                        kmls_stream_t stream);
+
+/* Words per bitmap row for n_playlists columns (padded to 256 playlists = 8 words). */
+int64_t kmls_bitmap_row_words(int64_t n_playlists);
+
+/* TransactionEncoder.transform, transposed and bit-packed: playlists in CSR
+ * (d_offsets[n_playlists+1], d_items[nnz]); track t goes to row d_row_of_item[t] (or is
+ * dropped when that is < 0 or >= n_rows). Writes every word of d_bitmap[n_rows][row_words].
+ * A track repeated inside a playlist sets its bit once. */
+int kmls_encode_bitmap(const int64_t* d_offsets, const int32_t* d_items, int64_t n_playlists,
+                       const int32_t* d_row_of_item, int32_t n_items, int32_t n_rows,
+                       uint32_t* d_bitmap, int64_t row_words, kmls_stream_t stream);
+
+/* setup_fptree's item counts: d_counts[r] = popcount of row r. */
+int kmls_row_popcount(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                      int32_t* d_counts, kmls_stream_t stream);
+
+/* d_dst row r = d_src row d_src_row[r] (puts rows into their final order). */
+int kmls_gather_rows(const uint32_t* d_src, const int32_t* d_src_row, int32_t n_rows_out,
+                     int64_t row_words, uint32_t* d_dst, kmls_stream_t stream);
+
+/* ---- level 2: pair supports (the k = 2 part of fpgrowth.fpg_step /
+ *      FPTree.conditional_tree; feeds the fold of main.py:282-296) ------------------------ */
+
+/* d_pair[i * n_rows + j] = |row i AND row j| for all i, j (symmetric, diagonal = support). */
+int kmls_pair_counts(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                     int32_t* d_pair, kmls_stream_t stream);
+
+/* Frequent-pair table: all (a, b), a < b, with d_pair[a][b] >= thr, sorted by (a, b).
+ * d_row_off[n_rows+1] receives the exclusive scan of per-row counts (d_row_off[n_rows] =
+ * number of pairs). With capacity == 0 only d_row_off is produced (sizing pass); otherwise
+ * d_items2[2*i], d_items2[2*i+1], d_counts[i] are written for rows that fit in capacity. */
+int kmls_pair_select(const int32_t* d_pair, int32_t n_rows, int32_t thr, int64_t capacity,
+                     int64_t* d_row_off, int32_t* d_items2, int32_t* d_counts,
+                     kmls_stream_t stream);
+
+/* fpcommon.generate_itemsets: support = count / N (IEEE double division). */
+int kmls_supports_f64(const int32_t* d_counts, int64_t n, int64_t n_playlists_total,
+                      double* d_out, kmls_stream_t stream);
+
+/* ---- levels k >= 3 (fpgrowth.fpg_step recursion, restated level-wise) ------------------- */
+
+size_t kmls_scan_scratch_bytes(int64_t n);
+/* d_out[n+1] = exclusive prefix sums of d_in[n] in 64 bits; d_out[n] = total. */
+int kmls_exclusive_scan_i32(const int32_t* d_in, int64_t n, int64_t* d_out, void* d_scratch,
+                            size_t scratch_bytes, kmls_stream_t stream);
+
+/* Fingerprint set of a level table d_items[n][k] (used for Apriori pruning). */
+int64_t kmls_set_capacity(int64_t n);
+int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t k, uint64_t* d_slots,
+                           int64_t capacity, kmls_stream_t stream);
+
+/* Candidate generation for level k+1 from level table d_items[n][k] (sorted): join of
+ * itemsets sharing their first k-1 members, Apriori-pruned (k == 2: against d_pair with
+ * threshold thr; k >= 3: against the fingerprint set of this level).
+ * kmls_join_count: d_kept_cnt[n], d_kept_mask[n] and the scan d_kept_off[n+1]
+ *                  (d_kept_off[n] = number of candidates).
+ * kmls_join_write: candidates (d_cand_p[c], d_cand_q[c]) = indices of the two parents,
+ *                  grouped by p in ascending order; d_grp_p / *d_n_groups = the parents that
+ *                  have at least one candidate. */
+int kmls_join_count(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
+                    int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
+                    int32_t* d_kept_cnt, uint32_t* d_kept_mask, int64_t* d_kept_off,
+                    void* d_scratch, size_t scratch_bytes, kmls_stream_t stream);
+int kmls_join_write(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
+                    int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
+                    const int32_t* d_kept_cnt, const uint32_t* d_kept_mask,
+                    const int64_t* d_kept_off, int32_t* d_cand_p, int32_t* d_cand_q,
+                    int32_t* d_grp_p, int64_t* d_n_groups, void* d_scratch, size_t scratch_bytes,
+                    kmls_stream_t stream);
+
+/* Support counts of the candidates: d_cand_cnt[c] = |AND of the k+1 member rows|. */
+int kmls_count_candidates(const uint32_t* d_bitmap, int64_t row_words, const int32_t* d_items,
+                          int32_t k, const int32_t* d_grp_p, int64_t n_groups,
+                          const int64_t* d_kept_off, const int32_t* d_cand_q, int64_t n_cand,
+                          int32_t* d_cand_cnt, kmls_stream_t stream);
+
+/* Filter by the integer threshold Tk = ceil(min_support * N) (fpgrowth.py) and emit the
+ * level k+1 table in order. kmls_emit_count: d_out_off[n_cand+1] (last = new level size). */
+int kmls_emit_count(const int32_t* d_cand_cnt, int64_t n_cand, int32_t thr, int64_t* d_out_off,
+                    void* d_scratch, size_t scratch_bytes, kmls_stream_t stream);
+int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t* d_cand_p,
+                    const int32_t* d_cand_q, const int32_t* d_cand_cnt, int64_t n_cand,
+                    int32_t thr, const int64_t* d_out_off, int32_t* d_out_items,
+                    int32_t* d_out_counts, kmls_stream_t stream);
+
+/* ---- rules (mlxtend association_rules semantics; the dormant path main.py:224-260 is the
+ *      only reference site of a min_confidence knob) -------------------------------------- */
+
+/* All level tables concatenated: level k's items start at sum_{j<k} level_sizes[j]*j in
+ * d_items and its counts at sum_{j<k} level_sizes[j] in d_counts; level_sizes is a HOST
+ * array indexed 1..max_k (index 0 unused). Exact map fingerprint -> itemset. */
+int kmls_itemset_map_build(const int32_t* d_items, const int32_t* d_counts,
+                           const int64_t* level_sizes, int32_t max_k, uint64_t* d_keys,
+                           int32_t* d_vals, int64_t capacity, kmls_stream_t stream);
+/* d_rule_cnt[x] = rules kept for the x-th itemset of size >= 2; *d_missing counts subset
+ * lookups that failed (0 for a downward-closed table; caller zeroes it). */
+int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
+                     int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
+                     int64_t capacity, int64_t n_playlists_total, double min_confidence,
+                     int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
+/* Rule r: itemset d_out_itemset[r] (global id), antecedent = members selected by the bits
+ * of d_out_antecedent[r] (bit t = t-th member), consequent = the rest. */
+int kmls_rules_write(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
+                     int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
+                     int64_t capacity, int64_t n_playlists_total, double min_confidence,
+                     const int64_t* d_rule_off, int32_t* d_out_itemset,
+                     uint32_t* d_out_antecedent, double* d_out_support, double* d_out_confidence,
+                     double* d_out_lift, int32_t* d_missing, kmls_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KMLS_B200_H_ */

@@ -1,1 +1,17 @@
-"""B200-native rule-generation hot path (package init filled in below)."""
+"""B200-native replacement for the rule-generation hot path of
+diogoneiss/kubernetes-machine-learning-server (machine-learning/main.py:262-313).
+
+``calculate_and_save_fp_growth_fast`` is the reference's own function boundary; the rest are
+the lower-level entry points it is built from. All compute runs in ``libkmls_b200.so``
+(``include/kmls_b200.h``); there is no CPU fallback.
+"""
+from . import synth  # noqa: F401  (numpy only)
+from ._lib import KmlsError, LIB_PATH  # noqa: F401
+from .miner import MineResult, RuleTable, generate_rules, mine_csr, rules_to_host, thresholds  # noqa: F401
+from .api import (calculate_and_save_fp_growth_fast, encode_transactions, itemsets_frame,  # noqa: F401
+                  mine_ids, recommendations_from_result, rules_frame, save_rules)
+
+__all__ = ["calculate_and_save_fp_growth_fast", "mine_csr", "mine_ids", "generate_rules",
+           "thresholds", "encode_transactions", "recommendations_from_result", "itemsets_frame",
+           "rules_frame", "save_rules", "rules_to_host", "MineResult", "RuleTable", "KmlsError",
+           "synth"]

@@ -1,0 +1,88 @@
+"""ctypes binding of ``libkmls_b200.so`` (declared in ``include/kmls_b200.h``).
+
+There is no CPU fallback: if the library is missing, or a call fails, this raises. The
+reference job would then fail and be retried by Kubernetes (``restartPolicy: OnFailure``,
+reference kubernetes/job.yaml:41), which is the error convention SURVEY.md §8b asks for.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_double, c_int32, c_int64, c_size_t, c_void_p
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkmls_b200.so")
+
+_P, _I32, _I64, _SZ, _F64 = c_void_p, c_int32, c_int64, c_size_t, c_double
+
+# name -> (restype, argtypes); mirrors include/kmls_b200.h one to one.
+SIGNATURES = {
+    "kmls_last_error": (ctypes.c_char_p, []),
+    "kmls_version": (ctypes.c_int, []),
+    "kmls_item_histogram": (ctypes.c_int, [_P, _I64, _I32, _P, _P]),
+    "kmls_bitmap_row_words": (_I64, [_I64]),
+    "kmls_encode_bitmap": (ctypes.c_int, [_P, _P, _I64, _P, _I32, _I32, _P, _I64, _P]),
+    "kmls_row_popcount": (ctypes.c_int, [_P, _I32, _I64, _P, _P]),
+    "kmls_gather_rows": (ctypes.c_int, [_P, _P, _I32, _I64, _P, _P]),
+    "kmls_pair_counts": (ctypes.c_int, [_P, _I32, _I64, _P, _P]),
+    "kmls_pair_select": (ctypes.c_int, [_P, _I32, _I32, _I64, _P, _P, _P, _P]),
+    "kmls_supports_f64": (ctypes.c_int, [_P, _I64, _I64, _P, _P]),
+    "kmls_scan_scratch_bytes": (_SZ, [_I64]),
+    "kmls_exclusive_scan_i32": (ctypes.c_int, [_P, _I64, _P, _P, _SZ, _P]),
+    "kmls_set_capacity": (_I64, [_I64]),
+    "kmls_itemset_set_build": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P]),
+    "kmls_join_count": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _SZ, _P]),
+    "kmls_join_write": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _P,
+                                       _P, _P, _P, _SZ, _P]),
+    "kmls_count_candidates": (ctypes.c_int, [_P, _I64, _P, _I32, _P, _I64, _P, _P, _I64, _P, _P]),
+    "kmls_emit_count": (ctypes.c_int, [_P, _I64, _I32, _P, _P, _SZ, _P]),
+    "kmls_emit_level": (ctypes.c_int, [_P, _I32, _P, _P, _P, _I64, _I32, _P, _P, _P, _P]),
+    "kmls_itemset_map_build": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _P]),
+    "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _P, _P, _P]),
+    "kmls_rules_write": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _P, _P, _P, _P,
+                                        _P, _P, _P, _P]),
+}
+
+_lib = None
+
+
+class KmlsError(RuntimeError):
+    """A call into libkmls_b200.so failed (CUDA error, bad argument, or a buffer that would
+    have overflowed — the library never truncates)."""
+
+
+def load() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise KmlsError(
+                f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                "g.build()'` (or `make -C kubernetes-machine-learning-server_b200/csrc`). "
+                "There is no CPU fallback for this path.")
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the library lacks a declared symbol
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def _arg(a):
+    # torch tensors are passed as their device (or host) address
+    if hasattr(a, "data_ptr"):
+        return a.data_ptr()
+    return a
+
+
+def call(name: str, *args):
+    """Call an int-returning entry point; raise KmlsError with the library's text on failure."""
+    lib = load()
+    rc = getattr(lib, name)(*[_arg(a) for a in args])
+    if rc != 0:
+        msg = lib.kmls_last_error().decode("utf-8", "replace")
+        raise KmlsError(f"{name} failed with code {rc}: {msg}")
+
+
+def value(name: str, *args):
+    """Call a value-returning helper (sizes)."""
+    return getattr(load(), name)(*[_arg(a) for a in args])

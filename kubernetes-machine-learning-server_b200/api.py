@@ -1,0 +1,187 @@
+"""The reference's plugin boundary for the rule-generation hot path.
+
+``calculate_and_save_fp_growth_fast`` has the name, arguments, return tuple, printed lines
+and error behaviour of reference machine-learning/main.py:262-313, so the job's ``__main__``
+(main.py:476, :461) and ``rest_api`` (rest_api/app/main.py:74-76, :229-254) keep working
+unchanged; behind it the work runs on the GPU through ``libkmls_b200.so``.
+
+Additions that the reference does not have: the frequent-itemset table
+and the rule table (antecedents, consequents, support, confidence, lift) are kept on the
+returned ``last_result`` / written by ``save_rules``; ``MIN_CONFIDENCE`` (default 0.04, the
+value hard-coded in the reference's dormant path, main.py:226-227) selects the rules.
+"""
+from __future__ import annotations
+
+import os
+import pickle
+from typing import Dict, Iterable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import _lib, miner
+
+MIN_CONFIDENCE = float(os.getenv("MIN_CONFIDENCE", 0.04))
+RULES_FILE = os.getenv("RULES_FILE", "rules.pickle")
+
+# The reference reads a module-global `total_songs` (main.py:49, set at :436, read at :304).
+# The patched job passes it as a keyword; this global is the fallback with the same name.
+total_songs = None
+
+# Result of the most recent call (itemset tables, rule table, timings) for callers that want
+# more than the reference's return value.
+last_result: Optional[dict] = None
+
+
+def _device() -> torch.device:
+    if not torch.cuda.is_available():
+        raise _lib.KmlsError("no CUDA device: the GPU rule-generation path has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def encode_transactions(transactions: Sequence[Sequence[str]]):
+    """Host half of TransactionEncoder.fit: ``columns_ = sorted(unique names)`` and the
+    transactions as ids in CSR. (Bit-packing — ``transform`` — happens on the device.)"""
+    lens = np.fromiter((len(t) for t in transactions), dtype=np.int64, count=len(transactions))
+    offsets = np.zeros(len(transactions) + 1, dtype=np.int64)
+    np.cumsum(lens, out=offsets[1:])
+    flat: List = []
+    for t in transactions:
+        flat.extend(t)
+    columns = sorted(set(flat))
+    mapping = {name: i for i, name in enumerate(columns)}
+    ids = np.fromiter((mapping[x] for x in flat), dtype=np.int32, count=len(flat))
+    return columns, offsets, ids
+
+
+def _shard(offsets: np.ndarray, ids: np.ndarray, rank: int, world: int):
+    n = len(offsets) - 1
+    lo, hi = (n * rank) // world, (n * (rank + 1)) // world
+    o = offsets[lo:hi + 1]
+    return (o - o[0]).astype(np.int64), ids[o[0]:o[-1]]
+
+
+def _dist_group():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        return dist.group.WORLD, dist.get_rank(), dist.get_world_size()
+    return None, 0, 1
+
+
+def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: float,
+             min_confidence: Optional[float] = None, max_len: Optional[int] = None):
+    """Host CSR of track ids in, device tables out: (MineResult, RuleTable or None).
+    Under torchrun each rank keeps a contiguous range of the playlists."""
+    device = _device()
+    group, rank, world = _dist_group()
+    n_total = len(offsets) - 1
+    if world > 1:
+        offsets, ids = _shard(offsets, ids, rank, world)
+    d_off = torch.from_numpy(np.ascontiguousarray(offsets)).to(device, non_blocking=True)
+    d_ids = torch.from_numpy(np.ascontiguousarray(ids)).to(device, non_blocking=True)
+    res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
+                         group=group, max_len=max_len)
+    rules = None
+    if min_confidence is not None:
+        rules = miner.generate_rules(res, min_confidence)
+    return res, rules
+
+
+def recommendations_from_result(res: miner.MineResult, columns: Sequence[str]
+                                ) -> Dict[str, Dict[str, float]]:
+    """The fold of main.py:282-296 from the level-1 and level-2 tables: every frequent single
+    name is a key (possibly with an empty dict) and d[a][b] = support({a, b}),
+    which is what the reference's max over all itemsets containing both evaluates to."""
+    out: Dict[str, Dict[str, float]] = {}
+    rows = res.row_items.cpu().numpy()
+    names = [columns[i] for i in rows]
+    # iterate singles in the caller's column order for a stable key order
+    for r in np.argsort(rows, kind="stable"):
+        out[names[r]] = {}
+    if len(res.levels) >= 2:
+        it2, ct2 = res.levels[1]
+        sup = torch.empty(ct2.numel(), dtype=torch.float64, device=ct2.device)
+        _lib.call("kmls_supports_f64", ct2, int(ct2.numel()), res.n_playlists, sup,
+                  torch.cuda.current_stream().cuda_stream)
+        it2 = it2.cpu().numpy()
+        sup = sup.cpu().numpy()
+        for (a, b), s in zip(it2.tolist(), sup.tolist()):
+            out[names[a]][names[b]] = s
+            out[names[b]][names[a]] = s
+    return out
+
+
+def itemsets_frame(res: miner.MineResult, columns: Sequence[str]) -> pd.DataFrame:
+    """What ``fpgrowth(df, min_support, use_colnames=True)`` returns: columns ``support``
+    (count / N) and ``itemsets`` (frozenset of names); row order is not part of parity."""
+    off, items, counts = res.to_host()
+    n = res.n_playlists
+    return pd.DataFrame({
+        "support": [int(c) / n for c in counts],
+        "itemsets": [frozenset(columns[i] for i in items[off[j]:off[j + 1]]) for j in range(len(counts))],
+    })
+
+
+def rules_frame(res: miner.MineResult, rules: miner.RuleTable, columns: Sequence[str]) -> pd.DataFrame:
+    rows = miner.rules_to_host(res, rules)
+    return pd.DataFrame({
+        "antecedents": [frozenset(columns[i] for i in a) for a, _, _, _, _ in rows],
+        "consequents": [frozenset(columns[i] for i in c) for _, c, _, _, _ in rows],
+        "support": [s for _, _, s, _, _ in rows],
+        "confidence": [c for _, _, _, c, _ in rows],
+        "lift": [l for _, _, _, _, l in rows],
+    })
+
+
+def calculate_and_save_fp_growth_fast(playlist_dict: dict, min_support=0.07, total_songs=None,
+                                      min_confidence: Optional[float] = None,
+                                      max_len: Optional[int] = None):
+    """Drop-in for reference machine-learning/main.py:262-313.
+
+    Returns ``(songs_to_song_sets, info, (songs_without_recommendations, duration))`` with
+    ``songs_to_song_sets: dict[str, dict[str, float]]`` made of plain Python objects
+    (rest_api's image has neither numpy nor torch). ``min_support <= 0`` raises ValueError as
+    mlxtend does; an empty result is ``{}`` (the reference's ``data is None`` branch,
+    main.py:274-277, is unreachable). CUDA failures raise (no CPU fallback)."""
+    global last_result
+    start_time = pd.Timestamp.now()
+    if min_support <= 0.0:
+        miner.thresholds(min_support, 1)
+    transactions = list(playlist_dict.values())
+    columns, offsets, ids = encode_transactions(transactions)
+    conf = MIN_CONFIDENCE if min_confidence is None else min_confidence
+    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf, max_len)
+    songs_to_song_sets = recommendations_from_result(res, columns)
+
+    ts = total_songs if total_songs is not None else globals()["total_songs"]
+    if ts is None:
+        ts = len(columns)
+    songs_without_recommendations = ts - len(songs_to_song_sets.keys())
+    print("Songs without recommendations:", songs_without_recommendations)
+    end_time = pd.Timestamp.now()
+    duration = end_time - start_time
+    print(f"Time elapsed in rule generation: {duration}")
+    info = f"min_support: {min_support} \tmissing songs: {songs_without_recommendations} \ttime: {duration}"
+    runtime_info = (songs_without_recommendations, duration)
+    last_result = {"columns": columns, "itemsets": res, "rules": rules, "min_confidence": conf}
+    return songs_to_song_sets, info, runtime_info
+
+
+def save_rules(path: str, result: Optional[dict] = None) -> None:
+    """Write the extra rule artifact: a dict of plain-Python columns ``antecedents``,
+    ``consequents`` (tuples of names), ``support``, ``confidence``, ``lift`` (floats),
+    loadable without numpy/torch. rest_api ignores it."""
+    result = result or last_result
+    if result is None or result.get("rules") is None:
+        raise ValueError("no rule table to save: run calculate_and_save_fp_growth_fast first")
+    df = rules_frame(result["itemsets"], result["rules"], result["columns"])
+    data = {
+        "antecedents": [tuple(sorted(a)) for a in df["antecedents"]],
+        "consequents": [tuple(sorted(c)) for c in df["consequents"]],
+        "support": [float(x) for x in df["support"]],
+        "confidence": [float(x) for x in df["confidence"]],
+        "lift": [float(x) for x in df["lift"]],
+    }
+    with open(path, "wb") as f:
+        pickle.dump(data, f)

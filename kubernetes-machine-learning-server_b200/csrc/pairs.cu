@@ -1,0 +1,236 @@
+// Level 2 of the hot path: pair co-occurrence counts and the frequent-pair table.
+//
+// Replaces the k=2 part of mlxtend's FP-tree mining (fpg_step / conditional_tree, reached
+// from reference machine-learning/main.py:272) and supplies everything the reference's
+// dict fold (main.py:282-296) needs: by anti-monotonicity the folded value of (a, b) is
+// exactly support({a, b}).
+#include "common.cuh"
+#include "kmls_b200.h"
+
+namespace kmls {
+
+// ---------------------------------------------------------------------------------------
+// K2 (CUDA-core form): C[i][j] = popcount(row_i AND row_j) for a 64x64 tile of row pairs.
+// 256 threads, each 4x4 pairs; both operand tiles staged in shared memory KC words at a
+// time. Only tiles with tile_j >= tile_i are computed; both C[i][j] and C[j][i] are written
+// so later lookups need no ordering. `ksplit` > 1 splits the playlist dimension over
+// blockIdx.y and accumulates with atomicAdd into a zeroed C.
+// The tensor-core form of the same contraction is in pair_gemm.cu.
+// ---------------------------------------------------------------------------------------
+constexpr int kPT = 64;   // tile edge (rows)
+constexpr int kKC = 32;   // words per staged chunk
+
+__global__ void __launch_bounds__(256) k_pair_counts(const uint32_t* __restrict__ bitmap,
+                                                     int32_t n_rows, int64_t row_words,
+                                                     int32_t n_tiles, int64_t words_per_split,
+                                                     int use_atomics, int32_t* __restrict__ C) {
+  // linear upper-triangular tile index -> (ti, tj), ti <= tj
+  int t = blockIdx.x, ti = 0;
+  {
+    int rem = t, len = n_tiles;
+    while (rem >= len) { rem -= len; --len; ++ti; }
+    t = ti + rem;
+  }
+  const int tj = t;
+  __shared__ uint32_t sa[kPT][kKC + 1];
+  __shared__ uint32_t sb[kPT][kKC + 1];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // j index group, i index group
+  int acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0;
+
+  const int64_t w_begin = (int64_t)blockIdx.y * words_per_split;
+  const int64_t w_end = min(row_words, w_begin + words_per_split);
+  const int lr = threadIdx.x >> 5, lw = threadIdx.x & 31;  // loader: 8 rows x 32 words per pass
+  for (int64_t w0 = w_begin; w0 < w_end; w0 += kKC) {
+#pragma unroll
+    for (int r = 0; r < kPT; r += 8) {
+      const int ri = ti * kPT + r + lr, rj = tj * kPT + r + lr;
+      const int64_t w = w0 + lw;
+      sa[r + lr][lw] = (ri < n_rows && w < w_end) ? __ldg(bitmap + (int64_t)ri * row_words + w) : 0u;
+      sb[r + lr][lw] = (rj < n_rows && w < w_end) ? __ldg(bitmap + (int64_t)rj * row_words + w) : 0u;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int w = 0; w < kKC; ++w) {
+      uint32_t a[4], b[4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x) { a[x] = sa[ty * 4 + x][w]; b[x] = sb[tx + 16 * x][w]; }
+#pragma unroll
+      for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[x][y] += __popc(a[x] & b[y]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int x = 0; x < 4; ++x)
+#pragma unroll
+    for (int y = 0; y < 4; ++y) {
+      const int i = ti * kPT + ty * 4 + x, j = tj * kPT + tx + 16 * y;
+      if (i >= n_rows || j >= n_rows) continue;
+      if (ti == tj && j < i) continue;  // the mirrored thread writes this one
+      if (use_atomics) {
+        atomicAdd(C + (int64_t)i * n_rows + j, acc[x][y]);
+        if (i != j) atomicAdd(C + (int64_t)j * n_rows + i, acc[x][y]);
+      } else {
+        C[(int64_t)i * n_rows + j] = acc[x][y];
+        C[(int64_t)j * n_rows + i] = acc[x][y];
+      }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// K6 part 1: frequent-pair table from C. Row a keeps the b > a with C[a][b] >= thr, in
+// ascending b: per-row counts -> one-block scan -> ordered write (ballot + popc rank).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_pair_row_counts(const int32_t* __restrict__ C,
+                                                         int32_t n_rows, int32_t thr,
+                                                         int64_t* __restrict__ row_cnt) {
+  const int lane = threadIdx.x & 31;
+  for (int a = blockIdx.x * 8 + (threadIdx.x >> 5); a < n_rows; a += gridDim.x * 8) {
+    const int32_t* row = C + (int64_t)a * n_rows;
+    int acc = 0;
+    for (int b = a + 1 + lane; b < n_rows; b += 32) acc += __ldg(row + b) >= thr;
+    acc = warp_sum(acc);
+    if (lane == 0) row_cnt[a] = acc;
+  }
+}
+
+// Exclusive scan of n int64 values by ONE block (n is a row count: at most ~1e5).
+__global__ void __launch_bounds__(1024) k_scan_one_block(const int64_t* __restrict__ in, int32_t n,
+                                                         int64_t* __restrict__ out) {
+  __shared__ int64_t warp_tot[32];
+  __shared__ int64_t carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + threadIdx.x;
+    int64_t v = i < n ? in[i] : 0, incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      int64_t u = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += u;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int64_t t = warp_tot[lane], ti = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        int64_t u = __shfl_up_sync(0xffffffffu, ti, o);
+        if (lane >= o) ti += u;
+      }
+      warp_tot[lane] = ti - t;  // exclusive over warps
+    }
+    __syncthreads();
+    const int64_t c = carry;
+    if (i < n) out[i] = c + warp_tot[warp] + incl - v;
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = c + warp_tot[31] + incl;
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[n] = carry;
+}
+
+__global__ void __launch_bounds__(256) k_pair_write(const int32_t* __restrict__ C, int32_t n_rows,
+                                                    int32_t thr, const int64_t* __restrict__ row_off,
+                                                    int64_t capacity, int32_t* __restrict__ items2,
+                                                    int32_t* __restrict__ counts) {
+  const int lane = threadIdx.x & 31;
+  for (int a = blockIdx.x * 8 + (threadIdx.x >> 5); a < n_rows; a += gridDim.x * 8) {
+    const int32_t* row = C + (int64_t)a * n_rows;
+    int64_t pos = row_off[a];
+    if (row_off[a + 1] > capacity) continue;  // host reports the overflow
+    for (int b0 = a + 1; b0 < n_rows; b0 += 32) {
+      const int b = b0 + lane;
+      const int32_t c = b < n_rows ? __ldg(row + b) : -1;
+      const bool keep = b < n_rows && c >= thr;
+      const uint32_t m = __ballot_sync(0xffffffffu, keep);
+      if (keep) {
+        const int64_t o = pos + __popc(m & ((1u << lane) - 1));
+        items2[2 * o] = a;
+        items2[2 * o + 1] = b;
+        counts[o] = c;
+      }
+      pos += __popc(m);
+    }
+  }
+}
+
+// support = count / N exactly as Python's int / int true division gives it for these
+// magnitudes (both fit in 53 bits, so the quotient of the two doubles is correctly rounded).
+__global__ void k_supports(const int32_t* __restrict__ counts, int64_t n, double n_total,
+                           double* __restrict__ out) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = __ddiv_rn((double)counts[i], n_total);
+}
+
+}  // namespace kmls
+
+using namespace kmls;
+
+extern "C" int kmls_pair_counts(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                                int32_t* d_pair, kmls_stream_t stream) {
+  KMLS_REQUIRE(n_rows >= 0 && row_words >= 0, "kmls_pair_counts: negative size");
+  if (n_rows == 0) return 0;
+  KMLS_REQUIRE(d_bitmap && d_pair, "kmls_pair_counts: null pointer");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n_tiles = (n_rows + kPT - 1) / kPT;
+  const int64_t tri = (int64_t)n_tiles * (n_tiles + 1) / 2;
+  KMLS_REQUIRE(tri <= 0x7fffffff, "kmls_pair_counts: too many rows");
+  const int64_t chunks = (row_words + kKC - 1) / kKC;
+  int64_t ksplit = 1;
+  const int64_t target = (int64_t)num_sms() * 4;
+  if (tri < target) ksplit = std::min<int64_t>(std::max<int64_t>(chunks / 4, 1), (target + tri - 1) / tri);
+  ksplit = std::min<int64_t>(ksplit, 65535);
+  const int64_t words_per_split = ((chunks + ksplit - 1) / ksplit) * kKC;
+  ksplit = (row_words + words_per_split - 1) / words_per_split;
+  if (ksplit < 1) ksplit = 1;
+  if (ksplit > 1) KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
+  dim3 grid((unsigned)tri, (unsigned)ksplit);
+  k_pair_counts<<<grid, 256, 0, s>>>(d_bitmap, n_rows, row_words, n_tiles, words_per_split,
+                                     ksplit > 1 ? 1 : 0, d_pair);
+  KMLS_LAUNCHED("k_pair_counts");
+  return 0;
+}
+
+extern "C" int kmls_pair_select(const int32_t* d_pair, int32_t n_rows, int32_t thr,
+                                int64_t capacity, int64_t* d_row_off, int32_t* d_items2,
+                                int32_t* d_counts, kmls_stream_t stream) {
+  KMLS_REQUIRE(n_rows >= 0 && capacity >= 0, "kmls_pair_select: negative size");
+  KMLS_REQUIRE(d_row_off, "kmls_pair_select: d_row_off is null");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n_rows == 0) {
+    KMLS_CUDA(cudaMemsetAsync(d_row_off, 0, sizeof(int64_t), s));
+    return 0;
+  }
+  KMLS_REQUIRE(d_pair, "kmls_pair_select: null pointer");
+  // d_row_off doubles as the count buffer: counts go to [1, n_rows], are scanned in place
+  // from a shifted view. Keep it simple: counts into d_row_off[0..n), scan in place.
+  int grid = std::min((n_rows + 7) / 8, num_sms() * 16);
+  k_pair_row_counts<<<grid, 256, 0, s>>>(d_pair, n_rows, thr, d_row_off);
+  KMLS_LAUNCHED("k_pair_row_counts");
+  k_scan_one_block<<<1, 1024, 0, s>>>(d_row_off, n_rows, d_row_off);
+  KMLS_LAUNCHED("k_scan_one_block");
+  if (capacity > 0) {
+    KMLS_REQUIRE(d_items2 && d_counts, "kmls_pair_select: null output");
+    k_pair_write<<<grid, 256, 0, s>>>(d_pair, n_rows, thr, d_row_off, capacity, d_items2, d_counts);
+    KMLS_LAUNCHED("k_pair_write");
+  }
+  return 0;
+}
+
+extern "C" int kmls_supports_f64(const int32_t* d_counts, int64_t n, int64_t n_playlists_total,
+                                 double* d_out, kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && n_playlists_total > 0, "kmls_supports_f64: bad size");
+  if (n == 0) return 0;
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 8);
+  k_supports<<<grid, 256, 0, (cudaStream_t)stream>>>(d_counts, n, (double)n_playlists_total, d_out);
+  KMLS_LAUNCHED("k_supports");
+  return 0;
+}

@@ -1,0 +1,380 @@
+"""Level-wise frequent-itemset mining on one or several B200s.
+
+Host control loop around the CUDA kernels of ``libkmls_b200.so``. It replaces what the
+reference delegates to mlxtend at machine-learning/main.py:267-272
+(``TransactionEncoder().fit().transform()`` + ``fpgrowth(df, min_support, use_colnames=True)``)
+and produces the same result set, level by level:
+
+    level 1   K_hist -> [allreduce] -> K0 encode -> K1 popcount -> [allreduce]
+    level 2   K2 pair counts -> [allreduce] -> pair select
+    level k   K3 join+prune -> K4 count -> [allreduce] -> filter/emit   (until empty)
+
+PyTorch supplies device memory, the stream and ``torch.distributed``; every computation on
+playlist data is one of this repository's kernels. Multi-GPU: each rank holds a contiguous
+range of playlists (bitmap columns); candidate generation is replicated and deterministic,
+so the only exchange is one integer sum-allreduce per level.
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+from typing import List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+
+
+def thresholds(min_support: float, n_transactions: int) -> Tuple[int, int]:
+    """The two integer thresholds mlxtend's two float/int tests amount to.
+
+    T1 = min{c : c / float(N) >= min_support}   level 1, fpcommon.setup_fptree
+    Tk = math.ceil(min_support * N)             levels >= 2, fpgrowth.fpgrowth
+    Computed on the host exactly as Python computes them; the device only ever compares
+    integers."""
+    if min_support <= 0.0:
+        raise ValueError(
+            "`min_support` must be a positive number within the interval `(0, 1]`. "
+            "Got %s." % min_support)
+    n = int(n_transactions)
+    tk = int(math.ceil(min_support * n))
+    if n == 0:
+        return 0, tk
+    c = max(0, min(n + 1, tk))
+    while c > 0 and (c - 1) / float(n) >= min_support:
+        c -= 1
+    while c <= n and not (c / float(n) >= min_support):
+        c += 1
+    return c, tk
+
+
+@dataclasses.dataclass
+class MineResult:
+    """Frequent itemsets as device tables. ``levels[k-1] = (items[n_k, k], counts[n_k])``
+    where members are ROW indices of the bitmap (ascending support order); ``row_items``
+    maps a row to the caller's track id."""
+    n_playlists: int
+    t1: int
+    tk: int
+    row_items: torch.Tensor                       # int32[F1]: row -> track id
+    levels: List[Tuple[torch.Tensor, torch.Tensor]]
+    pair_counts: Optional[torch.Tensor] = None    # int32[F1, F1]
+    stats: Optional[dict] = None
+
+    @property
+    def n_itemsets(self) -> int:
+        return sum(int(c.numel()) for _, c in self.levels)
+
+    def to_host(self):
+        """(offsets int64[M+1], items int32[sum k] as TRACK ids, counts int64[M]); itemsets
+        ordered by size then lexicographically by row, members in row order."""
+        offs, items, counts = [np.zeros(1, np.int64)], [], []
+        base = 0
+        rows = self.row_items.cpu().numpy()
+        for k, (it, ct) in enumerate(self.levels, start=1):
+            n = int(ct.numel())
+            if n == 0:
+                continue
+            items.append(rows[it.cpu().numpy().reshape(-1)])
+            counts.append(ct.cpu().numpy().astype(np.int64))
+            offs.append(base + k * np.arange(1, n + 1, dtype=np.int64))
+            base += k * n
+        if not items:
+            return np.zeros(1, np.int64), np.zeros(0, np.int32), np.zeros(0, np.int64)
+        return np.concatenate(offs), np.concatenate(items).astype(np.int32), np.concatenate(counts)
+
+    def as_dict(self):
+        off, items, counts = self.to_host()
+        return {frozenset(items[off[i]:off[i + 1]].tolist()): int(counts[i])
+                for i in range(len(counts))}
+
+
+class _Dev:
+    """Small conveniences over torch allocations on the current CUDA device."""
+
+    def __init__(self, device):
+        self.device = device
+        self.scratch = torch.empty(1 << 20, dtype=torch.uint8, device=device)
+
+    def empty(self, n, dtype):
+        return torch.empty(max(int(n), 1), dtype=dtype, device=self.device)[:int(n)]
+
+    def scan_scratch(self, n):
+        need = int(_lib.value("kmls_scan_scratch_bytes", int(n)))
+        if self.scratch.numel() < need:
+            self.scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self.scratch, self.scratch.numel()
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _allreduce(t: torch.Tensor, group):
+    if group is not None:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+
+
+def _world(group):
+    if group is None:
+        return 1
+    import torch.distributed as dist
+    return dist.get_world_size(group)
+
+
+def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
+             n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
+             max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
+             pair_impl: str = "auto") -> MineResult:
+    """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
+    playlist, this rank's shard) for itemsets with the reference's thresholds.
+
+    ``n_playlists_total`` is N of the whole job (sum over ranks); it defaults to the local
+    count (allreduced when ``group`` is given)."""
+    if min_support <= 0.0:
+        thresholds(min_support, 1)  # raises the reference's ValueError
+    if not (offsets.is_cuda and items.is_cuda):
+        raise _lib.KmlsError("mine_csr needs CUDA tensors: this path has no CPU fallback")
+    assert offsets.dtype == torch.int64 and items.dtype == torch.int32
+    dev = _Dev(offsets.device)
+    s = _stream()
+    n_local = int(offsets.numel()) - 1
+    nnz = int(items.numel())
+    if n_playlists_total is None:
+        n_playlists_total = n_local
+        if group is not None:
+            t = torch.tensor([n_local], dtype=torch.int64, device=dev.device)
+            _allreduce(t, group)
+            n_playlists_total = int(t.item())
+    n_total = int(n_playlists_total)
+    t1, tk = thresholds(min_support, n_total)
+    stats = {"levels": [], "t1": t1, "tk": tk, "n_playlists": n_total, "nnz_local": nnz}
+    empty_i32 = dev.empty(0, torch.int32)
+
+    def result(row_items, levels, pair=None):
+        return MineResult(n_total, t1, tk, row_items, levels, pair, stats)
+
+    if n_total == 0 or n_items == 0:
+        return result(empty_i32, [])
+
+    # ---- level 1 -------------------------------------------------------------------------
+    occ = dev.empty(n_items, torch.int32)
+    _lib.call("kmls_item_histogram", items, nnz, n_items, occ, s)
+    _allreduce(occ, group)
+    cand = torch.nonzero(occ >= max(t1, 1)).reshape(-1)              # ascending track id
+    if cand.numel() == 0:
+        return result(empty_i32, [])
+    order = torch.argsort(occ[cand], stable=True)                    # by (occ, id)
+    cand = cand[order]
+    n_rows = int(cand.numel())
+    row_of_item = torch.full((n_items,), -1, dtype=torch.int32, device=dev.device)
+    row_of_item[cand] = torch.arange(n_rows, dtype=torch.int32, device=dev.device)
+    row_words = int(_lib.value("kmls_bitmap_row_words", n_local))
+    bitmap = dev.empty(n_rows * row_words, torch.int32)
+    _lib.call("kmls_encode_bitmap", offsets, items, n_local, row_of_item, n_items, n_rows,
+              bitmap, row_words, s)
+    counts1 = dev.empty(n_rows, torch.int32)
+    _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s)
+    _allreduce(counts1, group)
+    if not bool(torch.equal(counts1, occ[cand])):
+        # some playlist repeated a track: exact supports differ from the occurrence counts,
+        # so drop rows that fell below T1 and restore ascending-support order
+        keep = torch.nonzero(counts1 >= max(t1, 1)).reshape(-1)
+        order = torch.argsort(counts1[keep], stable=True)
+        src = keep[order].to(torch.int32)
+        n_rows = int(src.numel())
+        if n_rows == 0:
+            return result(empty_i32, [])
+        bitmap2 = dev.empty(n_rows * row_words, torch.int32)
+        _lib.call("kmls_gather_rows", bitmap, src, n_rows, row_words, bitmap2, s)
+        bitmap, counts1, cand = bitmap2, counts1[src.long()].contiguous(), cand[src.long()]
+    row_items = cand.to(torch.int32)
+    lvl1_items = torch.arange(n_rows, dtype=torch.int32, device=dev.device).reshape(-1, 1)
+    levels = [(lvl1_items, counts1)]
+    stats["levels"].append({"k": 1, "candidates": n_items, "frequent": n_rows})
+    stats["row_words"] = row_words
+    if n_rows < 2 or (max_len is not None and max_len <= 1):
+        return result(row_items, levels)
+
+    # ---- level 2 -------------------------------------------------------------------------
+    pair = dev.empty(n_rows * n_rows, torch.int32)
+    if pair_impl == "auto":
+        pair_impl = "popc"
+    if pair_impl == "popc":
+        _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
+    else:
+        raise ValueError(f"unknown pair_impl {pair_impl!r}")
+    _allreduce(pair, group)
+    thr = tk
+    if t1 < tk:
+        # mlxtend's root single-path shortcut applies no Tk test:
+        # the root FP-tree is one path iff the supports are nested, i.e. every pair count
+        # equals the rarer member's support. Rows are in ascending-support order.
+        p2 = pair.view(n_rows, n_rows)
+        upper = torch.triu(torch.ones_like(p2, dtype=torch.bool), 1)
+        if bool(((p2 == counts1.view(-1, 1)) | ~upper).all()):
+            thr = t1
+    stats["thr_k"] = thr
+    row_off = dev.empty(n_rows + 1, torch.int64)
+    _lib.call("kmls_pair_select", pair, n_rows, thr, 0, row_off, 0, 0, s)
+    n2 = int(row_off[n_rows].item())
+    stats["levels"].append({"k": 2, "candidates": n_rows * (n_rows - 1) // 2, "frequent": n2})
+    if n2 == 0:
+        return result(row_items, levels, pair.view(n_rows, n_rows) if keep_pair_counts else None)
+    items_k = dev.empty(n2 * 2, torch.int32)
+    counts_k = dev.empty(n2, torch.int32)
+    _lib.call("kmls_pair_select", pair, n_rows, thr, n2, row_off, items_k, counts_k, s)
+    levels.append((items_k.view(n2, 2), counts_k))
+    total = n_rows + n2
+
+    # ---- levels k >= 3 -------------------------------------------------------------------
+    k = 2
+    while (max_len is None or k < max_len) and int(counts_k.numel()) >= 2:
+        n = int(counts_k.numel())
+        scratch, sbytes = dev.scan_scratch(n)
+        if k >= 3:
+            cap = int(_lib.value("kmls_set_capacity", n))
+            slots = dev.empty(cap, torch.int64)
+            _lib.call("kmls_itemset_set_build", items_k, n, k, slots, cap, s)
+        else:
+            cap, slots = 0, 0
+        kept_cnt = dev.empty(n, torch.int32)
+        kept_mask = dev.empty(n, torch.int32)
+        kept_off = dev.empty(n + 1, torch.int64)
+        _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair, n_rows, thr, kept_cnt,
+                  kept_mask, kept_off, scratch, sbytes, s)
+        n_cand = int(kept_off[n].item())
+        if n_cand == 0:
+            break
+        if total + n_cand > max_itemsets * 4:
+            raise _lib.KmlsError(f"level {k + 1}: {n_cand} candidates exceed the max_itemsets guard")
+        cand_p = dev.empty(n_cand, torch.int32)
+        cand_q = dev.empty(n_cand, torch.int32)
+        grp_p = dev.empty(n, torch.int32)
+        n_groups_d = dev.empty(1, torch.int64)
+        _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair, n_rows, thr, kept_cnt,
+                  kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
+        n_groups = int(n_groups_d.item())
+        cand_cnt = dev.empty(n_cand, torch.int32)
+        _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
+                  kept_off, cand_q, n_cand, cand_cnt, s)
+        _allreduce(cand_cnt, group)
+        scratch, sbytes = dev.scan_scratch(n_cand)
+        out_off = dev.empty(n_cand + 1, torch.int64)
+        _lib.call("kmls_emit_count", cand_cnt, n_cand, thr, out_off, scratch, sbytes, s)
+        n_next = int(out_off[n_cand].item())
+        stats["levels"].append({"k": k + 1, "candidates": n_cand, "groups": n_groups,
+                                "frequent": n_next})
+        if n_next == 0:
+            break
+        total += n_next
+        if total > max_itemsets:
+            raise _lib.KmlsError(
+                f"more than max_itemsets={max_itemsets} frequent itemsets at level {k + 1}; "
+                "raise the guard or min_support (results are never truncated)")
+        items_n = dev.empty(n_next * (k + 1), torch.int32)
+        counts_n = dev.empty(n_next, torch.int32)
+        _lib.call("kmls_emit_level", items_k, k, cand_p, cand_q, cand_cnt, n_cand, thr, out_off,
+                  items_n, counts_n, s)
+        k += 1
+        items_k, counts_k = items_n, counts_n
+        levels.append((items_k.view(n_next, k), counts_k))
+    return result(row_items, levels, pair.view(n_rows, n_rows) if keep_pair_counts else None)
+
+
+@dataclasses.dataclass
+class RuleTable:
+    """Rules as device columns: rule r is about itemset ``itemset[r]`` (global id: level
+    tables concatenated in level order); bit t of ``antecedent[r]`` selects its t-th member
+    (row order) into the antecedent, the rest is the consequent."""
+    itemset: torch.Tensor      # int32[R]
+    antecedent: torch.Tensor   # int32[R] (bit mask)
+    support: torch.Tensor      # float64[R]
+    confidence: torch.Tensor   # float64[R]
+    lift: torch.Tensor         # float64[R]
+    arena_items: torch.Tensor  # int32: all level tables' members (rows), level after level
+    level_sizes: List[int]     # index k -> number of k-itemsets (index 0 unused)
+
+    @property
+    def n_rules(self) -> int:
+        return int(self.itemset.numel())
+
+
+def generate_rules(res: MineResult, min_confidence: float,
+                   max_rules: int = 2_000_000_000) -> RuleTable:
+    """fp64 confidence/lift for every (itemset, antecedent) split, kept iff
+    confidence >= min_confidence (mlxtend ``association_rules`` semantics)."""
+    device = res.row_items.device
+    dev = _Dev(device)
+    s = _stream()
+    max_k = len(res.levels)
+    sizes = np.zeros(max_k + 2, dtype=np.int64)
+    for k, (_, ct) in enumerate(res.levels, start=1):
+        sizes[k] = int(ct.numel())
+    n_all = int(sizes.sum())
+    e_i32 = dev.empty(0, torch.int32)
+    e_f64 = dev.empty(0, torch.float64)
+    if max_k < 2 or n_all == 0 or int(sizes[2:].sum()) == 0:
+        arena = torch.cat([it.reshape(-1) for it, _ in res.levels]) if res.levels else e_i32
+        return RuleTable(e_i32, e_i32, e_f64, e_f64, e_f64, arena, sizes.tolist())
+    arena_items = torch.cat([it.reshape(-1) for it, _ in res.levels])
+    arena_counts = torch.cat([ct for _, ct in res.levels])
+    cap = int(_lib.value("kmls_set_capacity", n_all))
+    keys = dev.empty(cap, torch.int64)
+    vals = dev.empty(cap, torch.int32)
+    sizes_ptr = sizes.ctypes.data
+    _lib.call("kmls_itemset_map_build", arena_items, arena_counts, sizes_ptr, max_k, keys, vals,
+              cap, s)
+    n_x = n_all - int(sizes[1])
+    rule_cnt = dev.empty(n_x, torch.int32)
+    missing = torch.zeros(1, dtype=torch.int32, device=device)
+    _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
+              res.n_playlists, float(min_confidence), rule_cnt, missing, s)
+    scratch, sbytes = dev.scan_scratch(n_x)
+    rule_off = dev.empty(n_x + 1, torch.int64)
+    _lib.call("kmls_exclusive_scan_i32", rule_cnt, n_x, rule_off, scratch, sbytes, s)
+    n_rules = int(rule_off[n_x].item())
+    if int(missing.item()) != 0:
+        raise _lib.KmlsError("rule generation: a subset of a frequent itemset is missing from the "
+                             "itemset table (table not downward closed)")
+    if n_rules > max_rules:
+        raise _lib.KmlsError(f"{n_rules} rules exceed max_rules={max_rules} (never truncated)")
+    o_set = dev.empty(n_rules, torch.int32)
+    o_ante = dev.empty(n_rules, torch.int32)
+    o_sup = dev.empty(n_rules, torch.float64)
+    o_conf = dev.empty(n_rules, torch.float64)
+    o_lift = dev.empty(n_rules, torch.float64)
+    if n_rules:
+        _lib.call("kmls_rules_write", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
+                  res.n_playlists, float(min_confidence), rule_off, o_set, o_ante, o_sup, o_conf,
+                  o_lift, missing, s)
+    return RuleTable(o_set, o_ante, o_sup, o_conf, o_lift, arena_items, sizes.tolist())
+
+
+def rules_to_host(res: MineResult, rules: RuleTable):
+    """[(antecedent frozenset, consequent frozenset, support, confidence, lift)] with TRACK
+    ids as members — plain Python objects, for artifacts and tests (small tables only)."""
+    rows = res.row_items.cpu().numpy()
+    arena = rules.arena_items.cpu().numpy()
+    sizes = rules.level_sizes
+    id_off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    item_off = np.zeros(len(sizes) + 1, dtype=np.int64)
+    for k in range(1, len(sizes)):
+        id_off[k + 1] = id_off[k] + sizes[k]
+        item_off[k + 1] = item_off[k] + sizes[k] * k
+    out = []
+    ids = rules.itemset.cpu().numpy()
+    ante = rules.antecedent.cpu().numpy().astype(np.uint32)
+    sup, conf, lift = (t.cpu().numpy() for t in (rules.support, rules.confidence, rules.lift))
+    for r in range(len(ids)):
+        gid = int(ids[r])
+        k = int(np.searchsorted(id_off, gid, side="right")) - 1
+        b = item_off[k] + (gid - id_off[k]) * k
+        members = rows[arena[b:b + k]]
+        m = int(ante[r])
+        a = frozenset(int(members[t]) for t in range(k) if m >> t & 1)
+        c = frozenset(int(members[t]) for t in range(k) if not m >> t & 1)
+        out.append((a, c, float(sup[r]), float(conf[r]), float(lift[r])))
+    return out

@@ -58,14 +58,19 @@ def track_names(n_tracks: int) -> List[str]:
 
 
 def mpd_standin(seed: int = 1, n_playlists: int = 2246, n_uris: int = 2171,
-                n_shared_names: int = 48, mean_draws: float = 112.0, alpha: float = 0.15,
+                n_shared_names: int = 48, body_draws: float = 112.0, alpha: float = 0.5,
+                n_hits: int = 16, hit_hi: float = 0.30, hit_lo: float = 0.10,
                 vocabulary: List[str] | None = None) -> Dict[str, np.ndarray]:
-    """Stand-in for ``2023_spotify_ds{1,2}.csv`` matched to the statistics the reference's
-    report logs for ds2: 2,246 playlists, 2,171 track URIs of
-    which 48 names are shared by two URIs, about 240k rows, shallow popularity skew.
+    """Stand-in for ``2023_spotify_ds{1,2}.csv`` shaped after what the reference's report
+    logs for ds2: 2,246 playlists, 2,171 track URIs of which 48 names are
+    shared by two URIs, about 240k rows. Popularity: Zipf(alpha) body plus ``n_hits`` hit
+    tracks each present in a playlist with probability hit_hi..hit_lo, calibrated so that the
+    number of names at or above 3 / 5 / 10 % support (about 1.6k / 0.57k / 0.14k) follows the
+    report's sweep plot (about 1.57k / 0.76k / 0.12k) and so that frequent pairs and triples
+    exist at MIN_SUPPORT = 0.05 (independent draws alone give none).
 
     Returns the columns the hot path's callers use: ``pid`` (int64), ``track_uri`` (str),
-    ``track_name`` (str), one row per (playlist, uri) occurrence.
+    ``track_name`` (str), one row per (playlist, uri) occurrence, rows shuffled.
     """
     rng = np.random.Generator(np.random.PCG64(seed))
     n_names = n_uris - n_shared_names
@@ -81,13 +86,16 @@ def mpd_standin(seed: int = 1, n_playlists: int = 2246, n_uris: int = 2171,
     cdf = np.cumsum(w)
     cdf /= cdf[-1]
     perm = rng.permutation(n_uris)
-    lens = np.clip(rng.poisson(mean_draws, n_playlists), 5, 250)
+    lens = np.clip(rng.poisson(body_draws, n_playlists), 5, 250)
     u = rng.random(int(lens.sum()))
     uri = perm[np.minimum(np.searchsorted(cdf, u), n_uris - 1)]
     pid = np.repeat(np.arange(n_playlists, dtype=np.int64), lens)
+    hit = rng.random((n_playlists, n_hits)) < np.linspace(hit_hi, hit_lo, n_hits)
+    hp, hh = np.nonzero(hit)
+    pid = np.concatenate([pid, hp])
+    uri = np.concatenate([uri, perm[hh]])
     key = np.unique(pid * n_uris + uri)
     pid, uri = key // n_uris, key % n_uris
-    # shuffle rows so the stand-in is not conveniently grouped by playlist
     order = rng.permutation(len(pid))
     pid, uri = pid[order], uri[order]
     names = np.array(vocabulary, dtype=object)[uri_name[uri]]

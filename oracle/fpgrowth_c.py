@@ -37,6 +37,9 @@ def _load():
         lib.oracle_fpgrowth_level_counts.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         lib.oracle_fpgrowth_copy.argtypes = [ctypes.c_void_p] * 4
         lib.oracle_fpgrowth_free.argtypes = [ctypes.c_void_p]
+        lib.oracle_rules.restype = ctypes.c_int64
+        lib.oracle_rules.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_int,
+                                     ctypes.c_void_p]
         _lib = lib
     return _lib
 
@@ -55,7 +58,10 @@ class Mined:
 
 
 def fpgrowth(offsets: np.ndarray, items: np.ndarray, n_items: int, t1: int, tk: int,
-             max_len: int = 0, store: bool = True, n_threads: int = 0) -> Mined:
+             max_len: int = 0, store: bool = True, n_threads: int = 0,
+             rules_min_confidence: float | None = None) -> Mined:
+    """With ``rules_min_confidence`` the association rules are generated too (needs
+    store=True); the result then carries ``n_rules`` and ``rule_checksum``."""
     lib = _load()
     offsets = np.ascontiguousarray(offsets, dtype=np.int64)
     items = np.ascontiguousarray(items, dtype=np.int32)
@@ -68,6 +74,14 @@ def fpgrowth(offsets: np.ndarray, items: np.ndarray, n_items: int, t1: int, tk: 
         lv = np.zeros(64, dtype=np.uint64)
         lib.oracle_fpgrowth_level_counts(h, lv.ctypes.data)
         out = Mined(int(n), int(lib.oracle_fpgrowth_checksum(h)), lv.astype(np.int64))
+        out.n_rules = out.rule_checksum = None
+        if rules_min_confidence is not None:
+            cs = ctypes.c_uint64(0)
+            out.n_rules = int(lib.oracle_rules(h, len(offsets) - 1, float(rules_min_confidence),
+                                               n_threads, ctypes.byref(cs)))
+            if out.n_rules < 0:
+                raise RuntimeError("oracle: a subset of a frequent itemset is missing")
+            out.rule_checksum = int(cs.value)
         if store:
             tot = lib.oracle_fpgrowth_total_items(h)
             out.offsets = np.zeros(n + 1, dtype=np.int64)
@@ -102,6 +116,26 @@ def itemset_checksum(offsets: np.ndarray, items: np.ndarray, counts: np.ndarray)
         c = np.asarray(counts, dtype=np.int64).astype(np.uint64)
         tot = _mix64(h ^ _mix64(c * np.uint64(0x100000001B3) + k))
         return int(np.sum(tot, dtype=np.uint64)) & _M64
+
+
+def rule_checksum(rules) -> int:
+    """Same checksum as oracle_rules() for an iterable of (antecedent ids, consequent ids,
+    support, confidence, lift)."""
+    tot = 0
+    with np.errstate(over="ignore"):
+        def h(ids):
+            return int(np.sum(_mix64(np.asarray(sorted(ids), dtype=np.int64).astype(np.uint64) + np.uint64(1)),
+                              dtype=np.uint64))
+
+        def bits(x):
+            return int(np.float64(x).view(np.uint64))
+
+        def m(x):
+            return int(_mix64(np.array([x & _M64], dtype=np.uint64))[0])
+        for a, c, s, conf, lift in rules:
+            v = h(a) ^ m(h(c) + 0x1234) ^ m(bits(conf)) ^ m(bits(lift) + 1) ^ m(bits(s) + 2)
+            tot = (tot + m(v)) & _M64
+    return tot
 
 
 def dense_to_csr(onehot: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:

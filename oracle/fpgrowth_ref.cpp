@@ -288,6 +288,90 @@ void oracle_fpgrowth_copy(void* h, int64_t* offsets, int32_t* items, int64_t* co
   if (!s.items.empty()) std::memcpy(items, s.items.data(), s.items.size() * sizeof(int32_t));
   if (!s.counts.empty()) std::memcpy(counts, s.counts.data(), s.counts.size() * sizeof(int64_t));
 }
+// mlxtend.frequent_patterns.association_rules(metric="confidence", min_threshold=c) over
+// the stored itemsets (run with store=1): for every itemset X, |X| >= 2, and every non-empty
+// proper subset A: confidence = (cX/N)/(cA/N), lift = confidence/(cC/N), kept iff
+// confidence >= c. Returns the number of rules and an order-independent checksum over
+// (antecedent, consequent, support, confidence, lift) bit patterns; -1 if a subset is missing.
+int64_t oracle_rules(void* h, int64_t n_total, double min_conf, int n_threads, uint64_t* checksum) {
+  auto& s = ((Result*)h)->sink;
+  const int64_t n = (int64_t)s.counts.size();
+  uint64_t cap = 1024;
+  while (cap < 2 * (uint64_t)n) cap <<= 1;
+  std::vector<uint64_t> keys(cap, 0);
+  std::vector<int32_t> vals(cap, -1);
+  auto key_of = [&](const int32_t* it, int k) {
+    uint64_t hsum = 0;
+    for (int i = 0; i < k; ++i) hsum += mix64((uint64_t)it[i] + 1);
+    return mix64(hsum ^ ((uint64_t)k << 56)) | 1ull;
+  };
+  for (int64_t i = 0; i < n; ++i) {
+    int k = (int)(s.offsets[i + 1] - s.offsets[i]);
+    uint64_t key = key_of(s.items.data() + s.offsets[i], k), hh = key & (cap - 1);
+    while (keys[hh]) hh = (hh + 1) & (cap - 1);
+    keys[hh] = key; vals[hh] = (int32_t)i;
+  }
+  auto lookup = [&](const int32_t* it, int k) -> int64_t {
+    uint64_t key = key_of(it, k), hh = key & (cap - 1);
+    while (keys[hh]) {
+      if (keys[hh] == key) {
+        int64_t j = vals[hh];
+        if (s.offsets[j + 1] - s.offsets[j] == k && std::equal(it, it + k, s.items.data() + s.offsets[j]))
+          return s.counts[j];
+      }
+      hh = (hh + 1) & (cap - 1);
+    }
+    return -1;
+  };
+  int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
+  if (nt < 1) nt = 1;
+  std::vector<uint64_t> sums(nt, 0);
+  std::vector<int64_t> cnts(nt, 0);
+  std::atomic<int64_t> next{0};
+  std::atomic<int> missing{0};
+  auto bits = [](double d) { uint64_t u; std::memcpy(&u, &d, 8); return u; };
+  auto worker = [&](int tid) {
+    int32_t a[64], c[64];
+    const int64_t step = 4096;
+    for (int64_t b = next.fetch_add(step); b < n; b = next.fetch_add(step)) {
+      for (int64_t i = b; i < std::min(n, b + step); ++i) {
+        const int k = (int)(s.offsets[i + 1] - s.offsets[i]);
+        if (k < 2 || k > 30) continue;
+        const int32_t* x = s.items.data() + s.offsets[i];
+        const double sx = (double)s.counts[i] / (double)n_total;
+        for (uint32_t m = 1; m + 1 < (1u << k); ++m) {
+          int na = 0, nc = 0;
+          uint64_t ha = 0, hc = 0;
+          for (int t = 0; t < k; ++t) {
+            if (m >> t & 1) { a[na++] = x[t]; ha += mix64((uint64_t)x[t] + 1); }
+            else { c[nc++] = x[t]; hc += mix64((uint64_t)x[t] + 1); }
+          }
+          const int64_t ca = lookup(a, na);
+          if (ca < 0) { missing = 1; continue; }
+          const double sa = (double)ca / (double)n_total;
+          const double conf = sx / sa;
+          if (!(conf >= min_conf)) continue;
+          const int64_t cc = lookup(c, nc);
+          if (cc < 0) { missing = 1; continue; }
+          const double lift = conf / ((double)cc / (double)n_total);
+          cnts[tid]++;
+          sums[tid] += mix64(ha ^ mix64(hc + 0x1234) ^ mix64(bits(conf)) ^ mix64(bits(lift) + 1) ^
+                             mix64(bits(sx) + 2));
+        }
+      }
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < nt; ++t) pool.emplace_back(worker, t);
+  worker(0);
+  for (auto& th : pool) th.join();
+  if (missing) return -1;
+  int64_t total = 0; uint64_t cs = 0;
+  for (int t = 0; t < nt; ++t) { total += cnts[t]; cs += sums[t]; }
+  *checksum = cs;
+  return total;
+}
+
 void oracle_fpgrowth_free(void* h) { delete (Result*)h; }
 
 }  // extern "C"

@@ -1,0 +1,334 @@
+"""Parity of the CUDA path (through the C-ABI) against the CPU oracle, the hand-computed
+vectors and the committed golden fixtures. Integer work is compared bit-exact; the fp64
+columns (support, confidence, lift) are compared for bit equality as well, which is tighter
+than the 1e-12 relative tolerance BASELINE.json allows."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import kmls_b200
+from kmls_b200 import _lib, synth
+from oracle import fpgrowth_c, mlxtend_restated as M
+from conftest import ROOT, load_hand_vectors
+
+pytestmark = pytest.mark.gpu
+CASES = load_hand_vectors()
+GOLDEN = json.load(open(os.path.join(ROOT, "tests", "golden", "generated_cases.json")))["cases"]
+
+
+def dev():
+    return torch.device("cuda", 0)
+
+
+def stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _key(fs):
+    return "|".join(sorted(fs))
+
+
+def oracle_dict(off, items, n_items, s, max_len=0):
+    t1, tk = M.thresholds(s, len(off) - 1)
+    return fpgrowth_c.fpgrowth(off, items, n_items, t1, tk, max_len=max_len).as_dict()
+
+
+def rule_checksum(rules):
+    import hashlib
+    tot = 0
+    for a, c, s, conf, lift in rules:
+        key = (tuple(sorted(a)), tuple(sorted(c)), float(s).hex(), float(conf).hex(), float(lift).hex())
+        tot = (tot + int.from_bytes(hashlib.sha256(repr(key).encode()).digest()[:8], "little")) % (1 << 64)
+    return tot
+
+
+# ------------------------------------------------------------------------- kernels, one by one
+def test_item_histogram():
+    rng = np.random.default_rng(0)
+    for nnz, t in [(0, 5), (1, 1), (7, 3), (100003, 977), (1 << 20, 50000)]:
+        items = rng.integers(0, t, nnz).astype(np.int32)
+        d = torch.from_numpy(items).to(dev())
+        occ = torch.full((t,), -7, dtype=torch.int32, device=dev())
+        _lib.call("kmls_item_histogram", d, nnz, t, occ, stream())
+        assert (occ.cpu().numpy() == np.bincount(items, minlength=t)).all()
+
+
+@pytest.mark.parametrize("n,t,dup", [(1, 1, False), (255, 40, True), (256, 40, False), (257, 9000, True),
+                                     (5000, 300, True), (70001, 64, False)])
+def test_encode_popcount_roundtrip(n, t, dup):
+    rng = np.random.default_rng(n)
+    lens = rng.integers(0, min(t, 60) + 1, n)
+    rows = [rng.choice(t, l, replace=False) for l in lens]
+    if dup:
+        rows = [np.concatenate([r, r[:2]]) for r in rows]
+    off = np.zeros(n + 1, np.int64)
+    np.cumsum([len(r) for r in rows], out=off[1:])
+    items = (np.concatenate(rows) if off[-1] else np.zeros(0)).astype(np.int32)
+    # keep every second track, in a scrambled row order
+    kept = rng.permutation(np.arange(0, t, 2))
+    row_of = np.full(t, -1, np.int32)
+    row_of[kept] = np.arange(len(kept), dtype=np.int32)
+    W = int(_lib.value("kmls_bitmap_row_words", n))
+    bm = torch.full((len(kept) * W,), 0x5A5A5A5A, dtype=torch.int32, device=dev())
+    _lib.call("kmls_encode_bitmap", torch.from_numpy(off).to(dev()), torch.from_numpy(items).to(dev()), n,
+              torch.from_numpy(row_of).to(dev()), t, len(kept), bm, W, stream())
+    dense = np.zeros((len(kept), W * 32), bool)
+    for p, r in enumerate(rows):
+        for it in r:
+            if row_of[it] >= 0:
+                dense[row_of[it], p] = True
+    want = np.packbits(dense, axis=1, bitorder="little").view(np.uint32).reshape(len(kept), W)
+    got = bm.cpu().numpy().view(np.uint32).reshape(len(kept), W)
+    assert (got == want).all()
+    cnt = torch.empty(len(kept), dtype=torch.int32, device=dev())
+    _lib.call("kmls_row_popcount", bm, len(kept), W, cnt, stream())
+    assert (cnt.cpu().numpy() == dense.sum(1)).all()
+    # gather rows back into ascending-track order
+    src = torch.from_numpy(np.argsort(kept).astype(np.int32)).to(dev())
+    out = torch.empty_like(bm)
+    _lib.call("kmls_gather_rows", bm, src, len(kept), W, out, stream())
+    assert (out.cpu().numpy().view(np.uint32).reshape(len(kept), W) == want[np.argsort(kept)]).all()
+
+
+def test_row_popcount_long_rows():
+    rng = np.random.default_rng(1)
+    W = 8 * 700  # > 4096 words: one CTA per row
+    bm = rng.integers(0, 2**32, (5, W), dtype=np.uint64).astype(np.uint32)
+    d = torch.from_numpy(bm.view(np.int32)).to(dev())
+    cnt = torch.empty(5, dtype=torch.int32, device=dev())
+    _lib.call("kmls_row_popcount", d, 5, W, cnt, stream())
+    want = np.unpackbits(bm.view(np.uint8), axis=1).sum(1)
+    assert (cnt.cpu().numpy() == want).all()
+
+
+@pytest.mark.parametrize("rows,n", [(1, 100), (63, 300), (64, 256), (65, 5000), (200, 70000), (3, 400000)])
+def test_pair_counts_and_select(rows, n):
+    rng = np.random.default_rng(rows * 7 + n)
+    W = int(_lib.value("kmls_bitmap_row_words", n))
+    dense = rng.random((rows, n)) < rng.uniform(0.02, 0.6, (rows, 1))
+    full = np.zeros((rows, W * 32), bool)
+    full[:, :n] = dense
+    bm = np.packbits(full, axis=1, bitorder="little").view(np.int32).reshape(rows, W)
+    d = torch.from_numpy(bm).to(dev())
+    pair = torch.full((rows * rows,), -1, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts", d, rows, W, pair, stream())
+    want = dense.astype(np.int64) @ dense.astype(np.int64).T
+    got = pair.cpu().numpy().reshape(rows, rows)
+    assert (got == want).all()
+    thr = int(np.median(want[np.triu_indices(rows, 1)])) if rows > 1 else 1
+    row_off = torch.empty(rows + 1, dtype=torch.int64, device=dev())
+    _lib.call("kmls_pair_select", pair, rows, thr, 0, row_off, 0, 0, stream())
+    ii, jj = np.nonzero(np.triu(want >= thr, 1))
+    assert int(row_off[rows].item()) == len(ii)
+    if len(ii):
+        it2 = torch.empty(len(ii) * 2, dtype=torch.int32, device=dev())
+        ct2 = torch.empty(len(ii), dtype=torch.int32, device=dev())
+        _lib.call("kmls_pair_select", pair, rows, thr, len(ii), row_off, it2, ct2, stream())
+        assert (it2.cpu().numpy().reshape(-1, 2) == np.stack([ii, jj], 1)).all()
+        assert (ct2.cpu().numpy() == want[ii, jj]).all()
+        sup = torch.empty(len(ii), dtype=torch.float64, device=dev())
+        _lib.call("kmls_supports_f64", ct2, len(ii), n, sup, stream())
+        assert sup.cpu().numpy().tolist() == [int(c) / n for c in want[ii, jj]]
+
+
+def test_exclusive_scan():
+    rng = np.random.default_rng(2)
+    for n in [0, 1, 31, 1025, 3_000_001]:
+        x = rng.integers(0, 1000, n).astype(np.int32)
+        d = torch.from_numpy(x).to(dev())
+        out = torch.empty(n + 1, dtype=torch.int64, device=dev())
+        sb = int(_lib.value("kmls_scan_scratch_bytes", n))
+        scratch = torch.empty(sb, dtype=torch.uint8, device=dev())
+        _lib.call("kmls_exclusive_scan_i32", d, n, out, scratch, sb, stream())
+        want = np.concatenate([[0], np.cumsum(x.astype(np.int64))])
+        assert (out.cpu().numpy() == want).all()
+    # totals beyond 2^31 must not wrap
+    x = torch.full((3_000_000,), 1000, dtype=torch.int32, device=dev())
+    out = torch.empty(3_000_001, dtype=torch.int64, device=dev())
+    _lib.call("kmls_exclusive_scan_i32", x, 3_000_000, out, scratch, sb, stream())
+    assert int(out[-1].item()) == 3_000_000_000
+
+
+# ------------------------------------------------------------------- the whole path, small cases
+@pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
+def test_hand_vectors_through_the_plugin_boundary(case, capsys):
+    tx = case["transactions"]
+    playlist_dict = {100 + i: t for i, t in enumerate(tx)}
+    recs, info, (missing, duration) = kmls_b200.calculate_and_save_fp_growth_fast(
+        playlist_dict, case["min_support"], total_songs=10)
+    assert recs == case["recommendations"]
+    assert all(type(v) is float for d in recs.values() for v in d.values())
+    assert missing == 10 - len(recs)
+    out = capsys.readouterr().out
+    assert "Songs without recommendations:" in out and "Time elapsed in rule generation:" in out
+    assert info.startswith(f"min_support: {case['min_support']} \tmissing songs: {missing} \ttime: ")
+    last = kmls_b200.api.last_result
+    cols = last["columns"]
+    got = {_key(cols[i] for i in k): v for k, v in last["itemsets"].as_dict().items()}
+    assert got == case["itemsets"]
+    frame = kmls_b200.itemsets_frame(last["itemsets"], cols)
+    assert {_key(r.itemsets): r.support for r in frame.itertuples()} == \
+        {k: v / len(tx) for k, v in case["itemsets"].items()}
+    if "rules" in case:
+        res, rules = kmls_b200.mine_ids(*kmls_b200.encode_transactions(tx)[1:], len(cols),
+                                        case["min_support"], case["rules_min_confidence"])
+        rf = kmls_b200.rules_frame(res, rules, cols)
+        n = len(tx)
+        want = {}
+        for r in case["rules"]:
+            sx, sa, sc = r["cX"] / n, r["cA"] / n, r["cC"] / n
+            want[(r["antecedents"], r["consequents"])] = (sx, sx / sa, (sx / sa) / sc)
+        got = {(_key(r.antecedents), _key(r.consequents)): (r.support, r.confidence, r.lift)
+               for r in rf.itertuples()}
+        assert got == want
+
+
+def test_empty_and_degenerate_inputs():
+    assert kmls_b200.calculate_and_save_fp_growth_fast({}, 0.5)[0] == {}
+    assert kmls_b200.calculate_and_save_fp_growth_fast({1: [], 2: []}, 0.5)[0] == {}
+    assert kmls_b200.calculate_and_save_fp_growth_fast({1: ["only"]}, 0.5)[0] == {"only": {}}
+    with pytest.raises(ValueError):
+        kmls_b200.calculate_and_save_fp_growth_fast({1: ["a"]}, 0.0)
+    with pytest.raises(ValueError):
+        kmls_b200.calculate_and_save_fp_growth_fast({1: ["a"]}, -1.0)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_small_against_python_restatement(seed):
+    rng = np.random.default_rng(seed)
+    n, t = int(rng.integers(1, 400)), int(rng.integers(1, 24))
+    onehot = rng.random((n, t)) < rng.uniform(0.05, 0.7)
+    s = float(rng.choice([0.05, 0.07, 0.1, 0.2, 0.3, 0.035, 0.14]))
+    want = M.fpgrowth_counts(onehot, s)
+    off, items = fpgrowth_c.dense_to_csr(onehot)
+    res, _ = kmls_b200.mine_ids(off, items, t, s)
+    assert res.as_dict() == want
+
+
+def test_duplicates_inside_playlists_change_supports_not_results():
+    rng = np.random.default_rng(5)
+    n, t = 3000, 120
+    onehot = rng.random((n, t)) < 0.08
+    off, items = fpgrowth_c.dense_to_csr(onehot)
+    # repeat every playlist's items three times, scrambled
+    rows = [np.tile(items[off[i]:off[i + 1]], 3) for i in range(n)]
+    rows = [rng.permutation(r) for r in rows]
+    off3 = np.zeros(n + 1, np.int64)
+    np.cumsum([len(r) for r in rows], out=off3[1:])
+    items3 = np.concatenate(rows).astype(np.int32)
+    s = 0.08
+    want = M.fpgrowth_counts(onehot, s)
+    res, _ = kmls_b200.mine_ids(off3, items3, t, s)
+    assert res.as_dict() == want
+
+
+def test_max_len():
+    off, items = synth.zipf_playlists(2000, 200, mean_draws=20, alpha=0.8, seed=4)
+    for ml in (1, 2, 3):
+        res, _ = kmls_b200.mine_ids(off, items, 200, 0.03, max_len=ml)
+        assert res.as_dict() == oracle_dict(off, items, 200, 0.03, max_len=ml)
+
+
+# ----------------------------------------------------------------- golden fixtures (oracle-made)
+def _golden_input(g):
+    if g["generator"] == "zipf":
+        off, items = synth.zipf_playlists(**g["params"])
+        return off, items, g["params"]["n_tracks"]
+    d = synth.mpd_standin(**g["params"])
+    playlists = synth.group_by_playlist(d["pid"], d["track_name"])
+    columns, off, ids = kmls_b200.encode_transactions(list(playlists.values()))
+    return off, ids, len(columns)
+
+
+@pytest.mark.parametrize("g", GOLDEN, ids=[g["name"] for g in GOLDEN])
+def test_golden_fixture(g):
+    off, items, n_items = _golden_input(g)
+    assert len(off) - 1 == g["n_playlists"] and len(items) == g["nnz"]
+    res, rules = kmls_b200.mine_ids(off, items, n_items, g["min_support"], g["min_confidence"])
+    assert (res.t1, res.tk) == (g["t1"], g["tk"])
+    assert [0] + [int(c.numel()) for _, c in res.levels] == g["level_counts"]
+    o, i, c = res.to_host()
+    assert str(fpgrowth_c.itemset_checksum(o, i, c)) == g["itemset_checksum"]
+    assert rules.n_rules == g["n_rules"]
+    if g["n_rules"] <= 250_000:
+        assert str(rule_checksum(kmls_b200.rules_to_host(res, rules))) == g["rule_checksum"]
+    # and the live oracle on the same input, itemset by itemset
+    assert res.as_dict() == oracle_dict(off, items, n_items, g["min_support"])
+
+
+def test_mpd_standin_recommendations_match_reference_fold():
+    d = synth.mpd_standin(seed=1)
+    playlists = synth.group_by_playlist(d["pid"], d["track_name"])
+    total = len(set(d["track_uri"]))
+    recs, _, (missing, _) = kmls_b200.calculate_and_save_fp_growth_fast(playlists, 0.05, total_songs=total)
+    want, _ = M.calculate_and_save_fp_growth_fast(playlists, 0.05)
+    assert recs == want
+    assert missing == total - len(want)
+    # plain picklable objects only (rest_api has neither numpy nor torch)
+    import pickle
+    assert pickle.loads(pickle.dumps(recs)) == want
+
+
+def test_rules_against_oracle_medium():
+    off, items = synth.zipf_playlists(6000, 800, mean_draws=30, alpha=0.9, seed=21)
+    s, conf = 0.015, 0.35
+    res, rules = kmls_b200.mine_ids(off, items, 800, s, conf)
+    n = len(off) - 1
+    want_sets = oracle_dict(off, items, 800, s)
+    assert res.as_dict() == want_sets
+    want = M.association_rules([(v / n, k) for k, v in want_sets.items()], conf)
+    got = kmls_b200.rules_to_host(res, rules)
+    assert len(got) == len(want)
+    assert {(a, c): (x, y, z) for a, c, x, y, z in got} == {(a, c): (x, y, z) for a, c, x, y, z in want}
+
+
+def test_two_threshold_split_at_scale():
+    # s = 0.07, N = 100k: T1 and Tk differ for many N; counts near both must
+    # land on the right side at level 1 (T1) and at levels >= 2 (Tk)
+    n = 100
+    tx = [["p", "q"]] * 7 + [["r", "q"]] * 8 + [["r"]] + [["q"]] * 35 + [[]] * 49
+    assert kmls_b200.thresholds(0.07, n) == (7, 8)
+    recs, _, _ = kmls_b200.calculate_and_save_fp_growth_fast(dict(enumerate(tx)), 0.07, total_songs=3)
+    assert recs == {"p": {}, "q": {"r": 0.08}, "r": {"q": 0.08}}
+
+
+# --------------------------------------------------------------- full-size, size-independent checks
+def test_properties_at_scale():
+    """200k playlists x 20k tracks: (a) level-1 supports equal a numpy bincount of the
+    deduplicated input, (b) every itemset's count is <= the count of each of its parents'
+    (anti-monotone), (c) level tables are sorted and duplicate-free, (d) the checksum of the
+    whole table equals the C++ oracle's."""
+    n, t, s = 200_000, 20_000, 0.004
+    off, items = synth.zipf_playlists(n, t, mean_draws=50, alpha=1.0, seed=7)
+    res, rules = kmls_b200.mine_ids(off, items, t, s, 0.8)
+    rows = res.row_items.cpu().numpy()
+    c1 = np.bincount(items, minlength=t)  # generator output has no in-playlist duplicates
+    assert (res.levels[0][1].cpu().numpy() == c1[rows]).all()
+    assert set(rows.tolist()) == set(np.nonzero(c1 >= res.t1)[0].tolist())
+    prev = None
+    for k, (it, ct) in enumerate(res.levels, start=1):
+        it, ct = it.cpu().numpy().astype(np.int64), ct.cpu().numpy()
+        assert (ct >= (res.t1 if k == 1 else res.tk)).all()
+        if k > 1:
+            assert (np.diff(it, axis=1) > 0).all()
+            key = np.zeros(len(it), dtype=object)
+            order = np.lexsort(it.T[::-1])
+            assert (order == np.arange(len(it))).all(), "level table not sorted"
+            assert len(np.unique(it, axis=0)) == len(it)
+            # parent = itemset minus its last member, must exist with count >= child's
+            parent = {tuple(r): c for r, c in zip(prev[0].tolist(), prev[1].tolist())}
+            for r, c in list(zip(it.tolist(), ct.tolist()))[:: max(1, len(it) // 5000)]:
+                assert parent[tuple(r[:-1])] >= c
+        prev = (it, ct)
+    t1, tk = M.thresholds(s, n)
+    ref = fpgrowth_c.fpgrowth(off, items, t, t1, tk, store=False)
+    o, i, c = res.to_host()
+    assert res.n_itemsets == ref.n
+    assert [int(x.numel()) for _, x in res.levels] == ref.level_counts[1:len(res.levels) + 1].tolist()
+    assert fpgrowth_c.itemset_checksum(o, i, c) == ref.checksum
+    # rules: confidence >= threshold, support/lift consistent with the integer counts
+    conf = rules.confidence.cpu().numpy()
+    assert (conf >= 0.8).all() and (conf <= 1.0).all()
