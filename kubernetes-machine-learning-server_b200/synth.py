@@ -13,42 +13,56 @@ from typing import Dict, List, Tuple
 import numpy as np
 
 
+_ZIPF_CHUNK = 1 << 16  # playlists per independently seeded chunk (part of the definition)
+
+
+def _zipf_chunk(args):
+    n_chunk, n_tracks, mean_draws, alpha, seed, stream = args
+    rng = np.random.Generator(np.random.PCG64(seed).jumped(stream + 1))
+    perm = np.random.Generator(np.random.PCG64(seed + 1)).permutation(n_tracks).astype(np.int64)
+    w = np.arange(1, n_tracks + 1, dtype=np.float64) ** (-alpha)
+    cdf = np.cumsum(w)
+    cdf /= cdf[-1]
+    lens = np.clip(rng.poisson(mean_draws, n_chunk), 5, 250).astype(np.int64)
+    u = rng.random(int(lens.sum()))
+    ranks = np.minimum(np.searchsorted(cdf, u, side="left"), n_tracks - 1)
+    pid = np.repeat(np.arange(n_chunk, dtype=np.int64), lens)
+    key = np.unique(pid * n_tracks + perm[ranks])
+    counts = np.bincount(key // n_tracks, minlength=n_chunk)
+    return counts, (key % n_tracks).astype(np.int32)
+
+
 def zipf_playlists(n_playlists: int, n_tracks: int, mean_draws: float = 72.0,
                    alpha: float = 1.0, seed: int = 0, shard: int = 0,
-                   chunk: int = 1 << 18) -> Tuple[np.ndarray, np.ndarray]:
-    """Zipfian playlists (SURVEY.md §8d config 3/5).
+                   workers: int = 1) -> Tuple[np.ndarray, np.ndarray]:
+    """Zipfian playlists (SURVEY.md section 8d, configs 3 and 5).
 
     Per playlist: L = clip(Poisson(mean_draws), 5, 250) draws of a popularity rank by
     inverse CDF on weights r^-alpha; duplicates inside a playlist are dropped; rank r is
     mapped to a track id by a fixed permutation (seed+1) so ids are not popularity-sorted.
-    ``shard`` selects an independent stream (``PCG64(seed).jumped(shard)``) so that each
-    rank of a multi-GPU run generates its own playlists.
+    Playlists are generated in chunks of 65,536, chunk c of shard s from the independent
+    stream ``PCG64(seed).jumped(s * 65536 + c + 1)``: the result does not depend on
+    ``workers`` (processes used to generate chunks in parallel), and each rank of a
+    multi-GPU run can generate its own ``shard``.
 
     Returns (offsets int64[N+1], items int32[nnz]); items of a playlist are sorted by id.
     """
-    bitgen = np.random.PCG64(seed)
-    if shard:
-        bitgen = bitgen.jumped(shard)
-    rng = np.random.Generator(bitgen)
-    perm = np.random.Generator(np.random.PCG64(seed + 1)).permutation(n_tracks).astype(np.int32)
-    w = np.arange(1, n_tracks + 1, dtype=np.float64) ** (-alpha)
-    cdf = np.cumsum(w)
-    cdf /= cdf[-1]
-    counts = np.empty(n_playlists, dtype=np.int64)
-    parts: List[np.ndarray] = []
-    for p0 in range(0, n_playlists, chunk):
-        p1 = min(n_playlists, p0 + chunk)
-        lens = np.clip(rng.poisson(mean_draws, p1 - p0), 5, 250).astype(np.int64)
-        u = rng.random(int(lens.sum()))
-        ranks = np.searchsorted(cdf, u, side="left").astype(np.int64)
-        np.minimum(ranks, n_tracks - 1, out=ranks)
-        pid = np.repeat(np.arange(p1 - p0, dtype=np.int64), lens)
-        key = np.unique(pid * n_tracks + perm[ranks].astype(np.int64))
-        counts[p0:p1] = np.bincount(key // n_tracks, minlength=p1 - p0)
-        parts.append((key % n_tracks).astype(np.int32))
+    jobs = []
+    for c, p0 in enumerate(range(0, n_playlists, _ZIPF_CHUNK)):
+        jobs.append((min(_ZIPF_CHUNK, n_playlists - p0), n_tracks, mean_draws, alpha, seed,
+                     shard * 65536 + c))
+    if workers > 1 and len(jobs) > 1:
+        import concurrent.futures as cf
+        with cf.ProcessPoolExecutor(max_workers=min(workers, len(jobs))) as ex:
+            parts = list(ex.map(_zipf_chunk, jobs))
+    else:
+        parts = [_zipf_chunk(j) for j in jobs]
     offsets = np.zeros(n_playlists + 1, dtype=np.int64)
-    np.cumsum(counts, out=offsets[1:])
-    items = np.concatenate(parts) if parts else np.zeros(0, dtype=np.int32)
+    if parts:
+        np.cumsum(np.concatenate([c for c, _ in parts]), out=offsets[1:])
+        items = np.concatenate([i for _, i in parts])
+    else:
+        items = np.zeros(0, dtype=np.int32)
     return offsets, items
 
 
