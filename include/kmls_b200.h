@@ -136,18 +136,23 @@ int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t* d_cand_p,
 int kmls_itemset_map_build(const int32_t* d_items, const int32_t* d_counts,
                            const int64_t* level_sizes, int32_t max_k, uint64_t* d_keys,
                            int32_t* d_vals, int64_t capacity, kmls_stream_t stream);
-/* d_rule_cnt[x] = rules kept for the x-th itemset of size >= 2; *d_missing counts subset
- * lookups that failed (0 for a downward-closed table; caller zeroes it). */
+/* Itemsets of size >= 2 are numbered x = 0, 1, ... in table order; a call handles
+ * x_begin <= x < x_begin + x_count (ranks may split the table). d_rule_cnt[x - x_begin] =
+ * rules kept for itemset x; *d_missing counts subset lookups that failed (0 for a
+ * downward-closed table; caller zeroes it). */
 int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
                      int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
                      int64_t capacity, int64_t n_playlists_total, double min_confidence,
-                     int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
-/* Rule r: itemset d_out_itemset[r] (global id), antecedent = members selected by the bits
+                     int64_t x_begin, int64_t x_count, int32_t* d_rule_cnt, int32_t* d_missing,
+                     kmls_stream_t stream);
+/* d_rule_off = exclusive scan of d_rule_cnt (x_count + 1 entries).
+ * Rule r: itemset d_out_itemset[r] (global id), antecedent = members selected by the bits
  * of d_out_antecedent[r] (bit t = t-th member), consequent = the rest. */
 int kmls_rules_write(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
                      int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
                      int64_t capacity, int64_t n_playlists_total, double min_confidence,
-                     const int64_t* d_rule_off, int32_t* d_out_itemset,
+                     int64_t x_begin, int64_t x_count, const int64_t* d_rule_off,
+                     int32_t* d_out_itemset,
                      uint32_t* d_out_antecedent, double* d_out_support, double* d_out_confidence,
                      double* d_out_lift, int32_t* d_missing, kmls_stream_t stream);
 

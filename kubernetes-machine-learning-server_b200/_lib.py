@@ -38,9 +38,9 @@ SIGNATURES = {
     "kmls_emit_count": (ctypes.c_int, [_P, _I64, _I32, _P, _P, _SZ, _P]),
     "kmls_emit_level": (ctypes.c_int, [_P, _I32, _P, _P, _P, _I64, _I32, _P, _P, _P, _P]),
     "kmls_itemset_map_build": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _P]),
-    "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _P, _P, _P]),
-    "kmls_rules_write": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _P, _P, _P, _P,
-                                        _P, _P, _P, _P]),
+    "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _I64, _I64, _P, _P, _P]),
+    "kmls_rules_write": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _I64, _I64, _F64, _I64, _I64, _P, _P,
+                                        _P, _P, _P, _P, _P, _P]),
 }
 
 _lib = None
@@ -67,6 +67,22 @@ def load() -> ctypes.CDLL:
     return _lib
 
 
+# Kernels enqueued by one call of each entry point (for bench.py's `gpu_launches`; CUB scans
+# and selections count as the kernels they launch from inside this library).
+KERNELS_PER_CALL = {
+    "kmls_item_histogram": 1, "kmls_encode_bitmap": 1, "kmls_row_popcount": 1, "kmls_gather_rows": 1,
+    "kmls_pair_counts": 1, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
+    "kmls_itemset_set_build": 1, "kmls_join_count": 4, "kmls_join_write": 4, "kmls_count_candidates": 1,
+    "kmls_emit_count": 3, "kmls_emit_level": 1, "kmls_itemset_map_build": 1, "kmls_rules_count": 1,
+    "kmls_rules_write": 1,
+}
+
+# Optional tracing for bench.py: when TRACE is a list, every call is bracketed by CUDA events
+# on the current stream and appended as (name, start_event, end_event, algorithmic_bytes).
+TRACE = None
+CALLS = {}
+
+
 def _arg(a):
     # torch tensors are passed as their device (or host) address
     if hasattr(a, "data_ptr"):
@@ -74,13 +90,26 @@ def _arg(a):
     return a
 
 
-def call(name: str, *args):
+def call(name: str, *args, algo_bytes=None):
     """Call an int-returning entry point; raise KmlsError with the library's text on failure."""
     lib = load()
-    rc = getattr(lib, name)(*[_arg(a) for a in args])
+    CALLS[name] = CALLS.get(name, 0) + 1
+    if TRACE is not None:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(lib, name)(*[_arg(a) for a in args])
+        e1.record()
+        TRACE.append((name, e0, e1, algo_bytes))
+    else:
+        rc = getattr(lib, name)(*[_arg(a) for a in args])
     if rc != 0:
         msg = lib.kmls_last_error().decode("utf-8", "replace")
         raise KmlsError(f"{name} failed with code {rc}: {msg}")
+
+
+def kernel_launches() -> int:
+    return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in CALLS.items())
 
 
 def value(name: str, *args):

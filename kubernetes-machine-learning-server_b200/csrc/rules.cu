@@ -80,17 +80,20 @@ __device__ __forceinline__ int32_t subset_count(const Arena& a, const unsigned l
 // `sel` with the top member excluded; each handles the partition {A = sel, C = complement}
 // and therefore two rules (A -> C and C -> A) from two lookups. Pass 1 counts the kept rules
 // per itemset; pass 2 writes them at rule_off[x] + rank (ballot + popc rank), ordered by
-// sel, A -> C before C -> A.
+// sel, A -> C before C -> A. Only the itemsets x_begin .. x_begin + x_count - 1 (numbered
+// from the first 2-itemset) are processed, so ranks can split the table; rule_cnt/rule_off
+// are indexed from x_begin.
 __global__ void __launch_bounds__(256)
 k_rules(Arena a, const unsigned long long* __restrict__ keys, const int32_t* __restrict__ vals,
-        uint64_t mask, double n_total, double min_conf, int write, int32_t* __restrict__ rule_cnt,
+        uint64_t mask, double n_total, double min_conf, int64_t x_begin, int64_t x_count, int write,
+        int32_t* __restrict__ rule_cnt,
         const int64_t* __restrict__ rule_off, int32_t* __restrict__ out_itemset,
         uint32_t* __restrict__ out_antecedent, double* __restrict__ out_support,
         double* __restrict__ out_confidence, double* __restrict__ out_lift,
         int32_t* __restrict__ missing) {
   const int lane = threadIdx.x & 31;
-  const int64_t first = a.id_off[2], n = a.id_off[a.max_k + 1] - first;
-  for (int64_t xi = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); xi < n;
+  const int64_t first = a.id_off[2] + x_begin;
+  for (int64_t xi = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); xi < x_count;
        xi += (int64_t)gridDim.x * 8) {
     const int64_t gid = first + xi;
     int k = 2;
@@ -188,21 +191,24 @@ extern "C" int kmls_itemset_map_build(const int32_t* d_items, const int32_t* d_c
 
 static int launch_rules(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
                         int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
-                        int64_t capacity, int64_t n_total, double min_conf, int write,
-                        int32_t* d_rule_cnt, const int64_t* d_rule_off, int32_t* o_itemset,
+                        int64_t capacity, int64_t n_total, double min_conf, int64_t x_begin,
+                        int64_t x_count, int write, int32_t* d_rule_cnt, const int64_t* d_rule_off, int32_t* o_itemset,
                         uint32_t* o_ante, double* o_sup, double* o_conf, double* o_lift,
                         int32_t* d_missing, cudaStream_t s) {
   Arena a;
   int rc = make_arena(a, d_items, d_counts, level_sizes, max_k);
   if (rc) return rc;
   KMLS_REQUIRE(n_total > 0, "rules: n_playlists_total must be positive");
-  const int64_t n = a.id_off[max_k + 1] - a.id_off[2];
+  const int64_t n_x = a.id_off[max_k + 1] - a.id_off[2];
+  KMLS_REQUIRE(x_begin >= 0 && x_count >= 0 && x_begin + x_count <= std::max<int64_t>(n_x, 0),
+               "rules: itemset range out of bounds");
+  const int64_t n = x_count;
   if (max_k < 2 || n <= 0) return 0;
   KMLS_REQUIRE(capacity > 0 && (capacity & (capacity - 1)) == 0 && d_keys && d_vals && d_missing,
                "rules: bad map");
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 32);
   k_rules<<<grid, 256, 0, s>>>(a, (const unsigned long long*)d_keys, d_vals, (uint64_t)capacity - 1,
-                               (double)n_total, min_conf, write, d_rule_cnt, d_rule_off, o_itemset,
+                               (double)n_total, min_conf, x_begin, x_count, write, d_rule_cnt, d_rule_off, o_itemset,
                                o_ante, o_sup, o_conf, o_lift, d_missing);
   KMLS_LAUNCHED("k_rules");
   return 0;
@@ -211,22 +217,23 @@ static int launch_rules(const int32_t* d_items, const int32_t* d_counts, const i
 extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
                                 const int64_t* level_sizes, int32_t max_k, const uint64_t* d_keys,
                                 const int32_t* d_vals, int64_t capacity, int64_t n_playlists_total,
-                                double min_confidence, int32_t* d_rule_cnt, int32_t* d_missing,
-                                kmls_stream_t stream) {
+                                double min_confidence, int64_t x_begin, int64_t x_count,
+                                int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream) {
   return launch_rules(d_items, d_counts, level_sizes, max_k, d_keys, d_vals, capacity,
-                      n_playlists_total, min_confidence, 0, d_rule_cnt, nullptr, nullptr, nullptr,
-                      nullptr, nullptr, nullptr, d_missing, (cudaStream_t)stream);
+                      n_playlists_total, min_confidence, x_begin, x_count, 0, d_rule_cnt, nullptr,
+                      nullptr, nullptr, nullptr, nullptr, nullptr, d_missing, (cudaStream_t)stream);
 }
 
 extern "C" int kmls_rules_write(const int32_t* d_items, const int32_t* d_counts,
                                 const int64_t* level_sizes, int32_t max_k, const uint64_t* d_keys,
                                 const int32_t* d_vals, int64_t capacity, int64_t n_playlists_total,
-                                double min_confidence, const int64_t* d_rule_off,
-                                int32_t* d_out_itemset, uint32_t* d_out_antecedent,
-                                double* d_out_support, double* d_out_confidence, double* d_out_lift,
-                                int32_t* d_missing, kmls_stream_t stream) {
+                                double min_confidence, int64_t x_begin, int64_t x_count,
+                                const int64_t* d_rule_off, int32_t* d_out_itemset,
+                                uint32_t* d_out_antecedent, double* d_out_support,
+                                double* d_out_confidence, double* d_out_lift, int32_t* d_missing,
+                                kmls_stream_t stream) {
   return launch_rules(d_items, d_counts, level_sizes, max_k, d_keys, d_vals, capacity,
-                      n_playlists_total, min_confidence, 1, nullptr, d_rule_off, d_out_itemset,
-                      d_out_antecedent, d_out_support, d_out_confidence, d_out_lift, d_missing,
-                      (cudaStream_t)stream);
+                      n_playlists_total, min_confidence, x_begin, x_count, 1, nullptr, d_rule_off,
+                      d_out_itemset, d_out_antecedent, d_out_support, d_out_confidence, d_out_lift,
+                      d_missing, (cudaStream_t)stream);
 }

@@ -161,7 +161,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
 
     # ---- level 1 -------------------------------------------------------------------------
     occ = dev.empty(n_items, torch.int32)
-    _lib.call("kmls_item_histogram", items, nnz, n_items, occ, s)
+    _lib.call("kmls_item_histogram", items, nnz, n_items, occ, s, algo_bytes=4 * nnz)
     _allreduce(occ, group)
     cand = torch.nonzero(occ >= max(t1, 1)).reshape(-1)              # ascending track id
     if cand.numel() == 0:
@@ -174,9 +174,10 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     row_words = int(_lib.value("kmls_bitmap_row_words", n_local))
     bitmap = dev.empty(n_rows * row_words, torch.int32)
     _lib.call("kmls_encode_bitmap", offsets, items, n_local, row_of_item, n_items, n_rows,
-              bitmap, row_words, s)
+              bitmap, row_words, s, algo_bytes=4 * nnz + 8 * n_local + 4 * n_rows * row_words)
     counts1 = dev.empty(n_rows, torch.int32)
-    _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s)
+    _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s,
+              algo_bytes=4 * n_rows * row_words)
     _allreduce(counts1, group)
     if not bool(torch.equal(counts1, occ[cand])):
         # some playlist repeated a track: exact supports differ from the occurrence counts,
@@ -259,7 +260,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         n_groups = int(n_groups_d.item())
         cand_cnt = dev.empty(n_cand, torch.int32)
         _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
-                  kept_off, cand_q, n_cand, cand_cnt, s)
+                  kept_off, cand_q, n_cand, cand_cnt, s,
+                  algo_bytes=(n_cand + n_groups * k) * row_words * 4)
         _allreduce(cand_cnt, group)
         scratch, sbytes = dev.scan_scratch(n_cand)
         out_off = dev.empty(n_cand + 1, torch.int64)
@@ -302,10 +304,12 @@ class RuleTable:
         return int(self.itemset.numel())
 
 
-def generate_rules(res: MineResult, min_confidence: float,
-                   max_rules: int = 2_000_000_000) -> RuleTable:
+def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_000_000_000,
+                   part: Tuple[int, int] = (0, 1)) -> RuleTable:
     """fp64 confidence/lift for every (itemset, antecedent) split, kept iff
-    confidence >= min_confidence (mlxtend ``association_rules`` semantics)."""
+    confidence >= min_confidence (mlxtend ``association_rules`` semantics).
+    ``part = (i, n)`` generates only the rules of the i-th of n contiguous slices of the
+    itemset table (how ranks of a multi-GPU job divide the rule table among themselves)."""
     device = res.row_items.device
     dev = _Dev(device)
     s = _stream()
@@ -327,11 +331,13 @@ def generate_rules(res: MineResult, min_confidence: float,
     sizes_ptr = sizes.ctypes.data
     _lib.call("kmls_itemset_map_build", arena_items, arena_counts, sizes_ptr, max_k, keys, vals,
               cap, s)
-    n_x = n_all - int(sizes[1])
+    n_x_all = n_all - int(sizes[1])
+    x_begin = (n_x_all * part[0]) // part[1]
+    n_x = (n_x_all * (part[0] + 1)) // part[1] - x_begin
     rule_cnt = dev.empty(n_x, torch.int32)
     missing = torch.zeros(1, dtype=torch.int32, device=device)
     _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
-              res.n_playlists, float(min_confidence), rule_cnt, missing, s)
+              res.n_playlists, float(min_confidence), x_begin, n_x, rule_cnt, missing, s)
     scratch, sbytes = dev.scan_scratch(n_x)
     rule_off = dev.empty(n_x + 1, torch.int64)
     _lib.call("kmls_exclusive_scan_i32", rule_cnt, n_x, rule_off, scratch, sbytes, s)
@@ -348,8 +354,8 @@ def generate_rules(res: MineResult, min_confidence: float,
     o_lift = dev.empty(n_rules, torch.float64)
     if n_rules:
         _lib.call("kmls_rules_write", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
-                  res.n_playlists, float(min_confidence), rule_off, o_set, o_ante, o_sup, o_conf,
-                  o_lift, missing, s)
+                  res.n_playlists, float(min_confidence), x_begin, n_x, rule_off, o_set, o_ante,
+                  o_sup, o_conf, o_lift, missing, s)
     return RuleTable(o_set, o_ante, o_sup, o_conf, o_lift, arena_items, sizes.tolist())
 
 

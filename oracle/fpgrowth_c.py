@@ -40,6 +40,9 @@ def _load():
         lib.oracle_rules.restype = ctypes.c_int64
         lib.oracle_rules.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_int,
                                      ctypes.c_void_p]
+        lib.oracle_rules_strided.restype = ctypes.c_int64
+        lib.oracle_rules_strided.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_double,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
         _lib = lib
     return _lib
 

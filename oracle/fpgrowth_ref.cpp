@@ -293,7 +293,10 @@ void oracle_fpgrowth_copy(void* h, int64_t* offsets, int32_t* items, int64_t* co
 // proper subset A: confidence = (cX/N)/(cA/N), lift = confidence/(cC/N), kept iff
 // confidence >= c. Returns the number of rules and an order-independent checksum over
 // (antecedent, consequent, support, confidence, lift) bit patterns; -1 if a subset is missing.
-int64_t oracle_rules(void* h, int64_t n_total, double min_conf, int n_threads, uint64_t* checksum) {
+// `stride` > 1 generates the rules of every stride-th block of 4096 itemsets only (a bounded
+// sample for timing); stride 1 = all.
+int64_t oracle_rules_strided(void* h, int64_t n_total, double min_conf, int n_threads, int stride,
+                             uint64_t* checksum) {
   auto& s = ((Result*)h)->sink;
   const int64_t n = (int64_t)s.counts.size();
   uint64_t cap = 1024;
@@ -334,6 +337,7 @@ int64_t oracle_rules(void* h, int64_t n_total, double min_conf, int n_threads, u
     int32_t a[64], c[64];
     const int64_t step = 4096;
     for (int64_t b = next.fetch_add(step); b < n; b = next.fetch_add(step)) {
+      if (stride > 1 && (b / step) % stride != 0) continue;
       for (int64_t i = b; i < std::min(n, b + step); ++i) {
         const int k = (int)(s.offsets[i + 1] - s.offsets[i]);
         if (k < 2 || k > 30) continue;
@@ -370,6 +374,10 @@ int64_t oracle_rules(void* h, int64_t n_total, double min_conf, int n_threads, u
   for (int t = 0; t < nt; ++t) { total += cnts[t]; cs += sums[t]; }
   *checksum = cs;
   return total;
+}
+
+int64_t oracle_rules(void* h, int64_t n_total, double min_conf, int n_threads, uint64_t* checksum) {
+  return oracle_rules_strided(h, n_total, min_conf, n_threads, 1, checksum);
 }
 
 void oracle_fpgrowth_free(void* h) { delete (Result*)h; }
