@@ -100,7 +100,8 @@ int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t k, uint64_
  *                  (d_kept_off[n] = number of candidates).
  * kmls_join_write: candidates (d_cand_p[c], d_cand_q[c]) = indices of the two parents,
  *                  grouped by p in ascending order; d_grp_p / *d_n_groups = the parents that
- *                  have at least one candidate. */
+ *                  have at least one candidate (skipped when d_grp_p is NULL).
+ * A NULL d_pair (k == 2) or NULL d_slots (k >= 3) switches the pruning off. */
 int kmls_join_count(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
                     int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
                     int32_t* d_kept_cnt, uint32_t* d_kept_mask, int64_t* d_kept_off,
@@ -126,6 +127,35 @@ int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t* d_cand_p,
                     const int32_t* d_cand_q, const int32_t* d_cand_cnt, int64_t n_cand,
                     int32_t thr, const int64_t* d_out_off, int32_t* d_out_items,
                     int32_t* d_out_counts, kmls_stream_t stream);
+
+/* ---- conditional (projected) bitmaps: the bitmap analogue of FPTree.conditional_tree ---
+ * Every frequent itemset X = (P, x) of a level may own a bit row over the playlists that
+ * contain its class prefix P (columns compacted): row i starts at d_arena + d_rowptr[i] and
+ * is d_roww[i] words long (0 = no row; multiples of 4). Level 1 = the full bitmap
+ * (d_rowptr[r] = r * row_words, d_roww[r] = row_words). */
+
+/* d_cand_cnt[c] = |row(d_cand_p[c]) AND row(d_cand_q[c])| (this rank's playlists). */
+int kmls_count_pairs(const uint32_t* d_arena, const int64_t* d_rowptr, const int32_t* d_roww,
+                     const int32_t* d_cand_p, const int32_t* d_cand_q, int64_t n_cand,
+                     int32_t* d_cand_cnt, kmls_stream_t stream);
+/* kmls_emit_level that also records each new itemset's parents and its local count
+ * (d_cand_cnt = global counts used for the threshold, d_cand_cnt_local = this rank's). */
+int kmls_emit_level_px(const int32_t* d_items, int32_t k, const int32_t* d_cand_p,
+                       const int32_t* d_cand_q, const int32_t* d_cand_cnt,
+                       const int32_t* d_cand_cnt_local, int64_t n_cand, int32_t thr,
+                       const int64_t* d_out_off, int32_t* d_out_items, int32_t* d_out_counts,
+                       int32_t* d_out_counts_local, int32_t* d_out_par_p, int32_t* d_out_par_q,
+                       kmls_stream_t stream);
+/* Row widths of a new level: d_roww[o] = ceil(d_parent_cnt_local[d_par_p[o]] / 32) padded to
+ * 4 words if another itemset shares o's first parent, else 0. */
+int kmls_row_alloc(const int32_t* d_par_p, int64_t n, const int32_t* d_parent_cnt_local,
+                   int32_t* d_roww, kmls_stream_t stream);
+/* New rows: row(o) = row_old(d_par_q[o]) restricted to the columns set in
+ * row_old(d_par_p[o]), compacted (parallel bit extract). */
+int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
+                      const int32_t* d_roww_old, const int32_t* d_par_p, const int32_t* d_par_q,
+                      int64_t n, uint32_t* d_arena_new, const int64_t* d_rowptr_new,
+                      const int32_t* d_roww_new, kmls_stream_t stream);
 
 /* ---- rules (mlxtend association_rules semantics; the dormant path main.py:224-260 is the
  *      only reference site of a min_confidence knob) -------------------------------------- */

@@ -70,7 +70,7 @@ def _dist_group():
 
 
 def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: float,
-             min_confidence: Optional[float] = None, max_len: Optional[int] = None):
+             min_confidence: Optional[float] = None, max_len: Optional[int] = None, **mine_kwargs):
     """Host CSR of track ids in, device tables out: (MineResult, RuleTable or None).
     Under torchrun each rank keeps a contiguous range of the playlists."""
     device = _device()
@@ -81,7 +81,7 @@ def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: fl
     d_off = torch.from_numpy(np.ascontiguousarray(offsets)).to(device, non_blocking=True)
     d_ids = torch.from_numpy(np.ascontiguousarray(ids)).to(device, non_blocking=True)
     res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
-                         group=group, max_len=max_len)
+                         group=group, max_len=max_len, **mine_kwargs)
     rules = None
     if min_confidence is not None:
         rules = miner.generate_rules(res, min_confidence)

@@ -112,7 +112,7 @@ k_join(const int32_t* __restrict__ items, int64_t n, int k,
        p += (int64_t)gridDim.x * 8) {
     const int32_t* ip = items + p * k;
     uint64_t sum_p = 0;
-    if (k >= 3)
+    if (k >= 3 && slots != nullptr)
       for (int t = 0; t < k; ++t) sum_p += item_term(__ldg(ip + t));
     int total = 0;
     int64_t pos = write ? kept_off[p] : 0;
@@ -131,7 +131,9 @@ k_join(const int32_t* __restrict__ items, int64_t n, int k,
       } else if (in_class) {
         const int32_t y = __ldg(items + q * k + (k - 1));
         if (k == 2) {
-          keep = __ldg(pairC + (int64_t)__ldg(ip + 1) * n_rows + y) >= thr;
+          keep = pairC == nullptr || __ldg(pairC + (int64_t)__ldg(ip + 1) * n_rows + y) >= thr;
+        } else if (slots == nullptr) {
+          keep = true;  // pruning switched off: every join survives and gets counted
         } else {
           const uint64_t sum = sum_p + item_term(y);
           keep = true;
@@ -277,9 +279,11 @@ static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint6
                        const int64_t* d_kept_off, int32_t* d_cand_p, int32_t* d_cand_q,
                        cudaStream_t s) {
   KMLS_REQUIRE(n >= 0 && n <= 0x7fffffff && k >= 2 && k <= 30, "kmls_join: bad level size");
-  if (k == 2) KMLS_REQUIRE(d_pair && n_rows > 0, "kmls_join: level 2 needs the pair-count matrix");
-  else KMLS_REQUIRE(d_slots && capacity > 0 && (capacity & (capacity - 1)) == 0,
-                    "kmls_join: level >= 3 needs the fingerprint set");
+  // a null d_pair (k == 2) or null d_slots (k >= 3) switches Apriori pruning off
+  if (k == 2 && d_pair) KMLS_REQUIRE(n_rows > 0, "kmls_join: bad pair-count matrix size");
+  if (k >= 3 && d_slots) KMLS_REQUIRE(capacity > 0 && (capacity & (capacity - 1)) == 0,
+                                      "kmls_join: fingerprint set capacity must be a power of two");
+  if (!d_slots) capacity = 1;
   if (n == 0) return 0;
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 32);
   k_join<<<grid, 256, 0, s>>>(d_items, n, k, (const unsigned long long*)d_slots,
@@ -314,6 +318,7 @@ extern "C" int kmls_join_write(const int32_t* d_items, int64_t n, int32_t k,
                        const_cast<int32_t*>(d_kept_cnt), const_cast<uint32_t*>(d_kept_mask),
                        d_kept_off, d_cand_p, d_cand_q, s);
   if (rc) return rc;
+  if (d_grp_p == nullptr) return 0;  // caller does not need the parent list
   if (n == 0) {
     KMLS_CUDA(cudaMemsetAsync(d_n_groups, 0, sizeof(int64_t), s));
     return 0;

@@ -1,0 +1,237 @@
+// Conditional (projected) bitmaps for levels k >= 3.
+//
+// mlxtend's FP-Growth gets its speed from conditional trees: once a prefix is fixed only
+// the transactions containing it are looked at (FPTree.conditional_tree, reached from
+// reference machine-learning/main.py:272). The bitmap analogue used here: every frequent
+// k-itemset X = (P, x) owns a bit row over the playlists that contain its class prefix P
+// (columns compacted, so the row is c(P) bits wide, not N). Then
+//   * the support of a candidate (P, x_i, x_j) is popcount(row(P,x_i) AND row(P,x_j));
+//   * the row of a new (k+1)-itemset (P, x_i, x_j) is row(P,x_j) with the columns where
+//     row(P,x_i) is 0 squeezed out (a parallel bit extract), c(P,x_i) bits wide.
+// Level 1 is the full bitmap (P = {}, all N columns). Work per candidate therefore shrinks
+// with the support of its prefix instead of staying at N/8 bytes.
+#include "common.cuh"
+#include "kmls_b200.h"
+
+namespace kmls {
+
+// ---------------------------------------------------------------------------------------
+// K4 (projected form): one warp per candidate (p, q): popcount(row_p AND row_q) with 128-bit
+// loads and a warp-shuffle reduce. Both rows live in the class's compacted column space and
+// are roww[p] words wide. Algorithmic bytes: 2 * roww * 4 per candidate.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_count_pairs(const uint32_t* __restrict__ arena, const int64_t* __restrict__ rowptr,
+              const int32_t* __restrict__ roww, const int32_t* __restrict__ cand_p,
+              const int32_t* __restrict__ cand_q, int64_t n_cand, int32_t* __restrict__ cand_cnt) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_cand;
+       c += (int64_t)gridDim.x * 8) {
+    const int32_t p = __ldg(cand_p + c), q = __ldg(cand_q + c);
+    const int nv = __ldg(roww + p) >> 2;
+    const uint4* rp = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + p));
+    const uint4* rq = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + q));
+    int acc = 0;
+    for (int v = lane; v < nv; v += 32) acc += popc4(and4(ldg4(rp + v), ldg4(rq + v)));
+    acc = warp_sum(acc);
+    if (lane == 0) cand_cnt[c] = acc;
+  }
+}
+
+// Filter + emit with parents: like k_emit_level (levelk.cu) and also records, for every new
+// itemset, its two parents and its LOCAL count (this rank's playlists only), which sizes
+// the rows of the next level.
+__global__ void __launch_bounds__(256)
+k_emit_level_px(const int32_t* __restrict__ items, int k, const int32_t* __restrict__ cand_p,
+                const int32_t* __restrict__ cand_q, const int32_t* __restrict__ cand_cnt,
+                const int32_t* __restrict__ cand_cnt_local, int64_t n_cand, int32_t thr,
+                const int64_t* __restrict__ out_off, int32_t* __restrict__ out_items,
+                int32_t* __restrict__ out_counts, int32_t* __restrict__ out_counts_local,
+                int32_t* __restrict__ out_par_p, int32_t* __restrict__ out_par_q) {
+  for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_cand;
+       c += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t cnt = cand_cnt[c];
+    if (cnt < thr) continue;
+    const int64_t o = out_off[c];
+    const int32_t p = cand_p[c], q = cand_q[c];
+    const int32_t* ip = items + (int64_t)p * k;
+    int32_t* op = out_items + o * (k + 1);
+    for (int t = 0; t < k; ++t) op[t] = __ldg(ip + t);
+    op[k] = __ldg(items + (int64_t)q * k + (k - 1));
+    out_counts[o] = cnt;
+    out_counts_local[o] = cand_cnt_local[c];
+    out_par_p[o] = p;
+    out_par_q[o] = q;
+  }
+}
+
+// Row sizing: an itemset gets a row only if its class (same first parent) has at least two
+// members - a lone member can never be joined again. Width = ceil(local count of the
+// parent / 32) words, padded to 4 words (128-bit loads).
+__global__ void __launch_bounds__(256)
+k_row_alloc(const int32_t* __restrict__ par_p, int64_t n, const int32_t* __restrict__ parent_cnt_local,
+            int32_t* __restrict__ roww) {
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < n;
+       o += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t p = par_p[o];
+    const bool shared = (o > 0 && par_p[o - 1] == p) || (o + 1 < n && par_p[o + 1] == p);
+    const int32_t c = __ldg(parent_cnt_local + p);
+    roww[o] = shared ? (((c + 31) >> 5) + 3) & ~3 : 0;
+  }
+}
+
+// Parallel bit extract of one word (Hacker's Delight 7-4 "compress"): the bits of x selected
+// by m, packed towards bit 0.
+__device__ __forceinline__ uint32_t pext32(uint32_t x, uint32_t m) {
+  x &= m;
+  uint32_t mk = ~m << 1;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    uint32_t mp = mk ^ (mk << 1);
+    mp ^= mp << 2;
+    mp ^= mp << 4;
+    mp ^= mp << 8;
+    mp ^= mp << 16;
+    const uint32_t mv = mp & m;
+    m = (m ^ mv) | (mv >> (1 << i));
+    const uint32_t t = x & mv;
+    x = (x ^ t) | (t >> (1 << i));
+    mk &= ~mp;
+  }
+  return x;
+}
+
+// ---------------------------------------------------------------------------------------
+// Projection: one warp per new itemset o. new_row(o) = row(par_q[o]) with the columns where
+// row(par_p[o]) is 0 removed. 32 source words per iteration: per-lane pext, warp scan of the
+// mask popcounts for the bit offsets, assembly of the output words in a small per-warp
+// shared buffer (shared-memory atomicOr), coalesced store of the completed words.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
+               const int32_t* __restrict__ roww_old, const int32_t* __restrict__ par_p,
+               const int32_t* __restrict__ par_q, int64_t n, uint32_t* __restrict__ arena_new,
+               const int64_t* __restrict__ rowptr_new, const int32_t* __restrict__ roww_new) {
+  __shared__ uint32_t sbuf[8][36];
+  const int lane = threadIdx.x & 31;
+  uint32_t* buf = sbuf[threadIdx.x >> 5];
+  for (int64_t o = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); o < n;
+       o += (int64_t)gridDim.x * 8) {
+    const int w_new = __ldg(roww_new + o);
+    if (w_new == 0) continue;  // warp-uniform
+    const int32_t p = __ldg(par_p + o), q = __ldg(par_q + o);
+    const int w_old = __ldg(roww_old + p);
+    const uint32_t* msk = arena_old + __ldg(rowptr_old + p);
+    const uint32_t* src = arena_old + __ldg(rowptr_old + q);
+    uint32_t* dst = arena_new + __ldg(rowptr_new + o);
+    for (int i = lane; i < 36; i += 32) buf[i] = 0;
+    __syncwarp();
+    int base = 0;  // bits emitted so far
+    for (int blk = 0; blk < w_old; blk += 32) {
+      const int w = blk + lane;
+      const uint32_t m = w < w_old ? __ldg(msk + w) : 0u;
+      const uint32_t x = w < w_old ? __ldg(src + w) : 0u;
+      const int nb = __popc(m);
+      int incl = nb;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += u;
+      }
+      const int tot = __shfl_sync(0xffffffffu, incl, 31);
+      if (nb) {
+        const uint32_t c = pext32(x, m);
+        const int bitpos = (base & 31) + incl - nb;
+        const int word = bitpos >> 5, sh = bitpos & 31;
+        if (c) {
+          atomicOr(buf + word, c << sh);
+          if (sh + nb > 32) atomicOr(buf + word + 1, c >> (32 - sh));
+        }
+      }
+      __syncwarp();
+      const int nbits = (base & 31) + tot, full = nbits >> 5, w0 = base >> 5;
+      for (int i = lane; i < full; i += 32)
+        if (w0 + i < w_new) dst[w0 + i] = buf[i];
+      const uint32_t partial = buf[full];
+      __syncwarp();
+      for (int i = lane; i < 36; i += 32) buf[i] = 0;
+      __syncwarp();
+      if (lane == 0) buf[0] = partial;
+      __syncwarp();
+      base += tot;
+    }
+    int done = base >> 5;
+    if ((base & 31) && lane == 0 && done < w_new) dst[done] = buf[0];
+    if (base & 31) ++done;
+    for (int i = done + lane; i < w_new; i += 32) dst[i] = 0u;
+    __syncwarp();
+  }
+}
+
+}  // namespace kmls
+
+using namespace kmls;
+
+extern "C" int kmls_count_pairs(const uint32_t* d_arena, const int64_t* d_rowptr,
+                                const int32_t* d_roww, const int32_t* d_cand_p,
+                                const int32_t* d_cand_q, int64_t n_cand, int32_t* d_cand_cnt,
+                                kmls_stream_t stream) {
+  KMLS_REQUIRE(n_cand >= 0, "kmls_count_pairs: negative size");
+  if (n_cand == 0) return 0;
+  KMLS_REQUIRE(d_arena && d_rowptr && d_roww && d_cand_p && d_cand_q && d_cand_cnt,
+               "kmls_count_pairs: null pointer");
+  int grid = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)num_sms() * 64);
+  k_count_pairs<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena, d_rowptr, d_roww, d_cand_p,
+                                                        d_cand_q, n_cand, d_cand_cnt);
+  KMLS_LAUNCHED("k_count_pairs");
+  return 0;
+}
+
+extern "C" int kmls_emit_level_px(const int32_t* d_items, int32_t k, const int32_t* d_cand_p,
+                                  const int32_t* d_cand_q, const int32_t* d_cand_cnt,
+                                  const int32_t* d_cand_cnt_local, int64_t n_cand, int32_t thr,
+                                  const int64_t* d_out_off, int32_t* d_out_items,
+                                  int32_t* d_out_counts, int32_t* d_out_counts_local,
+                                  int32_t* d_out_par_p, int32_t* d_out_par_q,
+                                  kmls_stream_t stream) {
+  KMLS_REQUIRE(n_cand >= 0 && k >= 1, "kmls_emit_level_px: bad arguments");
+  if (n_cand == 0) return 0;
+  KMLS_REQUIRE(d_out_off && d_out_items && d_out_counts && d_out_counts_local && d_out_par_p &&
+                   d_out_par_q && d_cand_cnt_local,
+               "kmls_emit_level_px: null pointer");
+  int grid = (int)std::min<int64_t>((n_cand + 255) / 256, (int64_t)num_sms() * 16);
+  k_emit_level_px<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      d_items, k, d_cand_p, d_cand_q, d_cand_cnt, d_cand_cnt_local, n_cand, thr, d_out_off,
+      d_out_items, d_out_counts, d_out_counts_local, d_out_par_p, d_out_par_q);
+  KMLS_LAUNCHED("k_emit_level_px");
+  return 0;
+}
+
+extern "C" int kmls_row_alloc(const int32_t* d_par_p, int64_t n, const int32_t* d_parent_cnt_local,
+                              int32_t* d_roww, kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0, "kmls_row_alloc: negative size");
+  if (n == 0) return 0;
+  KMLS_REQUIRE(d_par_p && d_parent_cnt_local && d_roww, "kmls_row_alloc: null pointer");
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
+  k_row_alloc<<<grid, 256, 0, (cudaStream_t)stream>>>(d_par_p, n, d_parent_cnt_local, d_roww);
+  KMLS_LAUNCHED("k_row_alloc");
+  return 0;
+}
+
+extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
+                                 const int32_t* d_roww_old, const int32_t* d_par_p,
+                                 const int32_t* d_par_q, int64_t n, uint32_t* d_arena_new,
+                                 const int64_t* d_rowptr_new, const int32_t* d_roww_new,
+                                 kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0, "kmls_project_rows: negative size");
+  if (n == 0) return 0;
+  KMLS_REQUIRE(d_arena_old && d_rowptr_old && d_roww_old && d_par_p && d_par_q && d_arena_new &&
+                   d_rowptr_new && d_roww_new && (const void*)d_arena_old != (const void*)d_arena_new,
+               "kmls_project_rows: null or aliased pointer");
+  int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 64);
+  k_project_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena_old, d_rowptr_old, d_roww_old,
+                                                         d_par_p, d_par_q, n, d_arena_new,
+                                                         d_rowptr_new, d_roww_new);
+  KMLS_LAUNCHED("k_project_rows");
+  return 0;
+}

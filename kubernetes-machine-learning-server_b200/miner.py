@@ -127,12 +127,15 @@ def _world(group):
 def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
              n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
-             pair_impl: str = "auto") -> MineResult:
+             pair_impl: str = "auto", count_impl: str = "projected",
+             prune: bool = True) -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
     ``n_playlists_total`` is N of the whole job (sum over ranks); it defaults to the local
-    count (allreduced when ``group`` is given)."""
+    count (allreduced when ``group`` is given). ``count_impl``: "projected" counts candidates
+    on conditional (column-compacted) bitmaps, "fullwidth" on the full bitmap with the prefix
+    staged in shared memory. ``prune`` switches Apriori pruning of the joins."""
     if min_support <= 0.0:
         thresholds(min_support, 1)  # raises the reference's ValueError
     if not (offsets.is_cuda and items.is_cuda):
@@ -178,6 +181,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     counts1 = dev.empty(n_rows, torch.int32)
     _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s,
               algo_bytes=4 * n_rows * row_words)
+    counts1_local_box = [counts1.clone() if group is not None else counts1]
     _allreduce(counts1, group)
     if not bool(torch.equal(counts1, occ[cand])):
         # some playlist repeated a track: exact supports differ from the occurrence counts,
@@ -191,6 +195,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         bitmap2 = dev.empty(n_rows * row_words, torch.int32)
         _lib.call("kmls_gather_rows", bitmap, src, n_rows, row_words, bitmap2, s)
         bitmap, counts1, cand = bitmap2, counts1[src.long()].contiguous(), cand[src.long()]
+        counts1_local_box[0] = counts1_local_box[0][src.long()].contiguous()
     row_items = cand.to(torch.int32)
     lvl1_items = torch.arange(n_rows, dtype=torch.int32, device=dev.device).reshape(-1, 1)
     levels = [(lvl1_items, counts1)]
@@ -200,6 +205,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         return result(row_items, levels)
 
     # ---- level 2 -------------------------------------------------------------------------
+    counts1_local = counts1_local_box[0]
     pair = dev.empty(n_rows * n_rows, torch.int32)
     if pair_impl == "auto":
         pair_impl = "popc"
@@ -207,6 +213,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
     else:
         raise ValueError(f"unknown pair_impl {pair_impl!r}")
+    pair_local = pair.clone() if group is not None else pair
     _allreduce(pair, group)
     thr = tk
     if t1 < tk:
@@ -229,13 +236,41 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     _lib.call("kmls_pair_select", pair, n_rows, thr, n2, row_off, items_k, counts_k, s)
     levels.append((items_k.view(n2, 2), counts_k))
     total = n_rows + n2
+    projected = count_impl == "projected"
+    more = (max_len is None or 2 < max_len) and n2 >= 2
+
+    def project(arena_old, rowptr_old, roww_old, par_p, par_q, parent_cnt_local, n_new):
+        """Rows of a new level from the rows of its parents' level."""
+        roww = dev.empty(n_new, torch.int32)
+        _lib.call("kmls_row_alloc", par_p, n_new, parent_cnt_local, roww, s)
+        scratch, sbytes = dev.scan_scratch(n_new)
+        rowptr = dev.empty(n_new + 1, torch.int64)
+        _lib.call("kmls_exclusive_scan_i32", roww, n_new, rowptr, scratch, sbytes, s)
+        words = int(rowptr[n_new].item())
+        arena = dev.empty(words, torch.int32)
+        _lib.call("kmls_project_rows", arena_old, rowptr_old, roww_old, par_p, par_q, n_new, arena,
+                  rowptr, roww, s, algo_bytes=8 * words)
+        return arena, rowptr, roww, words
+
+    if projected and more:
+        rowptr1 = torch.arange(n_rows, dtype=torch.int64, device=dev.device) * row_words
+        roww1 = torch.full((n_rows,), row_words, dtype=torch.int32, device=dev.device)
+        it2 = items_k.view(n2, 2)
+        par_p, par_q = it2[:, 0].contiguous(), it2[:, 1].contiguous()
+        if group is not None:
+            cnt_loc_k = pair_local.view(n_rows, n_rows)[par_p.long(), par_q.long()].contiguous()
+        else:
+            cnt_loc_k = counts_k
+        arena_k, rowptr_k, roww_k, words = project(bitmap, rowptr1, roww1, par_p, par_q,
+                                                   counts1_local, n2)
+        stats["levels"][-1]["row_words_total"] = words
 
     # ---- levels k >= 3 -------------------------------------------------------------------
     k = 2
     while (max_len is None or k < max_len) and int(counts_k.numel()) >= 2:
         n = int(counts_k.numel())
         scratch, sbytes = dev.scan_scratch(n)
-        if k >= 3:
+        if k >= 3 and prune:
             cap = int(_lib.value("kmls_set_capacity", n))
             slots = dev.empty(cap, torch.int64)
             _lib.call("kmls_itemset_set_build", items_k, n, k, slots, cap, s)
@@ -244,7 +279,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         kept_cnt = dev.empty(n, torch.int32)
         kept_mask = dev.empty(n, torch.int32)
         kept_off = dev.empty(n + 1, torch.int64)
-        _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair, n_rows, thr, kept_cnt,
+        pair_arg = pair if (k == 2 and prune) else 0
+        _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
                   kept_mask, kept_off, scratch, sbytes, s)
         n_cand = int(kept_off[n].item())
         if n_cand == 0:
@@ -253,15 +289,23 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
             raise _lib.KmlsError(f"level {k + 1}: {n_cand} candidates exceed the max_itemsets guard")
         cand_p = dev.empty(n_cand, torch.int32)
         cand_q = dev.empty(n_cand, torch.int32)
-        grp_p = dev.empty(n, torch.int32)
-        n_groups_d = dev.empty(1, torch.int64)
-        _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair, n_rows, thr, kept_cnt,
-                  kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
-        n_groups = int(n_groups_d.item())
         cand_cnt = dev.empty(n_cand, torch.int32)
-        _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
-                  kept_off, cand_q, n_cand, cand_cnt, s,
-                  algo_bytes=(n_cand + n_groups * k) * row_words * 4)
+        if projected:
+            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
+                      kept_mask, kept_off, cand_p, cand_q, 0, 0, scratch, sbytes, s)
+            n_groups = None
+            _lib.call("kmls_count_pairs", arena_k, rowptr_k, roww_k, cand_p, cand_q, n_cand,
+                      cand_cnt, s)
+            cand_cnt_local = cand_cnt.clone() if group is not None else cand_cnt
+        else:
+            grp_p = dev.empty(n, torch.int32)
+            n_groups_d = dev.empty(1, torch.int64)
+            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
+                      kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
+            n_groups = int(n_groups_d.item())
+            _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
+                      kept_off, cand_q, n_cand, cand_cnt, s,
+                      algo_bytes=(n_cand + n_groups * k) * row_words * 4)
         _allreduce(cand_cnt, group)
         scratch, sbytes = dev.scan_scratch(n_cand)
         out_off = dev.empty(n_cand + 1, torch.int64)
@@ -278,8 +322,20 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
                 "raise the guard or min_support (results are never truncated)")
         items_n = dev.empty(n_next * (k + 1), torch.int32)
         counts_n = dev.empty(n_next, torch.int32)
-        _lib.call("kmls_emit_level", items_k, k, cand_p, cand_q, cand_cnt, n_cand, thr, out_off,
-                  items_n, counts_n, s)
+        if projected:
+            cnt_loc_n = dev.empty(n_next, torch.int32)
+            par_p = dev.empty(n_next, torch.int32)
+            par_q = dev.empty(n_next, torch.int32)
+            _lib.call("kmls_emit_level_px", items_k, k, cand_p, cand_q, cand_cnt, cand_cnt_local,
+                      n_cand, thr, out_off, items_n, counts_n, cnt_loc_n, par_p, par_q, s)
+            if (max_len is None or k + 1 < max_len) and n_next >= 2:
+                arena_k, rowptr_k, roww_k, words = project(arena_k, rowptr_k, roww_k, par_p, par_q,
+                                                           cnt_loc_k, n_next)
+                stats["levels"][-1]["row_words_total"] = words
+            cnt_loc_k = cnt_loc_n
+        else:
+            _lib.call("kmls_emit_level", items_k, k, cand_p, cand_q, cand_cnt, n_cand, thr, out_off,
+                      items_n, counts_n, s)
         k += 1
         items_k, counts_k = items_n, counts_n
         levels.append((items_k.view(n_next, k), counts_k))

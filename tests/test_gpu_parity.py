@@ -152,6 +152,66 @@ def test_exclusive_scan():
     assert int(out[-1].item()) == 3_000_000_000
 
 
+def test_project_rows_and_count_pairs():
+    """Projection = numpy boolean compress; pair count = popcount of the AND."""
+    rng = np.random.default_rng(3)
+    n_cols, n_rows = 5000, 40
+    W = int(_lib.value("kmls_bitmap_row_words", n_cols))
+    dense = rng.random((n_rows, n_cols)) < rng.uniform(0.01, 0.9, (n_rows, 1))
+    dense[7] = False                      # an empty mask row
+    dense[8] = True                       # a full mask row
+    full = np.zeros((n_rows, W * 32), bool)
+    full[:, :n_cols] = dense
+    bm = torch.from_numpy(np.packbits(full, axis=1, bitorder="little").view(np.int32).reshape(-1)).to(dev())
+    rowptr1 = torch.arange(n_rows, dtype=torch.int64, device=dev()) * W
+    roww1 = torch.full((n_rows,), W, dtype=torch.int32, device=dev())
+    cnt1 = torch.from_numpy(dense.sum(1).astype(np.int32)).to(dev())
+    # new "itemsets": (p, q) pairs sorted by p; p = 5 appears once only (gets no row)
+    pq = [(p, q) for p in range(0, 12) for q in range(p + 1, min(p + 4, n_rows))] + [(20, 30)]
+    par_p = torch.tensor([a for a, _ in pq], dtype=torch.int32, device=dev())
+    par_q = torch.tensor([b for _, b in pq], dtype=torch.int32, device=dev())
+    n = len(pq)
+    roww = torch.empty(n, dtype=torch.int32, device=dev())
+    _lib.call("kmls_row_alloc", par_p, n, cnt1, roww, stream())
+    want_w = [(((int(dense[a].sum()) + 31) // 32 + 3) // 4 * 4) if a != 20 else 0 for a, _ in pq]
+    assert roww.cpu().tolist() == want_w
+    sb = int(_lib.value("kmls_scan_scratch_bytes", n))
+    scratch = torch.empty(sb, dtype=torch.uint8, device=dev())
+    rowptr = torch.empty(n + 1, dtype=torch.int64, device=dev())
+    _lib.call("kmls_exclusive_scan_i32", roww, n, rowptr, scratch, sb, stream())
+    words = int(rowptr[n].item())
+    arena = torch.full((max(words, 1),), 0x7BADBEEF, dtype=torch.int32, device=dev())
+    _lib.call("kmls_project_rows", bm, rowptr1, roww1, par_p, par_q, n, arena, rowptr, roww, stream())
+    got = arena.cpu().numpy().view(np.uint32)
+    rp = rowptr.cpu().numpy()
+    for i, (a, b) in enumerate(pq):
+        if want_w[i] == 0:
+            continue
+        bits = np.zeros(want_w[i] * 32, bool)
+        sel = dense[b][dense[a]]
+        bits[:len(sel)] = sel
+        want = np.packbits(bits, bitorder="little").view(np.uint32)
+        assert (got[rp[i]:rp[i] + want_w[i]] == want).all(), (i, a, b)
+    # candidates: consecutive members of the same class
+    cand = [(i, j) for i in range(n) for j in range(i + 1, n) if pq[i][0] == pq[j][0] and want_w[i]]
+    cp = torch.tensor([i for i, _ in cand], dtype=torch.int32, device=dev())
+    cq = torch.tensor([j for _, j in cand], dtype=torch.int32, device=dev())
+    cc = torch.empty(len(cand), dtype=torch.int32, device=dev())
+    _lib.call("kmls_count_pairs", arena, rowptr, roww, cp, cq, len(cand), cc, stream())
+    want_c = [int((dense[pq[i][0]] & dense[pq[i][1]] & dense[pq[j][1]]).sum()) for i, j in cand]
+    assert cc.cpu().tolist() == want_c
+
+
+@pytest.mark.parametrize("count_impl,prune", [("projected", True), ("projected", False),
+                                              ("fullwidth", True), ("fullwidth", False)])
+def test_counting_variants_agree(count_impl, prune):
+    off, items = synth.zipf_playlists(9000, 700, mean_draws=30, alpha=0.9, seed=31)
+    want = oracle_dict(off, items, 700, 0.012)
+    res, _ = kmls_b200.mine_ids(off, items, 700, 0.012, count_impl=count_impl, prune=prune)
+    assert res.as_dict() == want
+    assert len(res.levels) >= 5
+
+
 # ------------------------------------------------------------------- the whole path, small cases
 @pytest.mark.parametrize("case", CASES, ids=[c["name"] for c in CASES])
 def test_hand_vectors_through_the_plugin_boundary(case, capsys):
