@@ -166,7 +166,7 @@ def test_project_rows_and_count_pairs():
     rowptr1 = torch.arange(n_rows, dtype=torch.int64, device=dev()) * W
     roww1 = torch.full((n_rows,), W, dtype=torch.int32, device=dev())
     cnt1 = torch.from_numpy(dense.sum(1).astype(np.int32)).to(dev())
-    # new "itemsets": (p, q) pairs sorted by p; p = 5 appears once only (gets no row)
+    # new "itemsets": (p, q) pairs sorted by p; p = 20 appears once only (gets no row)
     pq = [(p, q) for p in range(0, 12) for q in range(p + 1, min(p + 4, n_rows))] + [(20, 30)]
     par_p = torch.tensor([a for a, _ in pq], dtype=torch.int32, device=dev())
     par_q = torch.tensor([b for _, b in pq], dtype=torch.int32, device=dev())
