@@ -160,31 +160,38 @@ int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
 /* ---- rules (mlxtend association_rules semantics; the dormant path main.py:224-260 is the
  *      only reference site of a min_confidence knob) -------------------------------------- */
 
-/* All level tables concatenated: level k's items start at sum_{j<k} level_sizes[j]*j in
- * d_items and its counts at sum_{j<k} level_sizes[j] in d_counts; level_sizes is a HOST
- * array indexed 1..max_k (index 0 unused). Exact map fingerprint -> itemset. */
-int kmls_itemset_map_build(const int32_t* d_items, const int32_t* d_counts,
-                           const int64_t* level_sizes, int32_t max_k, uint64_t* d_keys,
-                           int32_t* d_vals, int64_t capacity, kmls_stream_t stream);
-/* Itemsets of size >= 2 are numbered x = 0, 1, ... in table order; a call handles
- * x_begin <= x < x_begin + x_count (ranks may split the table). d_rule_cnt[x - x_begin] =
- * rules kept for itemset x; *d_missing counts subset lookups that failed (0 for a
- * downward-closed table; caller zeroes it). */
+/* All level tables concatenated ("arena"): level k's members start at
+ * sum_{j<k} level_sizes[j]*j in d_items and its counts at sum_{j<k} level_sizes[j] in
+ * d_counts (= its first global id); level_sizes is a HOST array indexed 1..max_k (index 0
+ * unused). d_par[g - level_sizes[1]] = index, inside level k-1, of the parent (itemset
+ * without its last member) of the itemset with global id g (sizes >= 2 only).
+ *
+ * Exact subset index: (parent global id, last member) -> (global id, count), 16-byte slots,
+ * capacity a power of two >= 2 * (number of itemsets of size >= 2), 16-byte aligned. */
+int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
+                          const int64_t* level_sizes, int32_t max_k, void* d_slots,
+                          int64_t capacity, kmls_stream_t stream);
+/* (antecedent, consequent) splits examined per k-itemset = 2^(k-1) - 1 (each yields up to
+ * two rules); -1 if k is not supported (k > 15). */
+int64_t kmls_rules_parts_per_itemset(int32_t k);
+/* Pass 1 for the itemsets lvl_begin .. lvl_begin+lvl_count-1 of level k (ranks may split a
+ * level): d_part[lvl_count * parts_per_itemset(k)] (8 bytes each) receives the subset counts
+ * of every split, d_rule_cnt[lvl_count] the number of kept rules per itemset; *d_missing
+ * counts failed subset lookups (0 for a downward-closed table; caller zeroes it). */
 int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
-                     int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
-                     int64_t capacity, int64_t n_playlists_total, double min_confidence,
-                     int64_t x_begin, int64_t x_count, int32_t* d_rule_cnt, int32_t* d_missing,
+                     int32_t max_k, int32_t k, int64_t lvl_begin, int64_t lvl_count,
+                     const void* d_slots, int64_t capacity, int64_t n_playlists_total,
+                     double min_confidence, void* d_part, int32_t* d_rule_cnt, int32_t* d_missing,
                      kmls_stream_t stream);
-/* d_rule_off = exclusive scan of d_rule_cnt (x_count + 1 entries).
- * Rule r: itemset d_out_itemset[r] (global id), antecedent = members selected by the bits
- * of d_out_antecedent[r] (bit t = t-th member), consequent = the rest. */
-int kmls_rules_write(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
-                     int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
-                     int64_t capacity, int64_t n_playlists_total, double min_confidence,
-                     int64_t x_begin, int64_t x_count, const int64_t* d_rule_off,
-                     int32_t* d_out_itemset,
-                     uint32_t* d_out_antecedent, double* d_out_support, double* d_out_confidence,
-                     double* d_out_lift, int32_t* d_missing, kmls_stream_t stream);
+/* Pass 2: d_rule_off[lvl_count] = first output slot of each itemset (exclusive scan of the
+ * kept counts over everything this rank emits). Rule r: itemset d_out_itemset[r] (global
+ * id), antecedent = members selected by the bits of d_out_antecedent[r] (bit t = t-th
+ * member), consequent = the rest. */
+int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
+                     int32_t k, int64_t lvl_begin, int64_t lvl_count, int64_t n_playlists_total,
+                     double min_confidence, const void* d_part, const int64_t* d_rule_off,
+                     int32_t* d_out_itemset, uint32_t* d_out_antecedent, double* d_out_support,
+                     double* d_out_confidence, double* d_out_lift, kmls_stream_t stream);
 
 #ifdef __cplusplus
 }

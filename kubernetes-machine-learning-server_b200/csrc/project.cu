@@ -178,7 +178,8 @@ extern "C" int kmls_count_pairs(const uint32_t* d_arena, const int64_t* d_rowptr
                                 kmls_stream_t stream) {
   KMLS_REQUIRE(n_cand >= 0, "kmls_count_pairs: negative size");
   if (n_cand == 0) return 0;
-  KMLS_REQUIRE(d_arena && d_rowptr && d_roww && d_cand_p && d_cand_q && d_cand_cnt,
+  // d_arena may be NULL when no row of the level was materialised (all widths are 0)
+  KMLS_REQUIRE(d_rowptr && d_roww && d_cand_p && d_cand_q && d_cand_cnt,
                "kmls_count_pairs: null pointer");
   int grid = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)num_sms() * 64);
   k_count_pairs<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena, d_rowptr, d_roww, d_cand_p,
@@ -225,9 +226,12 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
                                  kmls_stream_t stream) {
   KMLS_REQUIRE(n >= 0, "kmls_project_rows: negative size");
   if (n == 0) return 0;
-  KMLS_REQUIRE(d_arena_old && d_rowptr_old && d_roww_old && d_par_p && d_par_q && d_arena_new &&
-                   d_rowptr_new && d_roww_new && (const void*)d_arena_old != (const void*)d_arena_new,
-               "kmls_project_rows: null or aliased pointer");
+  // an arena may be NULL when it holds no rows (all widths 0); rows of width 0 are skipped
+  KMLS_REQUIRE(d_rowptr_old && d_roww_old && d_par_p && d_par_q && d_rowptr_new && d_roww_new,
+               "kmls_project_rows: null pointer");
+  KMLS_REQUIRE(d_arena_new == nullptr || (const void*)d_arena_old != (const void*)d_arena_new,
+               "kmls_project_rows: source and destination arenas alias");
+  if (d_arena_new == nullptr) return 0;
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 64);
   k_project_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena_old, d_rowptr_old, d_roww_old,
                                                          d_par_p, d_par_q, n, d_arena_new,

@@ -9,18 +9,30 @@
 // kept iff confidence >= c. The operation order above is mlxtend's (it divides the already
 // rounded supports), so the doubles are bit-identical, not merely within 1e-12.
 //
-// All levels' tables live in one arena: items of level k start at item_off[k], its
-// itemsets have global ids id_off[k] .. id_off[k+1]-1, counts are indexed by global id.
+// Subset counts come from an EXACT index, not from fingerprints: the level tables form a
+// trie (an itemset's parent is the itemset without its last member), and the index maps the
+// 64-bit key (parent global id, last member) to (global id, count) - one 16-byte slot, one
+// 32-byte sector per probe, nothing to verify. A warp that owns a class (siblings sharing
+// the prefix P) first resolves all 2^(k-1) subsets of P by dynamic programming over that
+// index (subset = smaller subset + its largest member) into shared memory, then needs ONE
+// probe per (sibling, antecedent): the consequent's count.
+//
+// All levels' tables live in one arena: items of level k start at item_off[k], its itemsets
+// have global ids id_off[k] .. id_off[k+1]-1, counts are indexed by global id; `par` holds,
+// for every itemset of size >= 2 (indexed by global id - id_off[2]), the index of its parent
+// inside level k-1.
 #include "common.cuh"
 #include "kmls_b200.h"
 
 namespace kmls {
 
 constexpr int kMaxLevels = 32;
+constexpr int kMaxRuleK = 15;  // 2^(k-1) subset table per warp must fit in shared memory
 
 struct Arena {
   const int32_t* items;
   const int32_t* counts;
+  const int32_t* par;
   int64_t item_off[kMaxLevels + 2];
   int64_t id_off[kMaxLevels + 2];
   int max_k;
@@ -30,130 +42,187 @@ __device__ __forceinline__ const int32_t* itemset_ptr(const Arena& a, int k, int
   return a.items + a.item_off[k] + (gid - a.id_off[k]) * k;
 }
 
-// Exact map: fingerprint -> global id. Distinct itemsets with the same fingerprint occupy
-// different slots; a lookup verifies the members.
-__global__ void __launch_bounds__(256) k_map_build(Arena a, unsigned long long* __restrict__ keys,
-                                                   int32_t* __restrict__ vals, uint64_t mask) {
-  const int64_t n = a.id_off[a.max_k + 1];
-  for (int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < n;
+__device__ __forceinline__ uint64_t edge_key(int32_t parent_gid, int32_t item) {
+  return ((uint64_t)(uint32_t)parent_gid << 32) | (uint32_t)item;
+}
+constexpr unsigned long long kEmptyEdge = ~0ull;
+
+// slot = {key lo, key hi, child global id, child count}
+__global__ void __launch_bounds__(256) k_trie_build(Arena a, uint4* __restrict__ slots, uint64_t mask) {
+  const int64_t first = a.id_off[2], n = a.id_off[a.max_k + 1];
+  for (int64_t gid = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < n;
        gid += (int64_t)gridDim.x * blockDim.x) {
-    int k = 1;
+    int k = 2;
     while (gid >= a.id_off[k + 1]) ++k;
-    const int32_t* it = itemset_ptr(a, k, gid);
-    uint64_t s = 0;
-    for (int t = 0; t < k; ++t) s += item_term(__ldg(it + t));
-    const uint64_t key = finish_key(s, k);
-    uint64_t h = (key >> 20) & mask;
-    while (atomicCAS(keys + h, 0ull, (unsigned long long)key) != 0ull) h = (h + 1) & mask;
-    vals[h] = (int32_t)gid;
+    const int32_t parent = (int32_t)(a.id_off[k - 1] + __ldg(a.par + (gid - first)));
+    const int32_t last = __ldg(itemset_ptr(a, k, gid) + (k - 1));
+    const uint64_t key = edge_key(parent, last);
+    uint64_t h = mix64(key) & mask;
+    while (atomicCAS(reinterpret_cast<unsigned long long*>(slots + h), kEmptyEdge,
+                     (unsigned long long)key) != kEmptyEdge)
+      h = (h + 1) & mask;
+    reinterpret_cast<int2*>(slots + h)[1] = make_int2((int32_t)gid, __ldg(a.counts + gid));
   }
 }
 
-// count of the subset of `x` (k members) selected by `sel`; -1 if it is not in the map
-// (cannot happen for a downward-closed table; reported by the caller).
-__device__ __forceinline__ int32_t subset_count(const Arena& a, const unsigned long long* __restrict__ keys,
-                                                const int32_t* __restrict__ vals, uint64_t mask,
-                                                const int32_t* __restrict__ x, int k, uint32_t sel,
-                                                uint64_t sum) {
-  const int r = __popc(sel);
-  const uint64_t key = finish_key(sum, r);
-  uint64_t h = (key >> 20) & mask;
+// (child gid, child count) of the edge (parent_gid, item); gid = -1 if absent.
+__device__ __forceinline__ int2 trie_child(const uint4* __restrict__ slots, uint64_t mask,
+                                           int32_t parent_gid, int32_t item) {
+  const uint64_t key = edge_key(parent_gid, item);
+  uint64_t h = mix64(key) & mask;
   while (true) {
-    const unsigned long long v = __ldg(keys + h);
-    if (v == 0ull) return -1;
-    if (v == key) {
-      const int32_t gid = __ldg(vals + h);
-      if (gid >= a.id_off[r] && gid < a.id_off[r + 1]) {
-        const int32_t* it = itemset_ptr(a, r, gid);
-        bool same = true;
-        int j = 0;
-        for (int t = 0; t < k && same; ++t)
-          if (sel >> t & 1u) same = __ldg(it + j++) == __ldg(x + t);
-        if (same) return __ldg(a.counts + gid);
-      }
-    }
+    const uint4 s = __ldg(slots + h);
+    const uint64_t sk = ((uint64_t)s.y << 32) | s.x;
+    if (sk == key) return make_int2((int32_t)s.z, (int32_t)s.w);
+    if (sk == kEmptyEdge) return make_int2(-1, -1);
     h = (h + 1) & mask;
   }
 }
 
-// K5. One warp per itemset X (global ids of levels >= 2). Lanes enumerate the selections
-// `sel` with the top member excluded; each handles the partition {A = sel, C = complement}
-// and therefore two rules (A -> C and C -> A) from two lookups. Pass 1 counts the kept rules
-// per itemset; pass 2 writes them at rule_off[x] + rank (ballot + popc rank), ordered by
-// sel, A -> C before C -> A. Only the itemsets x_begin .. x_begin + x_count - 1 (numbered
-// from the first 2-itemset) are processed, so ranks can split the table; rule_cnt/rule_off
-// are indexed from x_begin.
+struct RuleVals {
+  bool k1, k2;
+  double c1, c2, l1, l2;
+};
+__device__ __forceinline__ RuleVals rule_values(double s_x, int32_t ca, int32_t cc, double n_total,
+                                                double min_conf) {
+  RuleVals r;
+  const double s_a = __ddiv_rn((double)ca, n_total), s_c = __ddiv_rn((double)cc, n_total);
+  r.c1 = __ddiv_rn(s_x, s_a);
+  r.c2 = __ddiv_rn(s_x, s_c);
+  r.k1 = r.c1 >= min_conf;
+  r.k2 = r.c2 >= min_conf;
+  r.l1 = __ddiv_rn(r.c1, s_c);
+  r.l2 = __ddiv_rn(r.c2, s_a);
+  return r;
+}
+
+// ---------------------------------------------------------------------------------------
+// K5 pass 1, one level k >= 2 per launch. One warp per itemset; only class heads (and the
+// first itemset of the range) work: they resolve the subsets of the class prefix P, then
+// walk their siblings. For every (itemset x, antecedent mask a over P) the pair
+// (count(A), count(C)) goes to `part` (so that pass 2 needs no lookups) and the number of
+// kept rules of x to rule_cnt. A = members of P selected by a; C = the rest of P plus the
+// last member.
+// ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-k_rules(Arena a, const unsigned long long* __restrict__ keys, const int32_t* __restrict__ vals,
-        uint64_t mask, double n_total, double min_conf, int64_t x_begin, int64_t x_count, int write,
-        int32_t* __restrict__ rule_cnt,
-        const int64_t* __restrict__ rule_off, int32_t* __restrict__ out_itemset,
-        uint32_t* __restrict__ out_antecedent, double* __restrict__ out_support,
-        double* __restrict__ out_confidence, double* __restrict__ out_lift,
-        int32_t* __restrict__ missing) {
-  const int lane = threadIdx.x & 31;
-  const int64_t first = a.id_off[2] + x_begin;
-  for (int64_t xi = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); xi < x_count;
-       xi += (int64_t)gridDim.x * 8) {
-    const int64_t gid = first + xi;
-    int k = 2;
-    while (gid >= a.id_off[k + 1]) ++k;
-    const int32_t* x = itemset_ptr(a, k, gid);
-    const double s_x = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
-    uint64_t total = 0;
-    for (int t = 0; t < k; ++t) total += item_term(__ldg(x + t));
-    const uint32_t full = (1u << k) - 1u, half = 1u << (k - 1);
-    int kept = 0;
-    int64_t pos = write ? rule_off[xi] : 0;
-    for (uint32_t s0 = 1; s0 < half; s0 += 32) {
-      const uint32_t sel = s0 + lane;
-      bool k1 = false, k2 = false;
-      double c1 = 0, c2 = 0, l1 = 0, l2 = 0;
-      if (sel < half) {
-        uint64_t sa = 0;
-        for (int t = 0; t < k; ++t)
-          if (sel >> t & 1u) sa += item_term(__ldg(x + t));
-        const int32_t ca = subset_count(a, keys, vals, mask, x, k, sel, sa);
-        const int32_t cc = subset_count(a, keys, vals, mask, x, k, full ^ sel, total - sa);
-        if (ca < 0 || cc < 0) {
-          atomicAdd(missing, 1);
-        } else {
-          const double s_a = __ddiv_rn((double)ca, n_total), s_c = __ddiv_rn((double)cc, n_total);
-          c1 = __ddiv_rn(s_x, s_a);
-          c2 = __ddiv_rn(s_x, s_c);
-          k1 = c1 >= min_conf;
-          k2 = c2 >= min_conf;
-          l1 = __ddiv_rn(c1, s_c);
-          l2 = __ddiv_rn(c2, s_a);
-        }
-      }
-      const uint32_t m1 = __ballot_sync(0xffffffffu, k1), m2 = __ballot_sync(0xffffffffu, k2);
-      if (write) {
-        const uint32_t below = (1u << lane) - 1u;
-        int64_t o = pos + __popc(m1 & below) + __popc(m2 & below);
-        if (k1) {
-          out_itemset[o] = (int32_t)gid; out_antecedent[o] = sel; out_support[o] = s_x;
-          out_confidence[o] = c1; out_lift[o] = l1;
-          ++o;
-        }
-        if (k2) {
-          out_itemset[o] = (int32_t)gid; out_antecedent[o] = full ^ sel; out_support[o] = s_x;
-          out_confidence[o] = c2; out_lift[o] = l2;
-        }
-        pos += __popc(m1) + __popc(m2);
-      } else {
-        kept += __popc(m1) + __popc(m2);
-      }
+k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4* __restrict__ slots,
+              uint64_t mask, double n_total, double min_conf, int2* __restrict__ part,
+              int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
+  extern __shared__ int32_t smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+  const int n_sub = 1 << (k - 1);          // subsets of P (including the empty one)
+  int32_t* tab_gid = smem + (size_t)warp * 2 * n_sub;
+  int32_t* tab_cnt = tab_gid + n_sub;
+  const int64_t lvl_first = a.id_off[k];   // global id of the level's first itemset
+  const int n_part = n_sub - 1;            // antecedent masks 1 .. n_sub-1
+  for (int64_t i = (int64_t)blockIdx.x * nwarps + warp; i < lvl_count;
+       i += (int64_t)gridDim.x * nwarps) {
+    const int32_t* x0 = itemset_ptr(a, k, lvl_first + lvl_begin + i);
+    if (i > 0) {                           // head test: prefix differs from the predecessor's
+      bool same = true;
+      for (int t = 0; t < k - 1; ++t) same = same && (__ldg(x0 + t) == __ldg(x0 - k + t));
+      if (same) continue;
     }
-    if (!write && lane == 0) rule_cnt[xi] = kept;
+    // subsets of P by DP over the trie index
+    for (int h = 0; h < k - 1; ++h) {
+      const int32_t ph = __ldg(x0 + h);
+      for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
+        const int rest = m ^ (1 << h);
+        int2 gc;
+        if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));   // level-1 id = row index
+        else gc = trie_child(slots, mask, tab_gid[rest], ph);
+        if (gc.x < 0) atomicAdd(missing, 1);
+        tab_gid[m] = gc.x;
+        tab_cnt[m] = gc.y;
+      }
+      __syncwarp();
+    }
+    // siblings
+    for (int64_t j = i; j < lvl_count; ++j) {
+      const int32_t* x = itemset_ptr(a, k, lvl_first + lvl_begin + j);
+      if (j > i) {
+        bool same = true;
+        for (int t = 0; t < k - 1; ++t) same = same && (__ldg(x + t) == __ldg(x0 + t));
+        if (!same) break;
+      }
+      const int32_t last = __ldg(x + (k - 1));
+      const double s_x = __ddiv_rn((double)__ldg(a.counts + lvl_first + lvl_begin + j), n_total);
+      int kept = 0;
+      for (int a0 = 1; a0 < n_sub; a0 += 32) {
+        const int am = a0 + lane;
+        bool k1 = false, k2 = false;
+        if (am < n_sub) {
+          const int32_t ca = tab_cnt[am];
+          const int rest = (n_sub - 1) ^ am;
+          int32_t cc;
+          if (rest == 0) cc = __ldg(a.counts + last);
+          else cc = trie_child(slots, mask, tab_gid[rest], last).y;
+          if (cc < 0 || ca < 0) {
+            atomicAdd(missing, 1);
+          } else {
+            const RuleVals r = rule_values(s_x, ca, cc, n_total, min_conf);
+            k1 = r.k1;
+            k2 = r.k2;
+          }
+          part[j * n_part + (am - 1)] = make_int2(ca, cc);
+        }
+        kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
+      }
+      if (lane == 0) rule_cnt[j] = kept;
+    }
+    __syncwarp();
   }
 }
 
-static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts,
+// K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) pairs of pass 1,
+// recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
+// rank): ordered by antecedent mask, A -> C before C -> A.
+__global__ void __launch_bounds__(256)
+k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
+              const int2* __restrict__ part, const int64_t* __restrict__ rule_off,
+              int32_t* __restrict__ out_itemset, uint32_t* __restrict__ out_antecedent,
+              double* __restrict__ out_support, double* __restrict__ out_confidence,
+              double* __restrict__ out_lift) {
+  const int lane = threadIdx.x & 31;
+  const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
+  const uint32_t full = (1u << k) - 1u;
+  const int64_t lvl_first = a.id_off[k];
+  for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < lvl_count;
+       j += (int64_t)gridDim.x * 8) {
+    const int64_t gid = lvl_first + lvl_begin + j;
+    const double s_x = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
+    int64_t pos = rule_off[j];
+    for (int a0 = 1; a0 < n_sub; a0 += 32) {
+      const int am = a0 + lane;
+      RuleVals r;
+      r.k1 = r.k2 = false;
+      if (am < n_sub) {
+        const int2 cc = __ldg(part + j * n_part + (am - 1));
+        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, min_conf);
+      }
+      const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
+      const uint32_t below = (1u << lane) - 1u;
+      int64_t o = pos + __popc(m1 & below) + __popc(m2 & below);
+      if (r.k1) {
+        out_itemset[o] = (int32_t)gid; out_antecedent[o] = (uint32_t)am; out_support[o] = s_x;
+        out_confidence[o] = r.c1; out_lift[o] = r.l1;
+        ++o;
+      }
+      if (r.k2) {
+        out_itemset[o] = (int32_t)gid; out_antecedent[o] = full ^ (uint32_t)am; out_support[o] = s_x;
+        out_confidence[o] = r.c2; out_lift[o] = r.l2;
+      }
+      pos += __popc(m1) + __popc(m2);
+    }
+  }
+}
+
+static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
                       const int64_t* level_sizes, int32_t max_k) {
-  KMLS_REQUIRE(max_k >= 0 && max_k <= kMaxLevels - 8, "rules: more than 24 levels are not supported");
+  KMLS_REQUIRE(max_k >= 0 && max_k <= kMaxLevels - 2, "rules: too many levels");
   a.items = d_items;
   a.counts = d_counts;
+  a.par = d_par;
   a.max_k = max_k;
   a.item_off[0] = a.item_off[1] = 0;
   a.id_off[0] = a.id_off[1] = 0;
@@ -171,69 +240,81 @@ static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts,
 
 using namespace kmls;
 
-extern "C" int kmls_itemset_map_build(const int32_t* d_items, const int32_t* d_counts,
-                                      const int64_t* level_sizes, int32_t max_k, uint64_t* d_keys,
-                                      int32_t* d_vals, int64_t capacity, kmls_stream_t stream) {
+extern "C" int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_counts,
+                                     const int32_t* d_par, const int64_t* level_sizes,
+                                     int32_t max_k, void* d_slots, int64_t capacity,
+                                     kmls_stream_t stream) {
   Arena a;
-  int rc = make_arena(a, d_items, d_counts, level_sizes, max_k);
+  int rc = make_arena(a, d_items, d_counts, d_par, level_sizes, max_k);
   if (rc) return rc;
-  const int64_t n = a.id_off[max_k + 1];
+  const int64_t n = a.id_off[max_k + 1] - a.id_off[2];
   KMLS_REQUIRE(capacity >= 2 * n && capacity > 0 && (capacity & (capacity - 1)) == 0,
-               "kmls_itemset_map_build: capacity must be a power of two >= 2n");
+               "kmls_trie_index_build: capacity must be a power of two >= 2n");
+  KMLS_REQUIRE(d_slots && ((uintptr_t)d_slots & 15) == 0, "kmls_trie_index_build: d_slots must be 16-byte aligned");
   cudaStream_t s = (cudaStream_t)stream;
-  KMLS_CUDA(cudaMemsetAsync(d_keys, 0, sizeof(uint64_t) * (size_t)capacity, s));
-  if (n == 0) return 0;
+  KMLS_CUDA(cudaMemsetAsync(d_slots, 0xFF, sizeof(uint4) * (size_t)capacity, s));
+  if (max_k < 2 || n <= 0) return 0;
+  KMLS_REQUIRE(d_par, "kmls_trie_index_build: d_par is null");
   int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
-  k_map_build<<<grid, 256, 0, s>>>(a, (unsigned long long*)d_keys, d_vals, (uint64_t)capacity - 1);
-  KMLS_LAUNCHED("k_map_build");
+  k_trie_build<<<grid, 256, 0, s>>>(a, (uint4*)d_slots, (uint64_t)capacity - 1);
+  KMLS_LAUNCHED("k_trie_build");
   return 0;
 }
 
-static int launch_rules(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
-                        int32_t max_k, const uint64_t* d_keys, const int32_t* d_vals,
-                        int64_t capacity, int64_t n_total, double min_conf, int64_t x_begin,
-                        int64_t x_count, int write, int32_t* d_rule_cnt, const int64_t* d_rule_off, int32_t* o_itemset,
-                        uint32_t* o_ante, double* o_sup, double* o_conf, double* o_lift,
-                        int32_t* d_missing, cudaStream_t s) {
-  Arena a;
-  int rc = make_arena(a, d_items, d_counts, level_sizes, max_k);
-  if (rc) return rc;
-  KMLS_REQUIRE(n_total > 0, "rules: n_playlists_total must be positive");
-  const int64_t n_x = a.id_off[max_k + 1] - a.id_off[2];
-  KMLS_REQUIRE(x_begin >= 0 && x_count >= 0 && x_begin + x_count <= std::max<int64_t>(n_x, 0),
-               "rules: itemset range out of bounds");
-  const int64_t n = x_count;
-  if (max_k < 2 || n <= 0) return 0;
-  KMLS_REQUIRE(capacity > 0 && (capacity & (capacity - 1)) == 0 && d_keys && d_vals && d_missing,
-               "rules: bad map");
-  int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 32);
-  k_rules<<<grid, 256, 0, s>>>(a, (const unsigned long long*)d_keys, d_vals, (uint64_t)capacity - 1,
-                               (double)n_total, min_conf, x_begin, x_count, write, d_rule_cnt, d_rule_off, o_itemset,
-                               o_ante, o_sup, o_conf, o_lift, d_missing);
-  KMLS_LAUNCHED("k_rules");
-  return 0;
+extern "C" int64_t kmls_rules_parts_per_itemset(int32_t k) {
+  return k >= 2 && k <= kMaxRuleK ? ((int64_t)1 << (k - 1)) - 1 : -1;
 }
 
 extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
-                                const int64_t* level_sizes, int32_t max_k, const uint64_t* d_keys,
-                                const int32_t* d_vals, int64_t capacity, int64_t n_playlists_total,
-                                double min_confidence, int64_t x_begin, int64_t x_count,
-                                int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream) {
-  return launch_rules(d_items, d_counts, level_sizes, max_k, d_keys, d_vals, capacity,
-                      n_playlists_total, min_confidence, x_begin, x_count, 0, d_rule_cnt, nullptr,
-                      nullptr, nullptr, nullptr, nullptr, nullptr, d_missing, (cudaStream_t)stream);
+                                const int64_t* level_sizes, int32_t max_k, int32_t k,
+                                int64_t lvl_begin, int64_t lvl_count, const void* d_slots,
+                                int64_t capacity, int64_t n_playlists_total, double min_confidence,
+                                void* d_part, int32_t* d_rule_cnt, int32_t* d_missing,
+                                kmls_stream_t stream) {
+  Arena a;
+  int rc = make_arena(a, d_items, d_counts, nullptr, level_sizes, max_k);
+  if (rc) return rc;
+  KMLS_REQUIRE(k >= 2 && k <= max_k, "kmls_rules_count: level out of range");
+  KMLS_REQUIRE(k <= kMaxRuleK, "kmls_rules_count: itemsets of more than 15 members are not supported");
+  KMLS_REQUIRE(n_playlists_total > 0, "kmls_rules_count: n_playlists_total must be positive");
+  KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
+               "kmls_rules_count: itemset range out of bounds");
+  if (lvl_count == 0) return 0;
+  KMLS_REQUIRE(d_slots && capacity > 0 && (capacity & (capacity - 1)) == 0 && d_part && d_rule_cnt && d_missing,
+               "kmls_rules_count: bad index or null pointer");
+  const size_t per_warp = sizeof(int32_t) * 2 * ((size_t)1 << (k - 1));
+  int warps = (int)std::min<size_t>(8, (200 * 1024) / per_warp);
+  KMLS_REQUIRE(warps >= 1, "kmls_rules_count: subset table does not fit in shared memory");
+  const size_t smem = per_warp * warps;
+  KMLS_CUDA(cudaFuncSetAttribute(k_rules_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  int grid = (int)std::min<int64_t>((lvl_count + warps - 1) / warps, (int64_t)num_sms() * 32);
+  k_rules_count<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(
+      a, k, lvl_begin, lvl_count, (const uint4*)d_slots, (uint64_t)capacity - 1,
+      (double)n_playlists_total, min_confidence, (int2*)d_part, d_rule_cnt, d_missing);
+  KMLS_LAUNCHED("k_rules_count");
+  return 0;
 }
 
-extern "C" int kmls_rules_write(const int32_t* d_items, const int32_t* d_counts,
-                                const int64_t* level_sizes, int32_t max_k, const uint64_t* d_keys,
-                                const int32_t* d_vals, int64_t capacity, int64_t n_playlists_total,
-                                double min_confidence, int64_t x_begin, int64_t x_count,
-                                const int64_t* d_rule_off, int32_t* d_out_itemset,
-                                uint32_t* d_out_antecedent, double* d_out_support,
-                                double* d_out_confidence, double* d_out_lift, int32_t* d_missing,
+extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
+                                int32_t k, int64_t lvl_begin, int64_t lvl_count,
+                                int64_t n_playlists_total, double min_confidence,
+                                const void* d_part, const int64_t* d_rule_off,
+                                int32_t* d_out_itemset, uint32_t* d_out_antecedent,
+                                double* d_out_support, double* d_out_confidence, double* d_out_lift,
                                 kmls_stream_t stream) {
-  return launch_rules(d_items, d_counts, level_sizes, max_k, d_keys, d_vals, capacity,
-                      n_playlists_total, min_confidence, x_begin, x_count, 1, nullptr, d_rule_off,
-                      d_out_itemset, d_out_antecedent, d_out_support, d_out_confidence, d_out_lift,
-                      d_missing, (cudaStream_t)stream);
+  Arena a;
+  int rc = make_arena(a, nullptr, d_counts, nullptr, level_sizes, max_k);
+  if (rc) return rc;
+  KMLS_REQUIRE(k >= 2 && k <= max_k && k <= kMaxRuleK, "kmls_rules_write: level out of range");
+  KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
+               "kmls_rules_write: itemset range out of bounds");
+  if (lvl_count == 0) return 0;
+  KMLS_REQUIRE(d_part && d_rule_off && d_out_itemset && d_out_antecedent && d_out_support &&
+                   d_out_confidence && d_out_lift, "kmls_rules_write: null pointer");
+  int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
+  k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int2*)d_part,
+      d_rule_off, d_out_itemset, d_out_antecedent, d_out_support, d_out_confidence, d_out_lift);
+  KMLS_LAUNCHED("k_rules_write");
+  return 0;
 }

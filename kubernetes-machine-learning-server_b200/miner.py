@@ -61,6 +61,8 @@ class MineResult:
     levels: List[Tuple[torch.Tensor, torch.Tensor]]
     pair_counts: Optional[torch.Tensor] = None    # int32[F1, F1]
     stats: Optional[dict] = None
+    # parents[k-2][i] = index, in level k-1, of level-k itemset i without its last member
+    parents: Optional[List[torch.Tensor]] = None
 
     @property
     def n_itemsets(self) -> int:
@@ -156,8 +158,10 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     stats = {"levels": [], "t1": t1, "tk": tk, "n_playlists": n_total, "nnz_local": nnz}
     empty_i32 = dev.empty(0, torch.int32)
 
+    parents: List[torch.Tensor] = []
+
     def result(row_items, levels, pair=None):
-        return MineResult(n_total, t1, tk, row_items, levels, pair, stats)
+        return MineResult(n_total, t1, tk, row_items, levels, pair, stats, parents)
 
     if n_total == 0 or n_items == 0:
         return result(empty_i32, [])
@@ -235,6 +239,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     counts_k = dev.empty(n2, torch.int32)
     _lib.call("kmls_pair_select", pair, n_rows, thr, n2, row_off, items_k, counts_k, s)
     levels.append((items_k.view(n2, 2), counts_k))
+    parents.append(items_k.view(n2, 2)[:, 0].contiguous())
     total = n_rows + n2
     projected = count_impl == "projected"
     more = (max_len is None or 2 < max_len) and n2 >= 2
@@ -322,20 +327,19 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
                 "raise the guard or min_support (results are never truncated)")
         items_n = dev.empty(n_next * (k + 1), torch.int32)
         counts_n = dev.empty(n_next, torch.int32)
+        cnt_loc_n = dev.empty(n_next, torch.int32)
+        par_p = dev.empty(n_next, torch.int32)
+        par_q = dev.empty(n_next, torch.int32)
+        _lib.call("kmls_emit_level_px", items_k, k, cand_p, cand_q, cand_cnt,
+                  cand_cnt_local if projected else cand_cnt, n_cand, thr, out_off, items_n,
+                  counts_n, cnt_loc_n, par_p, par_q, s)
+        parents.append(par_p)
         if projected:
-            cnt_loc_n = dev.empty(n_next, torch.int32)
-            par_p = dev.empty(n_next, torch.int32)
-            par_q = dev.empty(n_next, torch.int32)
-            _lib.call("kmls_emit_level_px", items_k, k, cand_p, cand_q, cand_cnt, cand_cnt_local,
-                      n_cand, thr, out_off, items_n, counts_n, cnt_loc_n, par_p, par_q, s)
             if (max_len is None or k + 1 < max_len) and n_next >= 2:
                 arena_k, rowptr_k, roww_k, words = project(arena_k, rowptr_k, roww_k, par_p, par_q,
                                                            cnt_loc_k, n_next)
                 stats["levels"][-1]["row_words_total"] = words
             cnt_loc_k = cnt_loc_n
-        else:
-            _lib.call("kmls_emit_level", items_k, k, cand_p, cand_q, cand_cnt, n_cand, thr, out_off,
-                      items_n, counts_n, s)
         k += 1
         items_k, counts_k = items_n, counts_n
         levels.append((items_k.view(n_next, k), counts_k))
@@ -381,19 +385,32 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
         return RuleTable(e_i32, e_i32, e_f64, e_f64, e_f64, arena, sizes.tolist())
     arena_items = torch.cat([it.reshape(-1) for it, _ in res.levels])
     arena_counts = torch.cat([ct for _, ct in res.levels])
-    cap = int(_lib.value("kmls_set_capacity", n_all))
-    keys = dev.empty(cap, torch.int64)
-    vals = dev.empty(cap, torch.int32)
-    sizes_ptr = sizes.ctypes.data
-    _lib.call("kmls_itemset_map_build", arena_items, arena_counts, sizes_ptr, max_k, keys, vals,
-              cap, s)
+    arena_par = torch.cat(res.parents)
     n_x_all = n_all - int(sizes[1])
+    cap = int(_lib.value("kmls_set_capacity", n_x_all))
+    slots = dev.empty(cap * 2, torch.int64)
+    sizes_ptr = sizes.ctypes.data
+    _lib.call("kmls_trie_index_build", arena_items, arena_counts, arena_par, sizes_ptr, max_k,
+              slots, cap, s)
     x_begin = (n_x_all * part[0]) // part[1]
-    n_x = (n_x_all * (part[0] + 1)) // part[1] - x_begin
+    x_end = (n_x_all * (part[0] + 1)) // part[1]
+    n_x = x_end - x_begin
     rule_cnt = dev.empty(n_x, torch.int32)
     missing = torch.zeros(1, dtype=torch.int32, device=device)
-    _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
-              res.n_playlists, float(min_confidence), x_begin, n_x, rule_cnt, missing, s)
+    # per level: the slice of this part that falls into the level
+    plan, lvl_start = [], 0
+    for k in range(2, max_k + 1):
+        lo, hi = max(x_begin, lvl_start), min(x_end, lvl_start + int(sizes[k]))
+        if hi > lo:
+            ppi = int(_lib.value("kmls_rules_parts_per_itemset", k))
+            if ppi < 0:
+                raise _lib.KmlsError(f"rule generation supports itemsets of at most 15 members, got {k}")
+            plan.append((k, lo - lvl_start, hi - lo, lo - x_begin, dev.empty((hi - lo) * ppi, torch.int64)))
+        lvl_start += int(sizes[k])
+    for k, lvl_begin, cnt, out0, part_buf in plan:
+        _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
+                  slots, cap, res.n_playlists, float(min_confidence), part_buf, rule_cnt[out0:],
+                  missing, s)
     scratch, sbytes = dev.scan_scratch(n_x)
     rule_off = dev.empty(n_x + 1, torch.int64)
     _lib.call("kmls_exclusive_scan_i32", rule_cnt, n_x, rule_off, scratch, sbytes, s)
@@ -409,9 +426,10 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     o_conf = dev.empty(n_rules, torch.float64)
     o_lift = dev.empty(n_rules, torch.float64)
     if n_rules:
-        _lib.call("kmls_rules_write", arena_items, arena_counts, sizes_ptr, max_k, keys, vals, cap,
-                  res.n_playlists, float(min_confidence), x_begin, n_x, rule_off, o_set, o_ante,
-                  o_sup, o_conf, o_lift, missing, s)
+        for k, lvl_begin, cnt, out0, part_buf in plan:
+            _lib.call("kmls_rules_write", arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
+                      res.n_playlists, float(min_confidence), part_buf, rule_off[out0:], o_set,
+                      o_ante, o_sup, o_conf, o_lift, s)
     return RuleTable(o_set, o_ante, o_sup, o_conf, o_lift, arena_items, sizes.tolist())
 
 
