@@ -88,6 +88,18 @@ size_t kmls_scan_scratch_bytes(int64_t n);
 int kmls_exclusive_scan_i32(const int32_t* d_in, int64_t n, int64_t* d_out, void* d_scratch,
                             size_t scratch_bytes, kmls_stream_t stream);
 
+/* No counterpart in the reference. Same result as kmls_exclusive_scan_i32 for callers that
+ * cannot supply scratch because they cannot allocate device memory (they only hold buffers
+ * handed to them: a plugin inside a pre-budgeted CUDA context, a loop that must avoid the
+ * device-wide stall of cudaMalloc/cudaFree, an FFI caller without a device allocator). The
+ * scratch is a 1 MiB array inside the library image (held on every GPU that loads the
+ * library until exit); n <= KMLS_NOALLOC_SCAN_MAX_N or the call fails with an error. The
+ * first call on a device resolves the array's address: issue it before any stream capture.
+ * Calls share the array, so calls that overlap on the GPU race - keep them on one stream. */
+#define KMLS_NOALLOC_SCAN_MAX_N 4194304
+int kmls_exclusive_scan_i32_noalloc(const int32_t* d_in, int64_t n, int64_t* d_out,
+                                    kmls_stream_t stream);
+
 /* Fingerprint set of a level table d_items[n][k] (used for Apriori pruning). */
 int64_t kmls_set_capacity(int64_t n);
 int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t k, uint64_t* d_slots,

@@ -29,6 +29,7 @@ SIGNATURES = {
     "kmls_supports_f64": (ctypes.c_int, [_P, _I64, _I64, _P, _P]),
     "kmls_scan_scratch_bytes": (_SZ, [_I64]),
     "kmls_exclusive_scan_i32": (ctypes.c_int, [_P, _I64, _P, _P, _SZ, _P]),
+    "kmls_exclusive_scan_i32_noalloc": (ctypes.c_int, [_P, _I64, _P, _P]),
     "kmls_set_capacity": (_I64, [_I64]),
     "kmls_itemset_set_build": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P]),
     "kmls_join_count": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _SZ, _P]),
@@ -78,6 +79,7 @@ def load() -> ctypes.CDLL:
 KERNELS_PER_CALL = {
     "kmls_item_histogram": 1, "kmls_encode_bitmap": 1, "kmls_row_popcount": 1, "kmls_gather_rows": 1,
     "kmls_pair_counts": 1, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
+    "kmls_exclusive_scan_i32_noalloc": 3,
     "kmls_itemset_set_build": 1, "kmls_join_count": 4, "kmls_join_write": 4, "kmls_count_candidates": 1,
     "kmls_emit_count": 3, "kmls_emit_level": 1, "kmls_trie_index_build": 1, "kmls_rules_count": 1,
     "kmls_rules_write": 1, "kmls_count_pairs": 1, "kmls_emit_level_px": 1, "kmls_row_alloc": 1,

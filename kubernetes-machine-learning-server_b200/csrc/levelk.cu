@@ -376,3 +376,58 @@ extern "C" int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t*
   KMLS_LAUNCHED("k_emit_level");
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------
+// kmls_exclusive_scan_i32_noalloc: the 64-bit exclusive scan above for callers that have no
+// way to hand over a scratch buffer.
+//
+// Who that is: code that only ever holds the input and output buffers somebody else gave
+// it. Typical cases are a plugin running inside another program's CUDA context whose device
+// memory was budgeted and carved up at start-up, a service loop that must not call
+// cudaMalloc/cudaFree because those calls serialise the whole device and would stall its
+// other streams, and a binding from a language that has a pointer to data but no device
+// allocator behind it. kmls_exclusive_scan_i32 needs kmls_scan_scratch_bytes(n) bytes of
+// scratch from such a caller; this variant brings its own.
+//
+// The scratch is the file-scope array below: it is part of the library image, so every GPU
+// that loads the library sets aside kNoAllocScratchBytes (1 MiB) of device memory until the
+// process exits, whether or not this entry point is ever called. The first call on a
+// device looks up the array's device address (cudaGetSymbolAddress - the array's name in
+// host code is not a device pointer) and caches it for that device; make that first call
+// outside any stream capture. Nothing is allocated or freed, here or in CUB.
+//
+// Limits and sharing: n <= KMLS_NOALLOC_SCAN_MAX_N (4,194,304) - larger inputs are refused
+// with an error, never truncated. All calls on a device use the same array. It keeps
+// whatever the previous call left in it; that is harmless because the scan's own init
+// kernel resets every tile state it reads before the scan kernel runs. Two calls that
+// overlap on the GPU (different streams, or different host threads) would race on the
+// array: serialise them on one stream.
+// ---------------------------------------------------------------------------------------
+namespace kmls {
+constexpr size_t kNoAllocScratchBytes = 1u << 20;
+static __device__ __align__(256) unsigned char g_noalloc_scan_scratch[kNoAllocScratchBytes];
+}  // namespace kmls
+
+extern "C" int kmls_exclusive_scan_i32_noalloc(const int32_t* d_in, int64_t n, int64_t* d_out,
+                                               kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && d_out, "kmls_exclusive_scan_i32_noalloc: bad arguments");
+  if (n > KMLS_NOALLOC_SCAN_MAX_N)
+    return fail(kCapacityError,
+                "kmls_exclusive_scan_i32_noalloc: n = %lld exceeds the built-in scratch limit of %d "
+                "elements; use kmls_exclusive_scan_i32 with caller scratch",
+                (long long)n, KMLS_NOALLOC_SCAN_MAX_N);
+  KMLS_REQUIRE(n == 0 || d_in, "kmls_exclusive_scan_i32_noalloc: d_in is null");
+  // device address of the array, looked up once per device with that device current
+  constexpr int kMaxDevices = 64;
+  static void* scratch_of_device[kMaxDevices] = {nullptr};
+  int dev = -1;
+  KMLS_CUDA(cudaGetDevice(&dev));
+  KMLS_REQUIRE(dev >= 0 && dev < kMaxDevices, "kmls_exclusive_scan_i32_noalloc: device index out of range");
+  void* scratch = scratch_of_device[dev];
+  if (scratch == nullptr) {
+    KMLS_CUDA(cudaGetSymbolAddress(&scratch, g_noalloc_scan_scratch));
+    KMLS_REQUIRE(scratch != nullptr, "kmls_exclusive_scan_i32_noalloc: no device address for the scratch array");
+    scratch_of_device[dev] = scratch;
+  }
+  return scan_i32(d_in, n, d_out, scratch, kNoAllocScratchBytes, ToI64(), (cudaStream_t)stream);
+}
