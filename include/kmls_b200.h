@@ -69,6 +69,16 @@ int kmls_gather_rows(const uint32_t* d_src, const int32_t* d_src_row, int32_t n_
 int kmls_pair_counts(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
                      int32_t* d_pair, kmls_stream_t stream);
 
+/* The same contraction on the tensor cores (tcgen05.mma kind::i8, int32 accumulators in
+ * TMEM, bit slices fetched by TMA and expanded to int8 inside the SM). Only entries with
+ * j >= i (upper triangle, diagonal included) are guaranteed to be written. d_scratch:
+ * kmls_pair_gemm_scratch_bytes() bytes, 16-byte aligned (holds a K-block-major copy of the
+ * bitmap). */
+size_t kmls_pair_gemm_scratch_bytes(int32_t n_rows, int64_t row_words);
+int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                        int32_t* d_pair, void* d_scratch, size_t scratch_bytes,
+                        kmls_stream_t stream);
+
 /* Frequent-pair table: all (a, b), a < b, with d_pair[a][b] >= thr, sorted by (a, b).
  * d_row_off[n_rows+1] receives the exclusive scan of per-row counts (d_row_off[n_rows] =
  * number of pairs). With capacity == 0 only d_row_off is produced (sizing pass); otherwise

@@ -25,6 +25,8 @@ SIGNATURES = {
     "kmls_row_popcount": (ctypes.c_int, [_P, _I32, _I64, _P, _P]),
     "kmls_gather_rows": (ctypes.c_int, [_P, _P, _I32, _I64, _P, _P]),
     "kmls_pair_counts": (ctypes.c_int, [_P, _I32, _I64, _P, _P]),
+    "kmls_pair_gemm_scratch_bytes": (_SZ, [_I32, _I64]),
+    "kmls_pair_counts_i8": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _SZ, _P]),
     "kmls_pair_select": (ctypes.c_int, [_P, _I32, _I32, _I64, _P, _P, _P, _P]),
     "kmls_supports_f64": (ctypes.c_int, [_P, _I64, _I64, _P, _P]),
     "kmls_scan_scratch_bytes": (_SZ, [_I64]),
@@ -78,7 +80,7 @@ def load() -> ctypes.CDLL:
 # and selections count as the kernels they launch from inside this library).
 KERNELS_PER_CALL = {
     "kmls_item_histogram": 1, "kmls_encode_bitmap": 1, "kmls_row_popcount": 1, "kmls_gather_rows": 1,
-    "kmls_pair_counts": 1, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
+    "kmls_pair_counts": 1, "kmls_pair_counts_i8": 2, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
     "kmls_exclusive_scan_i32_noalloc": 3,
     "kmls_itemset_set_build": 1, "kmls_join_count": 4, "kmls_join_write": 4, "kmls_count_candidates": 1,
     "kmls_emit_count": 3, "kmls_emit_level": 1, "kmls_trie_index_build": 1, "kmls_rules_count": 1,

@@ -212,9 +212,16 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     counts1_local = counts1_local_box[0]
     pair = dev.empty(n_rows * n_rows, torch.int32)
     if pair_impl == "auto":
-        pair_impl = "popc"
+        # tensor cores once there are enough 128x256 tiles and playlists to feed them
+        pair_impl = "i8" if (n_rows >= 256 and row_words >= 512) else "popc"
     if pair_impl == "popc":
         _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
+    elif pair_impl == "i8":
+        gbytes = int(_lib.value("kmls_pair_gemm_scratch_bytes", n_rows, row_words))
+        gscratch = dev.empty((gbytes + 7) // 8, torch.int64)
+        _lib.call("kmls_pair_counts_i8", bitmap, n_rows, row_words, pair, gscratch, gbytes, s,
+                  algo_bytes=n_rows * (n_rows + 1) * n_local)   # = int8 ops: 2 * N * F(F+1)/2
+        del gscratch
     else:
         raise ValueError(f"unknown pair_impl {pair_impl!r}")
     pair_local = pair.clone() if group is not None else pair

@@ -134,6 +134,26 @@ def test_pair_counts_and_select(rows, n):
         assert sup.cpu().numpy().tolist() == [int(c) / n for c in want[ii, jj]]
 
 
+@pytest.mark.parametrize("rows,n", [(64, 256), (129, 3000), (300, 70000), (1000, 200000), (257, 1024)])
+def test_pair_counts_tensor_core_matches_cuda_core(rows, n):
+    """tcgen05 int8 GEMM vs the AND+popc kernel: bit-equal on the upper triangle."""
+    rng = np.random.default_rng(rows + n)
+    W = int(_lib.value("kmls_bitmap_row_words", n))
+    dense = rng.random((rows, n)) < rng.uniform(0.01, 0.7, (rows, 1))
+    full = np.zeros((rows, W * 32), bool)
+    full[:, :n] = dense
+    bm = torch.from_numpy(np.packbits(full, axis=1, bitorder="little").view(np.int32).reshape(rows, W)).to(dev())
+    ref = torch.empty(rows * rows, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts", bm, rows, W, ref, stream())
+    got = torch.full((rows * rows,), -5, dtype=torch.int32, device=dev())
+    sb = int(_lib.value("kmls_pair_gemm_scratch_bytes", rows, W))
+    scratch = torch.empty(sb // 8 + 1, dtype=torch.int64, device=dev())
+    _lib.call("kmls_pair_counts_i8", bm, rows, W, got, scratch, sb, stream())
+    torch.cuda.synchronize()
+    iu = torch.triu(torch.ones(rows, rows, dtype=torch.bool, device=dev()))
+    assert torch.equal(got.view(rows, rows)[iu], ref.view(rows, rows)[iu])
+
+
 def test_exclusive_scan():
     rng = np.random.default_rng(2)
     for n in [0, 1, 31, 1025, 3_000_001]:
