@@ -190,7 +190,9 @@ def run_gpu(args):
         torch.cuda.synchronize()
 
     def step(o, i):
-        res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group)
+        res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group,
+                             prune=False if args.no_prune else None, pair_impl=args.pair_impl,
+                             count_impl=args.count_impl)
         rules = miner.generate_rules(res, conf, part=(rank, world))
         return res, rules
 
@@ -237,6 +239,11 @@ def run_gpu(args):
         d["calls"] += 1
         d["bytes"] += nbytes or 0
     top = max(per, key=lambda k: per[k]["ms"]) if per else None
+    if args.trace and rank == 0:
+        per_step = len(trace) // args.steps
+        for nm, a, b, nbytes in trace[-per_step:]:
+            log(f"[trace] {nm:28s} {a.elapsed_time(b):9.3f} ms  bytes={nbytes}")
+        log("[trace] level stats: " + json.dumps(info.get("stats", {}).get("levels", [])))
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -258,18 +265,29 @@ def run_gpu(args):
                         "re-read from L2, so this can exceed the HBM copy peak"}
 
     # ---- e2e: pinned host CSR in, tables back on the host ---------------------------------
+    pinned = {}
+
+    def to_host(i, t):
+        key = (i, t.dtype)
+        if key not in pinned or pinned[key].numel() < t.numel():
+            pinned[key] = torch.empty(max(t.numel(), 1), dtype=t.dtype).pin_memory()
+        dst = pinned[key][:t.numel()]
+        dst.copy_(t.reshape(-1), non_blocking=True)
+        return dst
+
     def e2e_step():
         o = h_off.to(device, non_blocking=True)
         i = h_items.to(device, non_blocking=True)
         res, rules = step(o, i)
-        outs = [res.row_items.cpu()]
-        for it, ct in res.levels:
-            outs.append(it.cpu())
-            outs.append(ct.cpu())
-        nr = rules.n_rules
+        outs = [to_host(0, res.row_items)]
+        for lv, (it, ct) in enumerate(res.levels):
+            outs.append(to_host(2 * lv + 1, it))
+            outs.append(to_host(2 * lv + 2, ct))
+        torch.cuda.synchronize()
         d2h = sum(x.numel() * x.element_size() for x in outs)
-        return d2h, nr
+        return d2h, rules.n_rules
 
+    e2e_step()   # untimed: sizes the pinned result buffers
     barrier()
     t0 = time.perf_counter()
     d2h = 0
@@ -326,6 +344,10 @@ def main():
     ap.add_argument("--impl", default="kmls_b200", choices=["kmls_b200", "reference"])
     ap.add_argument("--workload", default="zipf_1Mx100k_s0.001", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--trace", action="store_true", help="print every library call of the last timed step")
+    ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
+    ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc"])
+    ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -179,6 +179,20 @@ int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
                       int64_t n, uint32_t* d_arena_new, const int64_t* d_rowptr_new,
                       const int32_t* d_roww_new, kmls_stream_t stream);
 
+/* First projection (level 1 -> 2), where the masks are sparse single-track rows:
+ * kmls_row_tidlists turns every bitmap row r into the ascending list of its set columns at
+ * d_tids[d_tid_off[r] .. d_tid_off[r+1]) (d_tid_off = exclusive scan of the local row
+ * counts); kmls_project_rows_gather then builds row(a, b) by sampling bitmap row b at the
+ * columns of a (total_words = d_rowptr_new[n], the size of the new arena). Same output as
+ * kmls_project_rows on the full bitmap. */
+int kmls_row_tidlists(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                      const int64_t* d_tid_off, int32_t* d_tids, kmls_stream_t stream);
+int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_words, const int32_t* d_par_p,
+                             const int32_t* d_par_q, int64_t n, const int32_t* d_tids,
+                             const int64_t* d_tid_off, uint32_t* d_arena_new,
+                             const int64_t* d_rowptr_new, int64_t total_words,
+                             kmls_stream_t stream);
+
 /* ---- rules (mlxtend association_rules semantics; the dormant path main.py:224-260 is the
  *      only reference site of a min_confidence knob) -------------------------------------- */
 

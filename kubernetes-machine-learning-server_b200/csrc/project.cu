@@ -168,6 +168,109 @@ k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// First projection (level 1 -> level 2) by gathering. The masks there are the single-track
+// rows, on average a few percent dense, so scanning all N/32 mask words per new row wastes
+// almost all of the work. Instead each kept track's row is turned ONCE into the ascending
+// list of the playlists that contain it (k_row_tidlists); a new row (a, b) is then
+// row_b sampled at those positions: one gathered load + one ballot per 32 output bits.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_row_tidlists(const uint32_t* __restrict__ bitmap, int64_t row_words,
+               const int64_t* __restrict__ tid_off, int32_t* __restrict__ tids) {
+  __shared__ int warp_tot[8];
+  __shared__ int carry;
+  const uint32_t* row = bitmap + (int64_t)blockIdx.x * row_words;
+  int32_t* out = tids + tid_off[blockIdx.x];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int64_t w0 = 0; w0 < row_words; w0 += 256) {
+    const int64_t w = w0 + threadIdx.x;
+    uint32_t m = w < row_words ? __ldg(row + w) : 0u;
+    const int nb = __popc(m);
+    int incl = nb;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int u = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += u;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    int pos = carry + incl - nb;
+    for (int i = 0; i < warp; ++i) pos += warp_tot[i];
+    const int32_t colbase = (int32_t)(w << 5);
+    while (m) {
+      const int b = __ffs(m) - 1;
+      out[pos++] = colbase + b;
+      m &= m - 1;
+    }
+    __syncthreads();
+    if (threadIdx.x == 255) carry = pos;   // thread 255 ends at the block's total
+    __syncthreads();
+  }
+}
+
+// Work unit = 64 consecutive words of the new arena (rows are 4-word multiples, so a group
+// of 4 words never straddles two rows): every warp does the same amount of work no matter
+// how long the rows are, and 4 independent gathers are in flight per lane.
+__global__ void __launch_bounds__(256)
+k_project_gather(const uint32_t* __restrict__ bitmap, int64_t row_words,
+                 const int32_t* __restrict__ par_p, const int32_t* __restrict__ par_q, int64_t n,
+                 const int32_t* __restrict__ tids, const int64_t* __restrict__ tid_off,
+                 uint32_t* __restrict__ arena_new, const int64_t* __restrict__ rowptr_new,
+                 int64_t total_words) {
+  const int lane = threadIdx.x & 31;
+  const int64_t n_blocks = (total_words + 63) >> 6;
+  for (int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); blk < n_blocks;
+       blk += (int64_t)gridDim.x * 8) {
+    const int64_t g0 = blk << 6;
+    // first row o with rowptr[o + 1] > g0 (rows without storage are skipped by construction)
+    int64_t lo = 0, hi = n - 1;
+    while (lo < hi) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(rowptr_new + mid + 1) > g0) hi = mid; else lo = mid + 1;
+    }
+    int64_t o = lo, rbeg = __ldg(rowptr_new + o), rend = __ldg(rowptr_new + o + 1);
+    bool fresh = true;
+    const int32_t* tl = nullptr;
+    const uint32_t* src = nullptr;
+    int c = 0;
+#pragma unroll 1
+    for (int half = 0; half < 2; ++half) {
+      uint32_t mine = 0;
+      for (int i = 0; i < 32; i += 4) {
+        const int64_t g = g0 + half * 32 + i;
+        if (g >= total_words) break;
+        while (g >= rend) { ++o; rbeg = rend; rend = __ldg(rowptr_new + o + 1); fresh = true; }
+        if (fresh) {
+          const int32_t a = __ldg(par_p + o), b = __ldg(par_q + o);
+          const int64_t t_begin = __ldg(tid_off + a);
+          c = (int)(__ldg(tid_off + a + 1) - t_begin);
+          tl = tids + t_begin;
+          src = bitmap + (int64_t)b * row_words;
+          fresh = false;
+        }
+        const int t0 = (int)(g - rbeg) * 32 + lane;
+        int32_t pos[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) pos[j] = (t0 + 32 * j) < c ? __ldg(tl + t0 + 32 * j) : -1;
+        uint32_t bit[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          bit[j] = pos[j] >= 0 ? (__ldg(src + (pos[j] >> 5)) >> (pos[j] & 31)) & 1u : 0u;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t word = __ballot_sync(0xffffffffu, bit[j] != 0);
+          if (lane == i + j) mine = word;
+        }
+      }
+      const int64_t gw = g0 + half * 32 + lane;
+      if (gw < total_words) arena_new[gw] = mine;
+    }
+  }
+}
+
 }  // namespace kmls
 
 using namespace kmls;
@@ -237,5 +340,36 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
                                                          d_par_p, d_par_q, n, d_arena_new,
                                                          d_rowptr_new, d_roww_new);
   KMLS_LAUNCHED("k_project_rows");
+  return 0;
+}
+
+
+extern "C" int kmls_row_tidlists(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                                 const int64_t* d_tid_off, int32_t* d_tids, kmls_stream_t stream) {
+  using namespace kmls;
+  KMLS_REQUIRE(n_rows >= 0 && row_words >= 0, "kmls_row_tidlists: negative size");
+  if (n_rows == 0) return 0;
+  KMLS_REQUIRE(d_bitmap && d_tid_off && d_tids, "kmls_row_tidlists: null pointer");
+  k_row_tidlists<<<n_rows, 256, 0, (cudaStream_t)stream>>>(d_bitmap, row_words, d_tid_off, d_tids);
+  KMLS_LAUNCHED("k_row_tidlists");
+  return 0;
+}
+
+extern "C" int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_words,
+                                        const int32_t* d_par_p, const int32_t* d_par_q, int64_t n,
+                                        const int32_t* d_tids, const int64_t* d_tid_off,
+                                        uint32_t* d_arena_new, const int64_t* d_rowptr_new,
+                                        int64_t total_words, kmls_stream_t stream) {
+  using namespace kmls;
+  KMLS_REQUIRE(n >= 0 && total_words >= 0, "kmls_project_rows_gather: negative size");
+  if (n == 0 || total_words == 0) return 0;
+  KMLS_REQUIRE(d_bitmap && d_par_p && d_par_q && d_tids && d_tid_off && d_rowptr_new && d_arena_new,
+               "kmls_project_rows_gather: null pointer");
+  const int64_t n_blocks = (total_words + 63) / 64;
+  int grid = (int)std::min<int64_t>((n_blocks + 7) / 8, (int64_t)num_sms() * 64);
+  k_project_gather<<<grid, 256, 0, (cudaStream_t)stream>>>(d_bitmap, row_words, d_par_p, d_par_q, n,
+                                                           d_tids, d_tid_off, d_arena_new,
+                                                           d_rowptr_new, total_words);
+  KMLS_LAUNCHED("k_project_gather");
   return 0;
 }

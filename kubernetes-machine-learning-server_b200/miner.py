@@ -130,14 +130,20 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
              n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
              pair_impl: str = "auto", count_impl: str = "projected",
-             prune: bool = True) -> MineResult:
+             prune: Optional[bool] = None, first_projection: str = "gather") -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
     ``n_playlists_total`` is N of the whole job (sum over ranks); it defaults to the local
     count (allreduced when ``group`` is given). ``count_impl``: "projected" counts candidates
     on conditional (column-compacted) bitmaps, "fullwidth" on the full bitmap with the prefix
-    staged in shared memory. ``prune`` switches Apriori pruning of the joins."""
+    staged in shared memory. ``prune`` switches Apriori pruning of the joins (default: on for
+    "fullwidth", where a candidate costs N/8 bytes, off for "projected", where probing the
+    fingerprint set costs more than counting the few extra candidates - with members in
+    ascending-support order the subsets a probe checks drop a RARER member and are almost
+    always frequent). ``first_projection``: "gather" or "pext" for the level 1 -> 2 rows."""
+    if prune is None:
+        prune = count_impl != "projected"
     if min_support <= 0.0:
         thresholds(min_support, 1)  # raises the reference's ValueError
     if not (offsets.is_cuda and items.is_cuda):
@@ -251,8 +257,10 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     projected = count_impl == "projected"
     more = (max_len is None or 2 < max_len) and n2 >= 2
 
-    def project(arena_old, rowptr_old, roww_old, par_p, par_q, parent_cnt_local, n_new):
-        """Rows of a new level from the rows of its parents' level."""
+    def project(arena_old, rowptr_old, roww_old, par_p, par_q, parent_cnt_local, n_new,
+                first=False):
+        """Rows of a new level from the rows of its parents' level (``first``: from the full
+        bitmap, by gathering at the parents' column lists)."""
         roww = dev.empty(n_new, torch.int32)
         _lib.call("kmls_row_alloc", par_p, n_new, parent_cnt_local, roww, s)
         scratch, sbytes = dev.scan_scratch(n_new)
@@ -260,8 +268,18 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         _lib.call("kmls_exclusive_scan_i32", roww, n_new, rowptr, scratch, sbytes, s)
         words = int(rowptr[n_new].item())
         arena = dev.empty(words, torch.int32)
-        _lib.call("kmls_project_rows", arena_old, rowptr_old, roww_old, par_p, par_q, n_new, arena,
-                  rowptr, roww, s, algo_bytes=8 * words)
+        if first and first_projection == "gather":
+            scratch, sbytes = dev.scan_scratch(n_rows)
+            tid_off = dev.empty(n_rows + 1, torch.int64)
+            _lib.call("kmls_exclusive_scan_i32", parent_cnt_local, n_rows, tid_off, scratch, sbytes, s)
+            tids = dev.empty(int(tid_off[n_rows].item()), torch.int32)
+            _lib.call("kmls_row_tidlists", bitmap, n_rows, row_words, tid_off, tids, s,
+                      algo_bytes=4 * n_rows * row_words + 4 * int(tids.numel()))
+            _lib.call("kmls_project_rows_gather", bitmap, row_words, par_p, par_q, n_new, tids,
+                      tid_off, arena, rowptr, words, s, algo_bytes=4 * words)
+        else:
+            _lib.call("kmls_project_rows", arena_old, rowptr_old, roww_old, par_p, par_q, n_new,
+                      arena, rowptr, roww, s, algo_bytes=8 * words)
         return arena, rowptr, roww, words
 
     if projected and more:
@@ -274,7 +292,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         else:
             cnt_loc_k = counts_k
         arena_k, rowptr_k, roww_k, words = project(bitmap, rowptr1, roww1, par_p, par_q,
-                                                   counts1_local, n2)
+                                                   counts1_local, n2, first=True)
         stats["levels"][-1]["row_words_total"] = words
 
     # ---- levels k >= 3 -------------------------------------------------------------------

@@ -222,12 +222,14 @@ def test_project_rows_and_count_pairs():
     assert cc.cpu().tolist() == want_c
 
 
-@pytest.mark.parametrize("count_impl,prune", [("projected", True), ("projected", False),
-                                              ("fullwidth", True), ("fullwidth", False)])
-def test_counting_variants_agree(count_impl, prune):
+@pytest.mark.parametrize("count_impl,prune,first", [
+    ("projected", True, "gather"), ("projected", False, "gather"), ("projected", False, "pext"),
+    ("fullwidth", True, "gather"), ("fullwidth", False, "gather")])
+def test_counting_variants_agree(count_impl, prune, first):
     off, items = synth.zipf_playlists(9000, 700, mean_draws=30, alpha=0.9, seed=31)
     want = oracle_dict(off, items, 700, 0.012)
-    res, _ = kmls_b200.mine_ids(off, items, 700, 0.012, count_impl=count_impl, prune=prune)
+    res, _ = kmls_b200.mine_ids(off, items, 700, 0.012, count_impl=count_impl, prune=prune,
+                                first_projection=first)
     assert res.as_dict() == want
     assert len(res.levels) >= 5
 
