@@ -417,8 +417,21 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     sizes_ptr = sizes.ctypes.data
     _lib.call("kmls_trie_index_build", arena_items, arena_counts, arena_par, sizes_ptr, max_k,
               slots, cap, s)
-    x_begin = (n_x_all * part[0]) // part[1]
-    x_end = (n_x_all * (part[0] + 1)) // part[1]
+    # slice boundaries by work (2^(k-1) splits per k-itemset), not by itemset count, so
+    # that the ranks of a multi-GPU job get rule tables of similar size
+    def boundary(frac_num, frac_den):
+        weights = [int(sizes[k]) << (k - 1) for k in range(2, max_k + 1)]
+        target = (sum(weights) * frac_num) // frac_den
+        x = 0
+        for k, w in zip(range(2, max_k + 1), weights):
+            if target >= w:
+                target -= w
+                x += int(sizes[k])
+            else:
+                return x + (target >> (k - 1))
+        return x
+    x_begin = boundary(part[0], part[1])
+    x_end = boundary(part[0] + 1, part[1]) if part[0] + 1 < part[1] else n_x_all
     n_x = x_end - x_begin
     rule_cnt = dev.empty(n_x, torch.int32)
     missing = torch.zeros(1, dtype=torch.int32, device=device)
