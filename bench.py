@@ -34,7 +34,12 @@ WORKLOADS = {
     # name: (n_playlists per GPU, n_tracks, mean_draws, alpha, min_support, min_confidence)
     "zipf_1Mx100k_s0.001": (1_000_000, 100_000, 72.0, 1.0, 0.001, 0.04),
     "zipf_200kx20k_s0.004": (200_000, 20_000, 50.0, 1.0, 0.004, 0.04),      # quick check
+    # stand-ins for the reference's own (absent) CSVs, shaped after its report's ds2 log:
+    # (n_playlists, n_names, -, -, MIN_SUPPORT, MIN_CONFIDENCE); generator synth.mpd_standin(seed)
+    "mpd_standin_seed1_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
+    "mpd_standin_seed2_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
 }
+MIN_SUPPORT_OVERRIDE = None
 CPU_SAMPLE_PLAYLISTS = 100_000   # playlists of the CPU baseline's bounded sample
 CPU_RULE_STRIDE = 16             # rules are generated for 1/16 of the itemsets and scaled
 
@@ -46,6 +51,17 @@ def log(*a):
 def make_data(name, shard, n_override=None):
     from kmls_b200 import synth
     n, t, draws, alpha, s, conf = WORKLOADS[name]
+    if MIN_SUPPORT_OVERRIDE is not None:
+        s = MIN_SUPPORT_OVERRIDE
+    if name.startswith("mpd_standin"):
+        import kmls_b200
+        d = synth.mpd_standin(seed=int(name.split("seed")[1].split("_")[0]))
+        playlists = synth.group_by_playlist(d["pid"], d["track_name"])
+        columns, off, ids = kmls_b200.encode_transactions(list(playlists.values()))
+        if n_override:
+            off = off[:n_override + 1]
+            ids = ids[:off[-1]]
+        return off, ids, len(columns), s, conf
     if n_override:
         n = n_override
     cache = os.path.join("/tmp", "kmls_bench_cache")
@@ -63,6 +79,21 @@ def make_data(name, shard, n_override=None):
     except OSError:
         pass
     return off, items, t, s, conf
+
+
+def python_reference_run(name):
+    """The reference-faithful arm for the small stand-ins: the literal Python restatement of
+    mlxtend's TransactionEncoder + fpgrowth driven by the reference's own glue
+    (oracle.mlxtend_restated.calculate_and_save_fp_growth_fast = main.py:262-313), one thread,
+    exactly how the reference job runs it. Returns seconds."""
+    from kmls_b200 import synth
+    from oracle import mlxtend_restated as M
+    d = synth.mpd_standin(seed=int(name.split("seed")[1].split("_")[0]))
+    playlists = synth.group_by_playlist(d["pid"], d["track_name"])
+    s = MIN_SUPPORT_OVERRIDE if MIN_SUPPORT_OVERRIDE is not None else WORKLOADS[name][4]
+    t0 = time.time()
+    recs, data = M.calculate_and_save_fp_growth_fast(playlists, s)
+    return time.time() - t0, len(recs), len(data)
 
 
 class ClockSampler(threading.Thread):
@@ -135,7 +166,13 @@ def run_reference(args):
     name = args.workload
     vals = []
     for i in range(args.warmup + args.steps):
-        r = cpu_sample_run(name, threads)
+        if name.startswith("mpd_standin"):
+            sec, n_keys, n_sets = python_reference_run(name)
+            threads = 1
+            r = {"measured_s": sec, "estimate_full_s": sec,
+                 "sample": "the whole workload, Python restatement of mlxtend in the reference's glue, 1 thread"}
+        else:
+            r = cpu_sample_run(name, threads)
         log(f"[bench/reference] step {i}: measured {r['measured_s']:.1f}s -> estimate {r['estimate_full_s']:.1f}s")
         if i >= args.warmup:
             vals.append(r)
@@ -193,6 +230,8 @@ def run_gpu(args):
         res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group,
                              prune=False if args.no_prune else None, pair_impl=args.pair_impl,
                              count_impl=args.count_impl)
+        if args.no_rules:
+            return res, miner.RuleTable(*[torch.empty(0, device=device)] * 6, [])
         rules = miner.generate_rules(res, conf, part=(rank, world))
         return res, rules
 
@@ -211,7 +250,10 @@ def run_gpu(args):
         log(f"[bench] rank {rank} warmup {i}: {time.time() - t0:.3f}s itemsets={res.n_itemsets} "
             f"rules={rules.n_rules} levels={[int(c.numel()) for _, c in res.levels]}")
         info = {"itemsets": res.n_itemsets, "rules_this_rank": rules.n_rules,
-                "levels": [int(c.numel()) for _, c in res.levels], "stats": res.stats}
+                "levels": [int(c.numel()) for _, c in res.levels], "stats": res.stats,
+                # classes per level (distinct parents), for the rule kernel's probe count
+                "classes": [0, 0] + [int((p[1:] != p[:-1]).sum().item()) + 1 if p.numel() else 0
+                                     for p in (res.parents or [])]}
         del res, rules
 
     # ---- timed region: K steps, inputs resident in HBM ------------------------------------
@@ -251,18 +293,42 @@ def run_gpu(args):
         pass
     peak, peak_src = (peaks["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs") if "hbm_gbs" in peaks else \
         (6650.0, "fallback of B200_PROFILING.md")
-    # the roofline object describes the support-counting kernel (the HBM/L2-bound hot loop);
-    # `kernels` below lists every entry point's share of the step
-    rk = "kmls_count_candidates"
-    roof = None
-    if rk in per and per[rk]["ms"] > 0:
-        ach = per[rk]["bytes"] / (per[rk]["ms"] / 1e3) / 1e9
-        roof = {"kernel": "k_count_candidates", "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                "frac": ach / peak, "traffic": None, "peak_source": peak_src,
-                "avg_launch_ms": per[rk]["ms"] / per[rk]["calls"],
-                "algorithmic_bytes_per_launch": per[rk]["bytes"] / per[rk]["calls"],
-                "note": "algorithmic bytes = (candidates + parents*k) * row_bytes per level; rows are "
-                        "re-read from L2, so this can exceed the HBM copy peak"}
+    # Roofline objects. Algorithmic work per launch:
+    #   k_rules_count  16 B per index probe + 8 B per (itemset, antecedent) split written
+    #   k_rules_write  8 B per split read + 32 B per rule written
+    #   k_pair_gemm_i8 2 * N * F(F+1)/2 int8 ops (upper triangle incl. diagonal)
+    #   others         the bytes the caller annotates (miner.py, algo_bytes=...)
+    int8_peak = 2.0 * peaks.get("bf16_tflops", 1590.0)   # TOP/s: int8 dense = 2x the measured bf16 GEMM peak
+    lv_sizes = info.get("levels", [])
+    classes = info.get("classes", [])
+    splits = sum(n * ((1 << (k - 1)) - 1) for k, n in enumerate(lv_sizes, start=1) if k >= 2)
+    probes = sum(classes[k] * max((1 << (k - 1)) - k, 0) + n * max((1 << (k - 1)) - 2, 0)
+                 for k, n in enumerate(lv_sizes, start=1) if k >= 2 and k < len(classes) + 0)
+    algo = {
+        "kmls_rules_count": (16 * probes + 8 * splits) / max(world, 1),
+        "kmls_rules_write": (8 * splits) / max(world, 1) + 32 * (info.get("rules_this_rank") or 0),
+    }
+
+    def roof_of(nm, kernel, bound):
+        if nm not in per or per[nm]["ms"] <= 0:
+            return None
+        sec = per[nm]["ms"] / 1e3 / args.steps           # all launches of one step
+        work = algo.get(nm, per[nm]["bytes"] / args.steps)
+        if bound == "tensor":
+            ach, pk, unit, src = work / sec / 1e12, int8_peak, "TOP/s", "2 x bf16_tflops of MEASURED_PEAKS.json"
+        else:
+            ach, pk, unit, src = work / sec / 1e9, peak, "GB/s", peak_src
+        return {"kernel": kernel, "bound": bound, "achieved": ach, "peak": pk, "unit": unit,
+                "frac": ach / pk, "traffic": None, "peak_source": src,
+                "launches_per_step": per[nm]["calls"] / args.steps, "ms_per_step": sec * 1e3,
+                "algorithmic_work_per_step": work}
+
+    kernel_of = {"kmls_rules_count": ("k_rules_count", "hbm"), "kmls_rules_write": ("k_rules_write", "hbm"),
+                 "kmls_pair_counts_i8": ("k_pair_gemm_i8", "tensor"), "kmls_project_rows": ("k_project_rows", "hbm"),
+                 "kmls_count_candidates": ("k_count_candidates", "hbm"), "kmls_encode_bitmap": ("k_encode_bitmap", "hbm"),
+                 "kmls_row_popcount": ("k_row_popcount", "hbm"), "kmls_item_histogram": ("k_item_histogram", "hbm")}
+    rooflines = {k: roof_of(k, *v) for k, v in kernel_of.items() if k in per}
+    roof = rooflines.get(top) or next((r for r in rooflines.values() if r), None)
 
     # ---- e2e: pinned host CSR in, tables back on the host ---------------------------------
     pinned = {}
@@ -297,12 +363,38 @@ def run_gpu(args):
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
     h2d = h_off.numel() * 8 + h_items.numel() * 4
 
+    verify = None
+    if args.verify and world == 1:
+        from oracle import fpgrowth_c, mlxtend_restated as M
+        res, rules = step(d_off, d_items)
+        o_, i_, c_ = res.to_host()
+        got = {"levels": [int(c.numel()) for _, c in res.levels], "checksum": fpgrowth_c.itemset_checksum(o_, i_, c_),
+               "n_rules": rules.n_rules}
+        del res, rules
+        t1_, tk_ = M.thresholds(s, n_local)
+        t0 = time.time()
+        ref = fpgrowth_c.fpgrowth(off, items, n_tracks, t1_, tk_, store=True,
+                                  rules_min_confidence=None if args.no_rules else conf)
+        want = {"levels": ref.level_counts[1:len(got["levels"]) + 1].tolist(), "checksum": ref.checksum,
+                "n_rules": 0 if args.no_rules else ref.n_rules}
+        verify = {"ok": got == want, "gpu": {k: str(v) for k, v in got.items()},
+                  "oracle": {k: str(v) for k, v in want.items()}, "oracle_seconds": time.time() - t0,
+                  "oracle_threads": os.cpu_count()}
+        log(f"[bench] verify: {verify}")
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         threads = os.cpu_count() or 1
-        r = cpu_sample_run(name, threads)
-        cpu = {"value": r["estimate_full_s"], "unit": "s", "cores": threads, "kind": "port",
-               "sample": r["sample"], "measured_sample_s": r["measured_s"]}
+        if name.startswith("mpd_standin"):
+            sec, n_keys, n_sets = python_reference_run(name)
+            cpu = {"value": sec, "unit": "s", "cores": 1, "kind": "port",
+                   "sample": "the whole workload: Python restatement of mlxtend inside the reference's own "
+                             f"glue (main.py:262-313), single thread as the reference runs; {n_sets} itemsets, "
+                             f"{n_keys} keys; no rule table (the reference computes none)"}
+        else:
+            r = cpu_sample_run(name, threads)
+            cpu = {"value": r["estimate_full_s"], "unit": "s", "cores": threads, "kind": "port",
+                   "sample": r["sample"], "measured_sample_s": r["measured_s"]}
 
     if rank == 0:
         n, t, draws, alpha, _, _ = WORKLOADS[name]
@@ -313,16 +405,18 @@ def run_gpu(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
             "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u32+f64",
             "data": "synthetic",
-            "config": {"workload": name, "n_playlists_per_gpu": n, "n_tracks": t, "mean_draws": draws,
-                       "zipf_alpha": alpha, "min_support": s, "min_confidence": conf,
+            "config": {"workload": name, "n_playlists_per_gpu": n_local, "n_tracks": n_tracks, "mean_draws": draws,
+                       "zipf_alpha": alpha, "min_support": s, "min_confidence": None if args.no_rules else conf,
                        "parallelism": f"playlist-sharded x{world}, rules split by itemset range",
-                       "l2": "inputs larger than L2 (CSR 0.5 GB, bitmap 0.75 GB per GPU)"},
+                       "l2": ("inputs larger than L2 (CSR 0.5 GB, bitmap 0.75 GB per GPU)" if n_local >= 500_000
+                              else "small workload: inputs fit in L2, launch/latency-bound")},
             "clocks": clocks,
             "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": "host CSR -> device -> mine + rules -> itemset tables back on the host; the "
                             "rule table stays on the device (sharded by rank)"},
             "gpu_launches": launches,
             "roofline": roof,
+            "rooflines": {k: v for k, v in rooflines.items() if v},
             "cpu_baseline": cpu,
             "support_counts_per_s": n_counts / step_s if step_s else None,
             "itemsets": info.get("itemsets"), "rules_rank0": info.get("rules_this_rank"),
@@ -330,6 +424,7 @@ def run_gpu(args):
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
             "top_kernel": top,
+            "verify_full_size": verify,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -345,10 +440,17 @@ def main():
     ap.add_argument("--workload", default="zipf_1Mx100k_s0.001", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--trace", action="store_true", help="print every library call of the last timed step")
+    ap.add_argument("--min-support", type=float, default=None, help="override the workload's min_support (sweeps)")
+    ap.add_argument("--no-rules", action="store_true", help="mine only (sweeps at supports whose rule table explodes)")
+    ap.add_argument("--verify", action="store_true",
+                    help="after the run, mine the FULL workload with the CPU oracle (minutes) and compare level "
+                         "sizes, the itemset checksum and the number of rules")
     ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
     ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc"])
     ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])
     args = ap.parse_args()
+    global MIN_SUPPORT_OVERRIDE
+    MIN_SUPPORT_OVERRIDE = args.min_support
     if args.impl == "reference":
         run_reference(args)
     else:

@@ -206,18 +206,35 @@ k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_p
       mbar_wait(op_empty(s), ph ^ 1u);
       const uint8_t* bits = gen_base + (bit_base - base) + s * kGBitBytes;
       uint8_t* ops = gen_base + s * kGOpBytes;
-#pragma unroll 4
-      for (int it = 0; it < (kGM + kGN) * 8 / (kGExpanderWarps * 32); ++it) {
-        const int idx = it * (kGExpanderWarps * 32) + et;
-        const int j = (idx >> 3) & 7;
-        const int r = (idx & 7) + 8 * (idx >> 6);
-        const uint32_t h = *reinterpret_cast<const uint16_t*>(bits + r * 16 + j * 2);
-        uint4 v;
-        v.x = ((h & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.y = (((h >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.z = (((h >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
-        v.w = (((h >> 12) & 0xFu) * 0x00204081u) & 0x01010101u;
-        *reinterpret_cast<uint4*>(ops + r * kGKBytes + ((j ^ (r & 7)) << 4)) = v;
+      // unit = (row, half): 64 bits in, four 16-byte chunks out. All loads first (so that no
+      // store sits between them and they overlap), then pure ALU + 128-bit stores. Lanes 0-7
+      // of a store hit 8 consecutive rows with the same logical chunk: the XOR swizzle puts
+      // them in 8 different 16-byte bank groups (conflict-free); the 64-bit loads of 16
+      // consecutive lanes cover 16 distinct bank pairs.
+      constexpr int kUnits = (kGM + kGN) * 2 / (kGExpanderWarps * 32);   // 3 per thread
+      uint2 in[kUnits];
+#pragma unroll
+      for (int it = 0; it < kUnits; ++it) {
+        const int u = it * (kGExpanderWarps * 32) + et;
+        const int r = ((u >> 4) << 3) + (u & 7), half = (u >> 3) & 1;
+        in[it] = *reinterpret_cast<const uint2*>(bits + r * 16 + half * 8);
+      }
+#pragma unroll
+      for (int it = 0; it < kUnits; ++it) {
+        const int u = it * (kGExpanderWarps * 32) + et;
+        const int r = ((u >> 4) << 3) + (u & 7), half = (u >> 3) & 1;
+        uint8_t* orow = ops + r * kGKBytes;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const uint32_t h = ((jj & 2) ? in[it].y : in[it].x) >> ((jj & 1) * 16);
+          uint4 v;
+          v.x = ((h & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.y = (((h >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.z = (((h >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.w = (((h >> 12) & 0xFu) * 0x00204081u) & 0x01010101u;
+          const int j = half * 4 + jj;
+          *reinterpret_cast<uint4*>(orow + ((j ^ (r & 7)) << 4)) = v;
+        }
       }
       fence_proxy_async_smem();   // generic-proxy stores -> visible to the tensor core's async proxy
       __syncwarp();

@@ -111,7 +111,8 @@ __global__ void __launch_bounds__(256)
 k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
                const int32_t* __restrict__ roww_old, const int32_t* __restrict__ par_p,
                const int32_t* __restrict__ par_q, int64_t n, uint32_t* __restrict__ arena_new,
-               const int64_t* __restrict__ rowptr_new, const int32_t* __restrict__ roww_new) {
+               const int64_t* __restrict__ rowptr_new, const int32_t* __restrict__ roww_new,
+               int skip_w_old_upto) {
   __shared__ uint32_t sbuf[8][36];
   const int lane = threadIdx.x & 31;
   uint32_t* buf = sbuf[threadIdx.x >> 5];
@@ -121,6 +122,7 @@ k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
     if (w_new == 0) continue;  // warp-uniform
     const int32_t p = __ldg(par_p + o), q = __ldg(par_q + o);
     const int w_old = __ldg(roww_old + p);
+    if (w_old <= skip_w_old_upto) continue;
     const uint32_t* msk = arena_old + __ldg(rowptr_old + p);
     const uint32_t* src = arena_old + __ldg(rowptr_old + q);
     uint32_t* dst = arena_new + __ldg(rowptr_new + o);
@@ -338,7 +340,7 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 64);
   k_project_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena_old, d_rowptr_old, d_roww_old,
                                                          d_par_p, d_par_q, n, d_arena_new,
-                                                         d_rowptr_new, d_roww_new);
+                                                         d_rowptr_new, d_roww_new, -1);
   KMLS_LAUNCHED("k_project_rows");
   return 0;
 }

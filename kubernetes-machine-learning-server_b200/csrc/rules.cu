@@ -28,6 +28,7 @@ namespace kmls {
 
 constexpr int kMaxLevels = 32;
 constexpr int kMaxRuleK = 15;  // 2^(k-1) subset table per warp must fit in shared memory
+constexpr int kRuleIlp = 2;    // independent index probes in flight per lane
 
 struct Arena {
   const int32_t* items;
@@ -104,7 +105,7 @@ __device__ __forceinline__ RuleVals rule_values(double s_x, int32_t ca, int32_t 
 // kept rules of x to rule_cnt. A = members of P selected by a; C = the rest of P plus the
 // last member.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4* __restrict__ slots,
               uint64_t mask, double n_total, double min_conf, int2* __restrict__ part,
               int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
@@ -148,25 +149,59 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
       const int32_t last = __ldg(x + (k - 1));
       const double s_x = __ddiv_rn((double)__ldg(a.counts + lvl_first + lvl_begin + j), n_total);
       int kept = 0;
-      for (int a0 = 1; a0 < n_sub; a0 += 32) {
-        const int am = a0 + lane;
-        bool k1 = false, k2 = false;
-        if (am < n_sub) {
-          const int32_t ca = tab_cnt[am];
-          const int rest = (n_sub - 1) ^ am;
-          int32_t cc;
-          if (rest == 0) cc = __ldg(a.counts + last);
-          else cc = trie_child(slots, mask, tab_gid[rest], last).y;
-          if (cc < 0 || ca < 0) {
-            atomicAdd(missing, 1);
-          } else {
-            const RuleVals r = rule_values(s_x, ca, cc, n_total, min_conf);
-            k1 = r.k1;
-            k2 = r.k2;
+      // kRuleIlp antecedent masks per lane and iteration: their first index probes are all
+      // issued before any is consumed, which is what hides the DRAM/L2 latency here
+      for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
+        int am[kRuleIlp];
+        int32_t cc[kRuleIlp];
+        uint64_t key[kRuleIlp], h[kRuleIlp];
+        uint4 slot[kRuleIlp];
+        bool probe[kRuleIlp];
+#pragma unroll
+        for (int u = 0; u < kRuleIlp; ++u) {
+          am[u] = a0 + u * 32 + lane;
+          probe[u] = false;
+          cc[u] = -1;
+          if (am[u] < n_sub) {
+            const int rest = (n_sub - 1) ^ am[u];
+            if (rest == 0) {
+              cc[u] = __ldg(a.counts + last);
+            } else {
+              key[u] = edge_key(tab_gid[rest], last);
+              h[u] = mix64(key[u]) & mask;
+              slot[u] = __ldg(slots + h[u]);
+              probe[u] = true;
+            }
           }
-          part[j * n_part + (am - 1)] = make_int2(ca, cc);
         }
-        kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
+#pragma unroll
+        for (int u = 0; u < kRuleIlp; ++u) {
+          if (probe[u]) {
+            while (true) {
+              const uint64_t sk = ((uint64_t)slot[u].y << 32) | slot[u].x;
+              if (sk == key[u]) { cc[u] = (int32_t)slot[u].w; break; }
+              if (sk == kEmptyEdge) break;
+              h[u] = (h[u] + 1) & mask;
+              slot[u] = __ldg(slots + h[u]);
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kRuleIlp; ++u) {
+          bool k1 = false, k2 = false;
+          if (am[u] < n_sub) {
+            const int32_t ca = tab_cnt[am[u]];
+            if (cc[u] < 0 || ca < 0) {
+              atomicAdd(missing, 1);
+            } else {
+              const RuleVals r = rule_values(s_x, ca, cc[u], n_total, min_conf);
+              k1 = r.k1;
+              k2 = r.k2;
+            }
+            part[j * n_part + (am[u] - 1)] = make_int2(ca, cc[u]);
+          }
+          kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
+        }
       }
       if (lane == 0) rule_cnt[j] = kept;
     }
