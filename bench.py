@@ -41,7 +41,7 @@ WORKLOADS = {
 }
 MIN_SUPPORT_OVERRIDE = None
 CPU_SAMPLE_PLAYLISTS = 100_000   # playlists of the CPU baseline's bounded sample
-CPU_RULE_STRIDE = 16             # rules are generated for 1/16 of the itemsets and scaled
+CPU_RULE_STRIDE = 8              # rules are generated for 1/8 of the itemset table and scaled
 
 
 def log(*a):
@@ -130,32 +130,52 @@ class ClockSampler(threading.Thread):
 # ------------------------------------------------------------------------------ CPU arms
 def cpu_sample_run(name, threads):
     """The oracle (C++ restatement of the reference's FP-Growth + association_rules) on a
-    bounded sample: CPU_SAMPLE_PLAYLISTS playlists of the same distribution at the same
-    min_support (so the itemset structure is the workload's), all itemsets mined, rules
-    generated for every CPU_RULE_STRIDE-th slice of the itemset table. Returns measured and
-    extrapolated seconds."""
+    bounded sample of the workload, extrapolated to the full size:
+      * mining is timed on two samples (50k and 100k playlists of the same generator, same
+        min_support, so the itemset structure is the workload's) and extrapolated linearly in
+        the number of playlists (FP-tree construction grows with N, enumeration does not);
+      * rules are generated for every CPU_RULE_STRIDE-th run of 65,536 itemsets of the 100k
+        sample's table (their cost does not depend on N) and scaled by the share of
+        (itemset, antecedent) splits that the sample evaluated.
+    Checked once against a full-size run (profiles/): see BASELINE.md."""
     from oracle import fpgrowth_c, mlxtend_restated as M
-    n_full = WORKLOADS[name][0]
-    n_s = min(CPU_SAMPLE_PLAYLISTS, n_full)
-    off, items, t, s, conf = make_data(name, shard=0, n_override=n_s)
-    t1, tk = M.thresholds(s, n_s)
-    lib = fpgrowth_c._load()
     import ctypes
-    t0 = time.time()
-    h = lib.oracle_fpgrowth_run(off.ctypes.data, items.ctypes.data, n_s, t, t1, tk, 0, 1, threads)
-    t_mine = time.time() - t0
+    n_full = WORKLOADS[name][0]
+    lib = fpgrowth_c._load()
+    pts = []
+    h = None
+    for n_s in sorted({min(CPU_SAMPLE_PLAYLISTS // 2, n_full), min(CPU_SAMPLE_PLAYLISTS, n_full)}):
+        off, items, t, s, conf = make_data(name, shard=0, n_override=n_s)
+        t1, tk = M.thresholds(s, n_s)
+        if h is not None:
+            lib.oracle_fpgrowth_free(h)
+        t0 = time.time()
+        h = lib.oracle_fpgrowth_run(off.ctypes.data, items.ctypes.data, n_s, t, t1, tk, 0, 1, threads)
+        pts.append((n_s, time.time() - t0))
     n_sets = int(lib.oracle_fpgrowth_num_itemsets(h))
+    lv = np.zeros(64, dtype=np.uint64)
+    lib.oracle_fpgrowth_level_counts(h, lv.ctypes.data)
+    total_splits = sum(int(lv[k]) * ((1 << k) - 2) for k in range(2, 40))
     cs = ctypes.c_uint64(0)
     t0 = time.time()
-    n_rules = int(lib.oracle_rules_strided(h, n_s, conf, threads, CPU_RULE_STRIDE, ctypes.byref(cs)))
+    n_rules = int(lib.oracle_rules_strided(h, pts[-1][0], conf, threads, CPU_RULE_STRIDE, ctypes.byref(cs)))
     t_rules = time.time() - t0
+    rule_scale = total_splits / max(int(lib.oracle_rules_last_splits()), 1)
+    t_index = float(lib.oracle_rules_last_index_seconds())   # serial index build: not scaled
     lib.oracle_fpgrowth_free(h)
-    scale_n = n_full / n_s
-    est = t_mine * scale_n + t_rules * CPU_RULE_STRIDE
-    return {"measured_s": t_mine + t_rules, "mine_s": t_mine, "rules_s": t_rules, "estimate_full_s": est,
+    if len(pts) == 2 and pts[1][0] > pts[0][0]:
+        slope = max((pts[1][1] - pts[0][1]) / (pts[1][0] - pts[0][0]), 0.0)
+        t_mine_full = pts[1][1] + slope * (n_full - pts[1][0])
+    else:
+        t_mine_full = pts[-1][1] * n_full / pts[-1][0]
+    est = t_mine_full + t_index + (t_rules - t_index) * rule_scale
+    measured = sum(p[1] for p in pts) + t_rules
+    return {"measured_s": measured, "mine_s": pts[-1][1], "rules_s": t_rules, "estimate_full_s": est,
             "itemsets": n_sets, "rules_in_slice": n_rules,
-            "sample": (f"{n_s} of {n_full} playlists (same generator and min_support, mining time scaled "
-                       f"x{scale_n:g}); rules for 1/{CPU_RULE_STRIDE} of the itemset table (scaled x{CPU_RULE_STRIDE})")}
+            "sample": (f"mining timed on {' and '.join(str(p[0]) for p in pts)} of {n_full} playlists (same generator "
+                       f"and min_support) and extrapolated linearly in N to {t_mine_full:.1f} s; rules for every "
+                       f"{CPU_RULE_STRIDE}th run of 65,536 itemsets ({t_rules:.1f} s), scaled by the share of "
+                       f"(itemset, antecedent) splits evaluated (x{rule_scale:.2f})")}
 
 
 def run_reference(args):

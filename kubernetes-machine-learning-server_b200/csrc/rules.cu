@@ -47,6 +47,12 @@ __device__ __forceinline__ uint64_t edge_key(int32_t parent_gid, int32_t item) {
   return ((uint64_t)(uint32_t)parent_gid << 32) | (uint32_t)item;
 }
 constexpr unsigned long long kEmptyEdge = ~0ull;
+// slot of a key; `mask` = capacity - 1 (capacity a power of two). A full 64-bit mixer: the
+// keys are highly structured (small item ids, dense parent ids) and linear probing needs a
+// hash without clustering (a plain multiplicative hash made probe chains 7x longer).
+__device__ __forceinline__ uint64_t edge_slot(uint64_t key, uint64_t mask) {
+  return mix64(key) & mask;
+}
 
 // slot = {key lo, key hi, child global id, child count}
 __global__ void __launch_bounds__(256) k_trie_build(Arena a, uint4* __restrict__ slots, uint64_t mask) {
@@ -58,7 +64,7 @@ __global__ void __launch_bounds__(256) k_trie_build(Arena a, uint4* __restrict__
     const int32_t parent = (int32_t)(a.id_off[k - 1] + __ldg(a.par + (gid - first)));
     const int32_t last = __ldg(itemset_ptr(a, k, gid) + (k - 1));
     const uint64_t key = edge_key(parent, last);
-    uint64_t h = mix64(key) & mask;
+    uint64_t h = edge_slot(key, mask);
     while (atomicCAS(reinterpret_cast<unsigned long long*>(slots + h), kEmptyEdge,
                      (unsigned long long)key) != kEmptyEdge)
       h = (h + 1) & mask;
@@ -70,7 +76,7 @@ __global__ void __launch_bounds__(256) k_trie_build(Arena a, uint4* __restrict__
 __device__ __forceinline__ int2 trie_child(const uint4* __restrict__ slots, uint64_t mask,
                                            int32_t parent_gid, int32_t item) {
   const uint64_t key = edge_key(parent_gid, item);
-  uint64_t h = mix64(key) & mask;
+  uint64_t h = edge_slot(key, mask);
   while (true) {
     const uint4 s = __ldg(slots + h);
     const uint64_t sk = ((uint64_t)s.y << 32) | s.x;
@@ -97,6 +103,17 @@ __device__ __forceinline__ RuleVals rule_values(double s_x, int32_t ca, int32_t 
   return r;
 }
 
+// confidence >= min_conf for confidence = fl(fl(cx/N) / fl(ca/N)), decided from the float
+// ratio cx/ca whenever that is clearly (1e-5 relative, far above both the float and the
+// double rounding errors) on one side of the threshold; the exact doubles otherwise.
+__device__ __forceinline__ bool conf_keep(int32_t cx, int32_t ca, double s_x, double n_total,
+                                          double min_conf) {
+  const double r = (double)__fdividef((float)cx, (float)ca);
+  if (r > min_conf * 1.00001) return true;
+  if (r < min_conf * 0.99999) return false;
+  return __ddiv_rn(s_x, __ddiv_rn((double)ca, n_total)) >= min_conf;
+}
+
 // ---------------------------------------------------------------------------------------
 // K5 pass 1, one level k >= 2 per launch. One warp per itemset; only class heads (and the
 // first itemset of the range) work: they resolve the subsets of the class prefix P, then
@@ -105,6 +122,8 @@ __device__ __forceinline__ RuleVals rule_values(double s_x, int32_t ca, int32_t 
 // kept rules of x to rule_cnt. A = members of P selected by a; C = the rest of P plus the
 // last member.
 // ---------------------------------------------------------------------------------------
+constexpr int kRuleChunk = 64;   // consecutive itemsets handled by one warp
+
 __global__ void __launch_bounds__(256, 4)
 k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4* __restrict__ slots,
               uint64_t mask, double n_total, double min_conf, int2* __restrict__ part,
@@ -116,41 +135,43 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
   int32_t* tab_cnt = tab_gid + n_sub;
   const int64_t lvl_first = a.id_off[k];   // global id of the level's first itemset
   const int n_part = n_sub - 1;            // antecedent masks 1 .. n_sub-1
-  for (int64_t i = (int64_t)blockIdx.x * nwarps + warp; i < lvl_count;
-       i += (int64_t)gridDim.x * nwarps) {
-    const int32_t* x0 = itemset_ptr(a, k, lvl_first + lvl_begin + i);
-    if (i > 0) {                           // head test: prefix differs from the predecessor's
-      bool same = true;
-      for (int t = 0; t < k - 1; ++t) same = same && (__ldg(x0 + t) == __ldg(x0 - k + t));
-      if (same) continue;
-    }
-    // subsets of P by DP over the trie index
-    for (int h = 0; h < k - 1; ++h) {
-      const int32_t ph = __ldg(x0 + h);
-      for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
-        const int rest = m ^ (1 << h);
-        int2 gc;
-        if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));   // level-1 id = row index
-        else gc = trie_child(slots, mask, tab_gid[rest], ph);
-        if (gc.x < 0) atomicAdd(missing, 1);
-        tab_gid[m] = gc.x;
-        tab_cnt[m] = gc.y;
-      }
-      __syncwarp();
-    }
-    // siblings
-    for (int64_t j = i; j < lvl_count; ++j) {
+  const int64_t n_chunks = (lvl_count + kRuleChunk - 1) / kRuleChunk;
+  // A warp walks kRuleChunk consecutive itemsets. Consecutive classes of the sorted table
+  // usually differ only in the LAST member of their prefix, so the subsets of P that avoid
+  // the changed members are still in the table: only masks >= 2^d are resolved again, d =
+  // first prefix position that changed (d = 0 for the first class of the chunk).
+  for (int64_t ch = (int64_t)blockIdx.x * nwarps + warp; ch < n_chunks;
+       ch += (int64_t)gridDim.x * nwarps) {
+    const int64_t j_end = min(lvl_count, (ch + 1) * kRuleChunk);
+    const int32_t* head = nullptr;         // prefix owner whose subsets are in the table
+    for (int64_t j = ch * kRuleChunk; j < j_end; ++j) {
       const int32_t* x = itemset_ptr(a, k, lvl_first + lvl_begin + j);
-      if (j > i) {
-        bool same = true;
-        for (int t = 0; t < k - 1; ++t) same = same && (__ldg(x + t) == __ldg(x0 + t));
-        if (!same) break;
+      int d = 0;
+      if (head != nullptr) {
+        while (d < k - 1 && __ldg(x + d) == __ldg(head + d)) ++d;
+      }
+      if (head == nullptr || d < k - 1) {
+        for (int h = d; h < k - 1; ++h) {
+          const int32_t ph = __ldg(x + h);
+          for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
+            const int rest = m ^ (1 << h);
+            int2 gc;
+            if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));   // level-1 id = row index
+            else gc = trie_child(slots, mask, tab_gid[rest], ph);
+            if (gc.x < 0) atomicAdd(missing, 1);
+            tab_gid[m] = gc.x;
+            tab_cnt[m] = gc.y;
+          }
+          __syncwarp();
+        }
+        head = x;
       }
       const int32_t last = __ldg(x + (k - 1));
-      const double s_x = __ddiv_rn((double)__ldg(a.counts + lvl_first + lvl_begin + j), n_total);
+      const int32_t c_x = __ldg(a.counts + lvl_first + lvl_begin + j);
+      const double s_x = __ddiv_rn((double)c_x, n_total);
       int kept = 0;
       // kRuleIlp antecedent masks per lane and iteration: their first index probes are all
-      // issued before any is consumed, which is what hides the DRAM/L2 latency here
+      // issued before any is consumed
       for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
         int am[kRuleIlp];
         int32_t cc[kRuleIlp];
@@ -168,7 +189,7 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
               cc[u] = __ldg(a.counts + last);
             } else {
               key[u] = edge_key(tab_gid[rest], last);
-              h[u] = mix64(key[u]) & mask;
+              h[u] = edge_slot(key[u], mask);
               slot[u] = __ldg(slots + h[u]);
               probe[u] = true;
             }
@@ -194,9 +215,8 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
             if (cc[u] < 0 || ca < 0) {
               atomicAdd(missing, 1);
             } else {
-              const RuleVals r = rule_values(s_x, ca, cc[u], n_total, min_conf);
-              k1 = r.k1;
-              k2 = r.k2;
+              k1 = conf_keep(c_x, ca, s_x, n_total, min_conf);
+              k2 = conf_keep(c_x, cc[u], s_x, n_total, min_conf);
             }
             part[j * n_part + (am[u] - 1)] = make_int2(ca, cc[u]);
           }
@@ -322,7 +342,8 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
   KMLS_REQUIRE(warps >= 1, "kmls_rules_count: subset table does not fit in shared memory");
   const size_t smem = per_warp * warps;
   KMLS_CUDA(cudaFuncSetAttribute(k_rules_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  int grid = (int)std::min<int64_t>((lvl_count + warps - 1) / warps, (int64_t)num_sms() * 32);
+  const int64_t n_chunks = (lvl_count + kRuleChunk - 1) / kRuleChunk;
+  int grid = (int)std::min<int64_t>((n_chunks + warps - 1) / warps, (int64_t)num_sms() * 32);
   k_rules_count<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (const uint4*)d_slots, (uint64_t)capacity - 1,
       (double)n_playlists_total, min_confidence, (int2*)d_part, d_rule_cnt, d_missing);

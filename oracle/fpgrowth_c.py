@@ -40,6 +40,10 @@ def _load():
         lib.oracle_rules.restype = ctypes.c_int64
         lib.oracle_rules.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_int,
                                      ctypes.c_void_p]
+        lib.oracle_rules_last_index_seconds.restype = ctypes.c_double
+        lib.oracle_rules_last_index_seconds.argtypes = []
+        lib.oracle_rules_last_splits.restype = ctypes.c_int64
+        lib.oracle_rules_last_splits.argtypes = []
         lib.oracle_rules_strided.restype = ctypes.c_int64
         lib.oracle_rules_strided.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_double,
                                              ctypes.c_int, ctypes.c_int, ctypes.c_void_p]

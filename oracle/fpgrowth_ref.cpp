@@ -22,6 +22,7 @@
 #include <numeric>
 #include <vector>
 #include <atomic>
+#include <chrono>
 #include <thread>
 
 namespace {
@@ -293,14 +294,24 @@ void oracle_fpgrowth_copy(void* h, int64_t* offsets, int32_t* items, int64_t* co
 // proper subset A: confidence = (cX/N)/(cA/N), lift = confidence/(cC/N), kept iff
 // confidence >= c. Returns the number of rules and an order-independent checksum over
 // (antecedent, consequent, support, confidence, lift) bit patterns; -1 if a subset is missing.
-// `stride` > 1 generates the rules of every stride-th block of 4096 itemsets only (a bounded
-// sample for timing); stride 1 = all.
+// `stride` > 1 generates the rules of every stride-th block of itemsets only (a bounded
+// sample for timing: runs of 65,536 consecutive itemsets, so that the sample keeps the
+// cache locality a full pass has and still averages over the whole table);
+// stride 1 = all.
+static std::atomic<int64_t> g_last_splits{0};
+static double g_last_index_seconds = 0.0;
+// seconds the last oracle_rules* call spent building its (serial) subset index
+double oracle_rules_last_index_seconds() { return g_last_index_seconds; }
+// number of (itemset, antecedent) splits the last oracle_rules* call evaluated
+int64_t oracle_rules_last_splits() { return g_last_splits.load(); }
+
 int64_t oracle_rules_strided(void* h, int64_t n_total, double min_conf, int n_threads, int stride,
                              uint64_t* checksum) {
   auto& s = ((Result*)h)->sink;
   const int64_t n = (int64_t)s.counts.size();
   uint64_t cap = 1024;
   while (cap < 2 * (uint64_t)n) cap <<= 1;
+  const auto t_index0 = std::chrono::steady_clock::now();
   std::vector<uint64_t> keys(cap, 0);
   std::vector<int32_t> vals(cap, -1);
   auto key_of = [&](const int32_t* it, int k) {
@@ -314,6 +325,8 @@ int64_t oracle_rules_strided(void* h, int64_t n_total, double min_conf, int n_th
     while (keys[hh]) hh = (hh + 1) & (cap - 1);
     keys[hh] = key; vals[hh] = (int32_t)i;
   }
+  g_last_index_seconds =
+      std::chrono::duration<double>(std::chrono::steady_clock::now() - t_index0).count();
   auto lookup = [&](const int32_t* it, int k) -> int64_t {
     uint64_t key = key_of(it, k), hh = key & (cap - 1);
     while (keys[hh]) {
@@ -329,20 +342,21 @@ int64_t oracle_rules_strided(void* h, int64_t n_total, double min_conf, int n_th
   int nt = n_threads > 0 ? n_threads : (int)std::thread::hardware_concurrency();
   if (nt < 1) nt = 1;
   std::vector<uint64_t> sums(nt, 0);
-  std::vector<int64_t> cnts(nt, 0);
+  std::vector<int64_t> cnts(nt, 0), splits(nt, 0);
   std::atomic<int64_t> next{0};
   std::atomic<int> missing{0};
   auto bits = [](double d) { uint64_t u; std::memcpy(&u, &d, 8); return u; };
   auto worker = [&](int tid) {
     int32_t a[64], c[64];
-    const int64_t step = 4096;
+    const int64_t step = stride > 1 ? 256 : 4096;
     for (int64_t b = next.fetch_add(step); b < n; b = next.fetch_add(step)) {
-      if (stride > 1 && (b / step) % stride != 0) continue;
+      if (stride > 1 && ((b / step) >> 8) % stride != 0) continue;  // runs of 256 blocks (65,536 itemsets)
       for (int64_t i = b; i < std::min(n, b + step); ++i) {
         const int k = (int)(s.offsets[i + 1] - s.offsets[i]);
         if (k < 2 || k > 30) continue;
         const int32_t* x = s.items.data() + s.offsets[i];
         const double sx = (double)s.counts[i] / (double)n_total;
+        splits[tid] += ((int64_t)1 << k) - 2;
         for (uint32_t m = 1; m + 1 < (1u << k); ++m) {
           int na = 0, nc = 0;
           uint64_t ha = 0, hc = 0;
@@ -371,7 +385,9 @@ int64_t oracle_rules_strided(void* h, int64_t n_total, double min_conf, int n_th
   for (auto& th : pool) th.join();
   if (missing) return -1;
   int64_t total = 0; uint64_t cs = 0;
-  for (int t = 0; t < nt; ++t) { total += cnts[t]; cs += sums[t]; }
+  int64_t sp = 0;
+  for (int t = 0; t < nt; ++t) { total += cnts[t]; cs += sums[t]; sp += splits[t]; }
+  g_last_splits = sp;
   *checksum = cs;
   return total;
 }
