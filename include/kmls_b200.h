@@ -123,14 +123,16 @@ int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t k, uint64_
  * kmls_join_write: candidates (d_cand_p[c], d_cand_q[c]) = indices of the two parents,
  *                  grouped by p in ascending order; d_grp_p / *d_n_groups = the parents that
  *                  have at least one candidate (skipped when d_grp_p is NULL).
- * A NULL d_pair (k == 2) or NULL d_slots (k >= 3) switches the pruning off. */
+ * A NULL d_pair (k == 2) or NULL d_slots (k >= 3) switches the pruning off. d_par (may be
+ * NULL) = each itemset's parent index in level k-1: with it, "same class" is one integer
+ * compare instead of k-1. */
 int kmls_join_count(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
                     int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
-                    int32_t* d_kept_cnt, uint32_t* d_kept_mask, int64_t* d_kept_off,
+                    const int32_t* d_par, int32_t* d_kept_cnt, uint32_t* d_kept_mask, int64_t* d_kept_off,
                     void* d_scratch, size_t scratch_bytes, kmls_stream_t stream);
 int kmls_join_write(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
                     int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
-                    const int32_t* d_kept_cnt, const uint32_t* d_kept_mask,
+                    const int32_t* d_par, const int32_t* d_kept_cnt, const uint32_t* d_kept_mask,
                     const int64_t* d_kept_off, int32_t* d_cand_p, int32_t* d_cand_q,
                     int32_t* d_grp_p, int64_t* d_n_groups, void* d_scratch, size_t scratch_bytes,
                     kmls_stream_t stream);

@@ -34,8 +34,8 @@ SIGNATURES = {
     "kmls_exclusive_scan_i32_noalloc": (ctypes.c_int, [_P, _I64, _P, _P]),
     "kmls_set_capacity": (_I64, [_I64]),
     "kmls_itemset_set_build": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P]),
-    "kmls_join_count": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _SZ, _P]),
-    "kmls_join_write": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _P,
+    "kmls_join_count": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _P, _SZ, _P]),
+    "kmls_join_write": (ctypes.c_int, [_P, _I64, _I32, _P, _I64, _P, _I32, _I32, _P, _P, _P, _P, _P, _P,
                                        _P, _P, _P, _SZ, _P]),
     "kmls_count_candidates": (ctypes.c_int, [_P, _I64, _P, _I32, _P, _I64, _P, _P, _I64, _P, _P]),
     "kmls_emit_count": (ctypes.c_int, [_P, _I64, _I32, _P, _P, _SZ, _P]),

@@ -103,7 +103,8 @@ __device__ __forceinline__ bool set_contains(const unsigned long long* __restric
 __global__ void __launch_bounds__(256)
 k_join(const int32_t* __restrict__ items, int64_t n, int k,
        const unsigned long long* __restrict__ slots, uint64_t mask,
-       const int32_t* __restrict__ pairC, int32_t n_rows, int32_t thr, int write,
+       const int32_t* __restrict__ pairC, int32_t n_rows, int32_t thr,
+       const int32_t* __restrict__ par, int write,
        int32_t* __restrict__ kept_cnt, uint32_t* __restrict__ kept_mask,
        const int64_t* __restrict__ kept_off, int32_t* __restrict__ cand_p,
        int32_t* __restrict__ cand_q) {
@@ -121,8 +122,12 @@ k_join(const int32_t* __restrict__ items, int64_t n, int k,
       const int64_t q = q0 + lane;
       bool in_class = q < n;
       if (in_class) {
-        const int32_t* iq = items + q * k;
-        for (int t = 0; t < k - 1; ++t) in_class = in_class && (__ldg(iq + t) == __ldg(ip + t));
+        if (par != nullptr) {             // same parent <=> same first k-1 members
+          in_class = __ldg(par + q) == __ldg(par + p);
+        } else {
+          const int32_t* iq = items + q * k;
+          for (int t = 0; t < k - 1; ++t) in_class = in_class && (__ldg(iq + t) == __ldg(ip + t));
+        }
       }
       const uint32_t cm = __ballot_sync(0xffffffffu, in_class);
       bool keep = false;
@@ -275,7 +280,7 @@ extern "C" int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t
 
 static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
                        int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
-                       int write, int32_t* d_kept_cnt, uint32_t* d_kept_mask,
+                       const int32_t* d_par, int write, int32_t* d_kept_cnt, uint32_t* d_kept_mask,
                        const int64_t* d_kept_off, int32_t* d_cand_p, int32_t* d_cand_q,
                        cudaStream_t s) {
   KMLS_REQUIRE(n >= 0 && n <= 0x7fffffff && k >= 2 && k <= 30, "kmls_join: bad level size");
@@ -287,7 +292,7 @@ static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint6
   if (n == 0) return 0;
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 32);
   k_join<<<grid, 256, 0, s>>>(d_items, n, k, (const unsigned long long*)d_slots,
-                              (uint64_t)capacity - 1, d_pair, n_rows, thr, write, d_kept_cnt,
+                              (uint64_t)capacity - 1, d_pair, n_rows, thr, d_par, write, d_kept_cnt,
                               d_kept_mask, d_kept_off, d_cand_p, d_cand_q);
   KMLS_LAUNCHED("k_join");
   return 0;
@@ -295,12 +300,12 @@ static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint6
 
 extern "C" int kmls_join_count(const int32_t* d_items, int64_t n, int32_t k,
                                const uint64_t* d_slots, int64_t capacity, const int32_t* d_pair,
-                               int32_t n_rows, int32_t thr, int32_t* d_kept_cnt,
-                               uint32_t* d_kept_mask, int64_t* d_kept_off, void* d_scratch,
-                               size_t scratch_bytes, kmls_stream_t stream) {
+                               int32_t n_rows, int32_t thr, const int32_t* d_par,
+                               int32_t* d_kept_cnt, uint32_t* d_kept_mask, int64_t* d_kept_off,
+                               void* d_scratch, size_t scratch_bytes, kmls_stream_t stream) {
   cudaStream_t s = (cudaStream_t)stream;
   KMLS_REQUIRE(d_kept_off, "kmls_join_count: null pointer");
-  int rc = launch_join(d_items, n, k, d_slots, capacity, d_pair, n_rows, thr, 0, d_kept_cnt,
+  int rc = launch_join(d_items, n, k, d_slots, capacity, d_pair, n_rows, thr, d_par, 0, d_kept_cnt,
                        d_kept_mask, nullptr, nullptr, nullptr, s);
   if (rc) return rc;
   return scan_i32(d_kept_cnt, n, d_kept_off, d_scratch, scratch_bytes, ToI64(), s);
@@ -308,13 +313,14 @@ extern "C" int kmls_join_count(const int32_t* d_items, int64_t n, int32_t k,
 
 extern "C" int kmls_join_write(const int32_t* d_items, int64_t n, int32_t k,
                                const uint64_t* d_slots, int64_t capacity, const int32_t* d_pair,
-                               int32_t n_rows, int32_t thr, const int32_t* d_kept_cnt,
+                               int32_t n_rows, int32_t thr, const int32_t* d_par,
+                               const int32_t* d_kept_cnt,
                                const uint32_t* d_kept_mask, const int64_t* d_kept_off,
                                int32_t* d_cand_p, int32_t* d_cand_q, int32_t* d_grp_p,
                                int64_t* d_n_groups, void* d_scratch, size_t scratch_bytes,
                                kmls_stream_t stream) {
   cudaStream_t s = (cudaStream_t)stream;
-  int rc = launch_join(d_items, n, k, d_slots, capacity, d_pair, n_rows, thr, 1,
+  int rc = launch_join(d_items, n, k, d_slots, capacity, d_pair, n_rows, thr, d_par, 1,
                        const_cast<int32_t*>(d_kept_cnt), const_cast<uint32_t*>(d_kept_mask),
                        d_kept_off, d_cand_p, d_cand_q, s);
   if (rc) return rc;

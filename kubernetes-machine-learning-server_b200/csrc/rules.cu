@@ -122,11 +122,11 @@ __device__ __forceinline__ bool conf_keep(int32_t cx, int32_t ca, double s_x, do
 // kept rules of x to rule_cnt. A = members of P selected by a; C = the rest of P plus the
 // last member.
 // ---------------------------------------------------------------------------------------
-constexpr int kRuleChunk = 64;   // consecutive itemsets handled by one warp
+constexpr int kRuleChunkMax = 64;   // consecutive itemsets handled by one warp (at most)
 
 __global__ void __launch_bounds__(256, 4)
 k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4* __restrict__ slots,
-              uint64_t mask, double n_total, double min_conf, int2* __restrict__ part,
+              uint64_t mask, double n_total, double min_conf, int chunk, int2* __restrict__ part,
               int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
   extern __shared__ int32_t smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -135,16 +135,16 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
   int32_t* tab_cnt = tab_gid + n_sub;
   const int64_t lvl_first = a.id_off[k];   // global id of the level's first itemset
   const int n_part = n_sub - 1;            // antecedent masks 1 .. n_sub-1
-  const int64_t n_chunks = (lvl_count + kRuleChunk - 1) / kRuleChunk;
-  // A warp walks kRuleChunk consecutive itemsets. Consecutive classes of the sorted table
+  const int64_t n_chunks = (lvl_count + chunk - 1) / chunk;
+  // A warp walks `chunk` consecutive itemsets. Consecutive classes of the sorted table
   // usually differ only in the LAST member of their prefix, so the subsets of P that avoid
   // the changed members are still in the table: only masks >= 2^d are resolved again, d =
   // first prefix position that changed (d = 0 for the first class of the chunk).
   for (int64_t ch = (int64_t)blockIdx.x * nwarps + warp; ch < n_chunks;
        ch += (int64_t)gridDim.x * nwarps) {
-    const int64_t j_end = min(lvl_count, (ch + 1) * kRuleChunk);
+    const int64_t j_end = min(lvl_count, (ch + 1) * chunk);
     const int32_t* head = nullptr;         // prefix owner whose subsets are in the table
-    for (int64_t j = ch * kRuleChunk; j < j_end; ++j) {
+    for (int64_t j = ch * chunk; j < j_end; ++j) {
       const int32_t* x = itemset_ptr(a, k, lvl_first + lvl_begin + j);
       int d = 0;
       if (head != nullptr) {
@@ -342,11 +342,13 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
   KMLS_REQUIRE(warps >= 1, "kmls_rules_count: subset table does not fit in shared memory");
   const size_t smem = per_warp * warps;
   KMLS_CUDA(cudaFuncSetAttribute(k_rules_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-  const int64_t n_chunks = (lvl_count + kRuleChunk - 1) / kRuleChunk;
+  // chunks long enough to reuse the subset table, short enough to keep every SM busy
+  const int chunk = (int)std::max<int64_t>(1, std::min<int64_t>(kRuleChunkMax, lvl_count / ((int64_t)num_sms() * 64)));
+  const int64_t n_chunks = (lvl_count + chunk - 1) / chunk;
   int grid = (int)std::min<int64_t>((n_chunks + warps - 1) / warps, (int64_t)num_sms() * 32);
   k_rules_count<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (const uint4*)d_slots, (uint64_t)capacity - 1,
-      (double)n_playlists_total, min_confidence, (int2*)d_part, d_rule_cnt, d_missing);
+      (double)n_playlists_total, min_confidence, chunk, (int2*)d_part, d_rule_cnt, d_missing);
   KMLS_LAUNCHED("k_rules_count");
   return 0;
 }

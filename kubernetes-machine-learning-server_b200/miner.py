@@ -310,7 +310,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         kept_mask = dev.empty(n, torch.int32)
         kept_off = dev.empty(n + 1, torch.int64)
         pair_arg = pair if (k == 2 and prune) else 0
-        _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
+        par_k = parents[-1]
+        _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair_arg, n_rows, thr, par_k, kept_cnt,
                   kept_mask, kept_off, scratch, sbytes, s)
         n_cand = int(kept_off[n].item())
         if n_cand == 0:
@@ -321,8 +322,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         cand_q = dev.empty(n_cand, torch.int32)
         cand_cnt = dev.empty(n_cand, torch.int32)
         if projected:
-            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
-                      kept_mask, kept_off, cand_p, cand_q, 0, 0, scratch, sbytes, s)
+            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, par_k,
+                      kept_cnt, kept_mask, kept_off, cand_p, cand_q, 0, 0, scratch, sbytes, s)
             n_groups = None
             _lib.call("kmls_count_pairs", arena_k, rowptr_k, roww_k, cand_p, cand_q, n_cand,
                       cand_cnt, s)
@@ -330,8 +331,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         else:
             grp_p = dev.empty(n, torch.int32)
             n_groups_d = dev.empty(1, torch.int64)
-            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, kept_cnt,
-                      kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
+            _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, par_k,
+                      kept_cnt, kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
             n_groups = int(n_groups_d.item())
             _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
                       kept_off, cand_q, n_cand, cand_cnt, s,
