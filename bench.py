@@ -36,9 +36,13 @@ WORKLOADS = {
     "zipf_200kx20k_s0.004": (200_000, 20_000, 50.0, 1.0, 0.004, 0.04),      # quick check
     # stand-ins for the reference's own (absent) CSVs, shaped after its report's ds2 log:
     # (n_playlists, n_names, -, -, MIN_SUPPORT, MIN_CONFIDENCE); generator synth.mpd_standin(seed)
+    # BASELINE.json config 5: 10M playlists x 2M tracks in total, row-sharded over the ranks
+    # (strong: the total is fixed, each of R ranks generates 10M/R playlists)
+    "zipf_10Mx2M_s0.001": (10_000_000, 2_000_000, 68.0, 1.0, 0.001, 0.04),
     "mpd_standin_seed1_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
     "mpd_standin_seed2_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
 }
+TOTAL_IS_FIXED = {"zipf_10Mx2M_s0.001"}   # workloads whose playlist count is the job's, not per GPU
 MIN_SUPPORT_OVERRIDE = None
 CPU_SAMPLE_PLAYLISTS = 100_000   # playlists of the CPU baseline's bounded sample
 CPU_RULE_STRIDE = 8              # rules are generated for 1/8 of the itemset table and scaled
@@ -234,7 +238,9 @@ def run_gpu(args):
         dist.init_process_group("nccl", device_id=device)
         group = dist.group.WORLD
     name = args.workload
-    off, items, n_tracks, s, conf = make_data(name, shard=rank)
+    fixed = name in TOTAL_IS_FIXED
+    off, items, n_tracks, s, conf = make_data(name, shard=rank,
+                                              n_override=WORKLOADS[name][0] // world if fixed else None)
     n_local = len(off) - 1
     n_total = n_local * world
     h_off = torch.from_numpy(off).pin_memory()
@@ -423,7 +429,8 @@ def run_gpu(args):
         line = {
             "metric": "mine+rules wall time", "value": step_s, "unit": "s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
-            "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u32+f64",
+            "higher_is_better": False, "scaling": "strong" if fixed else "weak", "vs_baseline": None,
+            "dtype": "u32+f64",
             "data": "synthetic",
             "config": {"workload": name, "n_playlists_per_gpu": n_local, "n_tracks": n_tracks, "mean_draws": draws,
                        "zipf_alpha": alpha, "min_support": s, "min_confidence": None if args.no_rules else conf,
@@ -440,6 +447,7 @@ def run_gpu(args):
             "cpu_baseline": cpu,
             "support_counts_per_s": n_counts / step_s if step_s else None,
             "itemsets": info.get("itemsets"), "rules_rank0": info.get("rules_this_rank"),
+            "peak_hbm_gb": torch.cuda.max_memory_allocated() / 1e9,
             "level_sizes": info.get("levels"),
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
