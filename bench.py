@@ -48,8 +48,17 @@ CPU_SAMPLE_PLAYLISTS = 100_000   # playlists of the CPU baseline's bounded sampl
 CPU_RULE_STRIDE = 8              # rules are generated for 1/8 of the itemset table and scaled
 
 
+_REAL_STDOUT = None
+
+
 def log(*a):
     print(*a, file=sys.stderr, flush=True)
+
+
+def emit(line):
+    out = _REAL_STDOUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
 
 
 def make_data(name, shard, n_override=None):
@@ -218,7 +227,7 @@ def run_reference(args):
         "cpu_baseline": {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": vals[0]["sample"]},
         "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------ GPU arm
@@ -454,12 +463,21 @@ def run_gpu(args):
             "top_kernel": top,
             "verify_full_size": verify,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
+    import faulthandler
+    faulthandler.enable()
+    # The contract is ONE JSON line on stdout. Libraries write there too (NCCL prints its
+    # version banner to stdout), so everything else is sent to stderr at the descriptor
+    # level and only the JSON line goes to the real stdout.
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
