@@ -170,16 +170,21 @@ int kmls_emit_level_px(const int32_t* d_items, int32_t k, const int32_t* d_cand_
                        const int64_t* d_out_off, int32_t* d_out_items, int32_t* d_out_counts,
                        int32_t* d_out_counts_local, int32_t* d_out_par_p, int32_t* d_out_par_q,
                        kmls_stream_t stream);
-/* Row widths of a new level: d_roww[o] = ceil(d_parent_cnt_local[d_par_p[o]] / 32) padded to
- * 4 words if another itemset shares o's first parent, else 0. */
+/* Row widths of a new level: 0 if no other itemset shares o's first parent p; else the
+ * parent's width d_parent_roww[p] if that is <= keep_words words (the row then stays in the parent's
+ * column space); else ceil(d_parent_cnt_local[p] / 32) padded to 4 words. d_parent_roww may be
+ * NULL (always compact). keep_words: the limit above (-1 = default, 256; pass the same value to
+ * kmls_project_rows). */
 int kmls_row_alloc(const int32_t* d_par_p, int64_t n, const int32_t* d_parent_cnt_local,
-                   int32_t* d_roww, kmls_stream_t stream);
+                   const int32_t* d_parent_roww, int32_t keep_words, int32_t* d_roww,
+                   kmls_stream_t stream);
 /* New rows: row(o) = row_old(d_par_q[o]) restricted to the columns set in
- * row_old(d_par_p[o]), compacted (parallel bit extract). */
+ * row_old(d_par_p[o]), compacted (parallel bit extract) - or, when the parents' rows are
+ * <= 128 words, row_old(p) AND row_old(q) uncompacted (widths as set by kmls_row_alloc). */
 int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
                       const int32_t* d_roww_old, const int32_t* d_par_p, const int32_t* d_par_q,
                       int64_t n, uint32_t* d_arena_new, const int64_t* d_rowptr_new,
-                      const int32_t* d_roww_new, kmls_stream_t stream);
+                      const int32_t* d_roww_new, int32_t keep_words, kmls_stream_t stream);
 
 /* First projection (level 1 -> 2), where the masks are sparse single-track rows:
  * kmls_row_tidlists turns every bitmap row r into the ascending list of its set columns at

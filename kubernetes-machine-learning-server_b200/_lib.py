@@ -42,8 +42,8 @@ SIGNATURES = {
     "kmls_emit_level": (ctypes.c_int, [_P, _I32, _P, _P, _P, _I64, _I32, _P, _P, _P, _P]),
     "kmls_count_pairs": (ctypes.c_int, [_P, _P, _P, _P, _P, _I64, _P, _P]),
     "kmls_emit_level_px": (ctypes.c_int, [_P, _I32, _P, _P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P]),
-    "kmls_row_alloc": (ctypes.c_int, [_P, _I64, _P, _P, _P]),
-    "kmls_project_rows": (ctypes.c_int, [_P, _P, _P, _P, _P, _I64, _P, _P, _P, _P]),
+    "kmls_row_alloc": (ctypes.c_int, [_P, _I64, _P, _P, _I32, _P, _P]),
+    "kmls_project_rows": (ctypes.c_int, [_P, _P, _P, _P, _P, _I64, _P, _P, _P, _I32, _P]),
     "kmls_row_tidlists": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P]),
     "kmls_project_rows_gather": (ctypes.c_int, [_P, _I64, _P, _P, _I64, _P, _P, _P, _P, _I64, _P]),
     "kmls_trie_index_build": (ctypes.c_int, [_P, _P, _P, _P, _I32, _P, _I64, _P]),

@@ -7,7 +7,8 @@
 // (columns compacted, so the row is c(P) bits wide, not N). Then
 //   * the support of a candidate (P, x_i, x_j) is popcount(row(P,x_i) AND row(P,x_j));
 //   * the row of a new (k+1)-itemset (P, x_i, x_j) is row(P,x_j) with the columns where
-//     row(P,x_i) is 0 squeezed out (a parallel bit extract), c(P,x_i) bits wide.
+//     row(P,x_i) is 0 squeezed out (a parallel bit extract), c(P,x_i) bits wide - or, once
+//     rows are at most 128 words, simply row(P,x_i) AND row(P,x_j) in the same columns.
 // Level 1 is the full bitmap (P = {}, all N columns). Work per candidate therefore shrinks
 // with the support of its prefix instead of staying at N/8 bytes.
 #include "common.cuh"
@@ -65,18 +66,27 @@ k_emit_level_px(const int32_t* __restrict__ items, int k, const int32_t* __restr
   }
 }
 
+// Columns are squeezed only while that shortens the work: a warp ANDs and popcounts up to
+// kKeepWords words (one 128-bit load per lane) in a single step, so a row that is already
+// that short is kept in its parent's column space (plain AND, no bit extract). The callers
+// pass the limit (`keep_words`, default 256; 0 = always squeeze) to both kernels below.
+constexpr int kKeepWordsDefault = 256;
+
 // Row sizing: an itemset gets a row only if its class (same first parent) has at least two
-// members - a lone member can never be joined again. Width = ceil(local count of the
-// parent / 32) words, padded to 4 words (128-bit loads).
+// members - a lone member can never be joined again. Width: the parent's row width if that
+// is already <= kKeepWords (the row stays in the parent's column space), else
+// ceil(local count of the parent / 32) words, padded to 4 words (128-bit loads).
 __global__ void __launch_bounds__(256)
 k_row_alloc(const int32_t* __restrict__ par_p, int64_t n, const int32_t* __restrict__ parent_cnt_local,
-            int32_t* __restrict__ roww) {
+            const int32_t* __restrict__ parent_roww, int keep_words, int32_t* __restrict__ roww) {
   for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < n;
        o += (int64_t)gridDim.x * blockDim.x) {
     const int32_t p = par_p[o];
     const bool shared = (o > 0 && par_p[o - 1] == p) || (o + 1 < n && par_p[o + 1] == p);
     const int32_t c = __ldg(parent_cnt_local + p);
-    roww[o] = shared ? (((c + 31) >> 5) + 3) & ~3 : 0;
+    const int32_t w_old = parent_roww ? __ldg(parent_roww + p) : 0x7fffffff;
+    const int32_t w = w_old <= keep_words ? w_old : ((((c + 31) >> 5) + 3) & ~3);
+    roww[o] = shared ? w : 0;
   }
 }
 
@@ -112,7 +122,7 @@ k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
                const int32_t* __restrict__ roww_old, const int32_t* __restrict__ par_p,
                const int32_t* __restrict__ par_q, int64_t n, uint32_t* __restrict__ arena_new,
                const int64_t* __restrict__ rowptr_new, const int32_t* __restrict__ roww_new,
-               int skip_w_old_upto) {
+               int keep_words) {
   __shared__ uint32_t sbuf[8][36];
   const int lane = threadIdx.x & 31;
   uint32_t* buf = sbuf[threadIdx.x >> 5];
@@ -122,10 +132,17 @@ k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
     if (w_new == 0) continue;  // warp-uniform
     const int32_t p = __ldg(par_p + o), q = __ldg(par_q + o);
     const int w_old = __ldg(roww_old + p);
-    if (w_old <= skip_w_old_upto) continue;
     const uint32_t* msk = arena_old + __ldg(rowptr_old + p);
     const uint32_t* src = arena_old + __ldg(rowptr_old + q);
     uint32_t* dst = arena_new + __ldg(rowptr_new + o);
+    if (w_old <= keep_words) {
+      // short rows keep their column space: new row = row(p) AND row(q)   (w_new == w_old)
+      const uint4* m4 = reinterpret_cast<const uint4*>(msk);
+      const uint4* s4 = reinterpret_cast<const uint4*>(src);
+      uint4* d4 = reinterpret_cast<uint4*>(dst);
+      for (int v = lane; v < (w_old >> 2); v += 32) d4[v] = and4(ldg4(m4 + v), ldg4(s4 + v));
+      continue;
+    }
     for (int i = lane; i < 36; i += 32) buf[i] = 0;
     __syncwarp();
     int base = 0;  // bits emitted so far
@@ -314,12 +331,15 @@ extern "C" int kmls_emit_level_px(const int32_t* d_items, int32_t k, const int32
 }
 
 extern "C" int kmls_row_alloc(const int32_t* d_par_p, int64_t n, const int32_t* d_parent_cnt_local,
-                              int32_t* d_roww, kmls_stream_t stream) {
+                              const int32_t* d_parent_roww, int32_t keep_words, int32_t* d_roww,
+                              kmls_stream_t stream) {
   KMLS_REQUIRE(n >= 0, "kmls_row_alloc: negative size");
   if (n == 0) return 0;
   KMLS_REQUIRE(d_par_p && d_parent_cnt_local && d_roww, "kmls_row_alloc: null pointer");
   int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
-  k_row_alloc<<<grid, 256, 0, (cudaStream_t)stream>>>(d_par_p, n, d_parent_cnt_local, d_roww);
+  if (keep_words < 0) keep_words = kKeepWordsDefault;
+  k_row_alloc<<<grid, 256, 0, (cudaStream_t)stream>>>(d_par_p, n, d_parent_cnt_local, d_parent_roww,
+                                                      keep_words, d_roww);
   KMLS_LAUNCHED("k_row_alloc");
   return 0;
 }
@@ -328,7 +348,7 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
                                  const int32_t* d_roww_old, const int32_t* d_par_p,
                                  const int32_t* d_par_q, int64_t n, uint32_t* d_arena_new,
                                  const int64_t* d_rowptr_new, const int32_t* d_roww_new,
-                                 kmls_stream_t stream) {
+                                 int32_t keep_words, kmls_stream_t stream) {
   KMLS_REQUIRE(n >= 0, "kmls_project_rows: negative size");
   if (n == 0) return 0;
   // an arena may be NULL when it holds no rows (all widths 0); rows of width 0 are skipped
@@ -340,7 +360,8 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 64);
   k_project_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena_old, d_rowptr_old, d_roww_old,
                                                          d_par_p, d_par_q, n, d_arena_new,
-                                                         d_rowptr_new, d_roww_new, -1);
+                                                         d_rowptr_new, d_roww_new,
+                                                         keep_words < 0 ? kKeepWordsDefault : keep_words);
   KMLS_LAUNCHED("k_project_rows");
   return 0;
 }

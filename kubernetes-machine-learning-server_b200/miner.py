@@ -130,7 +130,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
              n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
              pair_impl: str = "auto", count_impl: str = "projected",
-             prune: Optional[bool] = None, first_projection: str = "gather") -> MineResult:
+             prune: Optional[bool] = None, first_projection: str = "gather",
+             keep_words: Optional[int] = None) -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
@@ -144,6 +145,10 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     always frequent). ``first_projection``: "gather" or "pext" for the level 1 -> 2 rows."""
     if prune is None:
         prune = count_impl != "projected"
+    if keep_words is None:
+        # rows at most this wide stay in their parent's column space (AND, no bit extract)
+        import os
+        keep_words = int(os.environ.get("KMLS_KEEP_WORDS", 256))
     if min_support <= 0.0:
         thresholds(min_support, 1)  # raises the reference's ValueError
     if not (offsets.is_cuda and items.is_cuda):
@@ -262,7 +267,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         """Rows of a new level from the rows of its parents' level (``first``: from the full
         bitmap, by gathering at the parents' column lists)."""
         roww = dev.empty(n_new, torch.int32)
-        _lib.call("kmls_row_alloc", par_p, n_new, parent_cnt_local, roww, s)
+        _lib.call("kmls_row_alloc", par_p, n_new, parent_cnt_local, 0 if first else roww_old,
+                  keep_words, roww, s)
         scratch, sbytes = dev.scan_scratch(n_new)
         rowptr = dev.empty(n_new + 1, torch.int64)
         _lib.call("kmls_exclusive_scan_i32", roww, n_new, rowptr, scratch, sbytes, s)
@@ -279,7 +285,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
                       tid_off, arena, rowptr, words, s, algo_bytes=4 * words)
         else:
             _lib.call("kmls_project_rows", arena_old, rowptr_old, roww_old, par_p, par_q, n_new,
-                      arena, rowptr, roww, s, algo_bytes=8 * words)
+                      arena, rowptr, roww, 0 if first else keep_words, s, algo_bytes=8 * words)
         return arena, rowptr, roww, words
 
     if projected and more:

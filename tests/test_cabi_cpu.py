@@ -30,6 +30,16 @@ def test_library_exports_every_declared_symbol():
     assert set(names) == set(_lib.SIGNATURES), "ctypes table and header disagree"
 
 
+def test_library_is_not_older_than_its_sources():
+    """A stale libkmls_b200.so behind a changed header means ctypes calls with the wrong
+    argument lists (a crash on the GPU box, not an error): rebuild before anything else."""
+    import glob
+    srcs = glob.glob(os.path.join(ROOT, "kubernetes-machine-learning-server_b200", "csrc", "*.cu*")) + \
+        [os.path.join(ROOT, "include", "kmls_b200.h")]
+    newest = max(os.path.getmtime(p) for p in srcs)
+    assert os.path.getmtime(_lib.LIB_PATH) >= newest, "run __graft_entry__.build(): library older than sources"
+
+
 def test_version_and_error_text():
     lib = _lib.load()
     assert lib.kmls_version() == 100

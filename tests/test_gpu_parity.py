@@ -192,7 +192,7 @@ def test_project_rows_and_count_pairs():
     par_q = torch.tensor([b for _, b in pq], dtype=torch.int32, device=dev())
     n = len(pq)
     roww = torch.empty(n, dtype=torch.int32, device=dev())
-    _lib.call("kmls_row_alloc", par_p, n, cnt1, roww, stream())
+    _lib.call("kmls_row_alloc", par_p, n, cnt1, 0, 0, roww, stream())
     want_w = [(((int(dense[a].sum()) + 31) // 32 + 3) // 4 * 4) if a != 20 else 0 for a, _ in pq]
     assert roww.cpu().tolist() == want_w
     sb = int(_lib.value("kmls_scan_scratch_bytes", n))
@@ -201,7 +201,7 @@ def test_project_rows_and_count_pairs():
     _lib.call("kmls_exclusive_scan_i32", roww, n, rowptr, scratch, sb, stream())
     words = int(rowptr[n].item())
     arena = torch.full((max(words, 1),), 0x7BADBEEF, dtype=torch.int32, device=dev())
-    _lib.call("kmls_project_rows", bm, rowptr1, roww1, par_p, par_q, n, arena, rowptr, roww, stream())
+    _lib.call("kmls_project_rows", bm, rowptr1, roww1, par_p, par_q, n, arena, rowptr, roww, 0, stream())
     got = arena.cpu().numpy().view(np.uint32)
     rp = rowptr.cpu().numpy()
     for i, (a, b) in enumerate(pq):
@@ -222,14 +222,15 @@ def test_project_rows_and_count_pairs():
     assert cc.cpu().tolist() == want_c
 
 
-@pytest.mark.parametrize("count_impl,prune,first", [
-    ("projected", True, "gather"), ("projected", False, "gather"), ("projected", False, "pext"),
-    ("fullwidth", True, "gather"), ("fullwidth", False, "gather")])
-def test_counting_variants_agree(count_impl, prune, first):
+@pytest.mark.parametrize("count_impl,prune,first,keep", [
+    ("projected", True, "gather", None), ("projected", False, "gather", 0), ("projected", False, "pext", 8),
+    ("projected", False, "gather", 100000), ("fullwidth", True, "gather", None),
+    ("fullwidth", False, "gather", None)])
+def test_counting_variants_agree(count_impl, prune, first, keep):
     off, items = synth.zipf_playlists(9000, 700, mean_draws=30, alpha=0.9, seed=31)
     want = oracle_dict(off, items, 700, 0.012)
     res, _ = kmls_b200.mine_ids(off, items, 700, 0.012, count_impl=count_impl, prune=prune,
-                                first_projection=first)
+                                first_projection=first, keep_words=keep)
     assert res.as_dict() == want
     assert len(res.levels) >= 5
 
