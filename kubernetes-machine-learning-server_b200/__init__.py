@@ -7,11 +7,14 @@ the lower-level entry points it is built from. All compute runs in ``libkmls_b20
 """
 from . import synth  # noqa: F401  (numpy only)
 from ._lib import KmlsError, LIB_PATH  # noqa: F401
-from .miner import MineResult, RuleTable, generate_rules, mine_csr, rules_to_host, thresholds  # noqa: F401
-from .api import (calculate_and_save_fp_growth_fast, encode_transactions, itemsets_frame,  # noqa: F401
-                  mine_ids, recommendations_from_result, rules_frame, save_rules)
+from .miner import (MineResult, Prepared, RuleTable, generate_rules, mine_csr, prepare,  # noqa: F401
+                    rules_to_host, thresholds)
+from .api import (calculate_and_save_fp_growth_fast, encode_frame, encode_transactions,  # noqa: F401
+                  itemsets_frame, mine_ids, most_frequent_tracks, recommendations_from_frame,
+                  recommendations_from_result, rules_frame, save_rules, sweep_supports)
 
 __all__ = ["calculate_and_save_fp_growth_fast", "mine_csr", "mine_ids", "generate_rules",
            "thresholds", "encode_transactions", "recommendations_from_result", "itemsets_frame",
            "rules_frame", "save_rules", "rules_to_host", "MineResult", "RuleTable", "KmlsError",
-           "synth"]
+           "synth", "prepare", "Prepared", "encode_frame", "recommendations_from_frame",
+           "most_frequent_tracks", "sweep_supports"]

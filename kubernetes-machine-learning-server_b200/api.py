@@ -168,6 +168,86 @@ def calculate_and_save_fp_growth_fast(playlist_dict: dict, min_support=0.07, tot
     return songs_to_song_sets, info, runtime_info
 
 
+# --------------------------------------------------------------------------------------
+# The rows SURVEY.md section 8(f) marks "next": the callers and data formats either side of the path.
+# --------------------------------------------------------------------------------------
+def encode_frame(pid, track_name):
+    """(f1) Ingest without the Python dict: what ``group_tracks_by_playlist...`` (main.py:195-207)
+    + ``list(playlist_dict.values())`` (:265) + ``TransactionEncoder.fit`` produce, straight from the
+    CSV's two columns: ``columns`` = sorted unique names, CSR of name ids grouped by ``pid``
+    (playlists in ascending pid order, rows of a playlist in file order, duplicates kept)."""
+    pid = np.asarray(pid)
+    names = pd.Series(np.asarray(track_name, dtype=object))
+    cat = pd.Categorical(names, categories=sorted(set(names.tolist())))
+    ids = np.asarray(cat.codes, dtype=np.int32)
+    order = np.argsort(pid, kind="stable")
+    pid_s = pid[order]
+    starts = np.flatnonzero(np.concatenate([[True], pid_s[1:] != pid_s[:-1]])) if len(pid_s) else np.zeros(0, int)
+    offsets = np.concatenate([starts, [len(pid_s)]]).astype(np.int64)
+    return list(cat.categories), offsets, ids[order]
+
+
+def recommendations_from_frame(pid, track_name, min_support=0.07, total_songs=None,
+                               min_confidence: Optional[float] = None):
+    """``calculate_and_save_fp_growth_fast`` for the two CSV columns themselves (no dict of
+    lists of strings in between): same return tuple, same prints."""
+    global last_result
+    start_time = pd.Timestamp.now()
+    if min_support <= 0.0:
+        miner.thresholds(min_support, 1)
+    columns, offsets, ids = encode_frame(pid, track_name)
+    conf = MIN_CONFIDENCE if min_confidence is None else min_confidence
+    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf)
+    out = recommendations_from_result(res, columns)
+    ts = total_songs if total_songs is not None else (globals()["total_songs"] or len(columns))
+    missing = ts - len(out)
+    print("Songs without recommendations:", missing)
+    duration = pd.Timestamp.now() - start_time
+    print(f"Time elapsed in rule generation: {duration}")
+    last_result = {"columns": columns, "itemsets": res, "rules": rules, "min_confidence": conf}
+    return out, f"min_support: {min_support} \tmissing songs: {missing} \ttime: {duration}", (missing, duration)
+
+
+def most_frequent_tracks(columns: Sequence[str], occurrences) -> List[dict]:
+    """(f3) ``get_most_frequent_tracks`` (main.py:168-175) from the level-1 kernel's output:
+    the reference counts ROWS per track_name (``group_by("track_name").agg(count)``, repeats
+    inside a playlist included), which is exactly the occurrence histogram K_hist produces
+    (``Prepared.occurrences``). Sorted by count descending (ties by name, the reference's tie
+    order is unspecified). ``filter_best_tracks`` (main.py:177-184) then keeps a prefix."""
+    occ = np.asarray(occurrences.cpu() if hasattr(occurrences, "cpu") else occurrences)
+    order = sorted(range(len(columns)), key=lambda i: (-int(occ[i]), columns[i]))
+    return [{"track_name": columns[i], "count": int(occ[i])} for i in order if occ[i] > 0]
+
+
+def sweep_supports(playlist_dict: dict, supports: Iterable[float], total_songs=None) -> pd.DataFrame:
+    """(f4) The reference's support sweep (main.py:452-473: one full
+    ``calculate_and_save_fp_growth_fast`` per threshold, logging min_support,
+    songs_without_recommendations, duration) with the threshold-independent work done once: the
+    bitmap and the pair counts are built at the LOWEST support of the sweep and every threshold
+    mines on a suffix of their rows. Returns the reference's results frame."""
+    supports = [round(float(x), 3) for x in supports]
+    device = _device()
+    columns, offsets, ids = encode_transactions(list(playlist_dict.values()))
+    d_off = torch.from_numpy(offsets).to(device)
+    d_ids = torch.from_numpy(ids).to(device)
+    t_prep = pd.Timestamp.now()
+    prepared = miner.prepare(d_off, d_ids, len(columns), min(supports))
+    torch.cuda.synchronize()
+    prep_s = (pd.Timestamp.now() - t_prep).total_seconds()
+    ts = total_songs if total_songs is not None else (globals()["total_songs"] or len(columns))
+    rows = []
+    for s_ in supports:
+        t0 = pd.Timestamp.now()
+        res = miner.mine_csr(d_off, d_ids, len(columns), s_, prepared=prepared)
+        recs = recommendations_from_result(res, columns)
+        rows.append({"min_support": s_, "songs_without_recommendations": ts - len(recs),
+                     "duration": (pd.Timestamp.now() - t0).total_seconds(),
+                     "itemsets": res.n_itemsets})
+    out = pd.DataFrame(rows)
+    out.attrs["prepare_seconds"] = prep_s
+    return out
+
+
 def save_rules(path: str, result: Optional[dict] = None) -> None:
     """Write the extra rule artifact: a dict of plain-Python columns ``antecedents``,
     ``consequents`` (tuples of names), ``support``, ``confidence``, ``lift`` (floats),

@@ -126,12 +126,105 @@ def _world(group):
     return dist.get_world_size(group)
 
 
+@dataclasses.dataclass
+class Prepared:
+    """Levels 1 and 2 of a playlist set up to the pair counts: everything that does not
+    depend on the threshold except through WHICH rows exist. Rows are in ascending-support
+    order, so the rows (and the pair sub-matrix) of any higher min_support are a suffix."""
+    n_playlists: int
+    t1: int
+    row_words: int
+    n_rows: int
+    bitmap: torch.Tensor                 # int32[n_rows * row_words]
+    counts1: torch.Tensor                # int32[n_rows] global supports, ascending
+    counts1_local: torch.Tensor          # this rank's part
+    row_items: torch.Tensor              # int32[n_rows]: row -> track id
+    occurrences: torch.Tensor            # int32[n_items]: rows of the input per track (with repeats)
+    pair: Optional[torch.Tensor]         # int32[n_rows * n_rows] global pair counts (upper triangle valid)
+    pair_local: Optional[torch.Tensor]
+
+
+def prepare(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
+            n_playlists_total: Optional[int] = None, group=None, pair_impl: str = "auto",
+            with_pairs: bool = True) -> Prepared:
+    """K_hist -> [allreduce] -> K0 encode -> K1 popcount -> [allreduce] -> K2 pair counts ->
+    [allreduce] for the tracks frequent at ``min_support``."""
+    dev = _Dev(offsets.device)
+    s = _stream()
+    n_local = int(offsets.numel()) - 1
+    nnz = int(items.numel())
+    if n_playlists_total is None:
+        n_playlists_total = n_local
+        if group is not None:
+            t = torch.tensor([n_local], dtype=torch.int64, device=dev.device)
+            _allreduce(t, group)
+            n_playlists_total = int(t.item())
+    n_total = int(n_playlists_total)
+    t1, _ = thresholds(min_support, n_total)
+    e32 = dev.empty(0, torch.int32)
+    occ = dev.empty(n_items, torch.int32)
+    _lib.call("kmls_item_histogram", items, nnz, n_items, occ, s, algo_bytes=4 * nnz)
+    _allreduce(occ, group)
+    row_words = int(_lib.value("kmls_bitmap_row_words", n_local))
+    cand = torch.nonzero(occ >= max(t1, 1)).reshape(-1)              # ascending track id
+    if cand.numel() == 0:
+        return Prepared(n_total, t1, row_words, 0, e32, e32, e32, e32, occ, None, None)
+    order = torch.argsort(occ[cand], stable=True)                    # by (occ, id)
+    cand = cand[order]
+    n_rows = int(cand.numel())
+    row_of_item = torch.full((n_items,), -1, dtype=torch.int32, device=dev.device)
+    row_of_item[cand] = torch.arange(n_rows, dtype=torch.int32, device=dev.device)
+    bitmap = dev.empty(n_rows * row_words, torch.int32)
+    _lib.call("kmls_encode_bitmap", offsets, items, n_local, row_of_item, n_items, n_rows,
+              bitmap, row_words, s, algo_bytes=4 * nnz + 8 * n_local + 4 * n_rows * row_words)
+    counts1 = dev.empty(n_rows, torch.int32)
+    _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s,
+              algo_bytes=4 * n_rows * row_words)
+    counts1_local = counts1.clone() if group is not None else counts1
+    _allreduce(counts1, group)
+    if not bool(torch.equal(counts1, occ[cand])):
+        # some playlist repeated a track: exact supports differ from the occurrence counts,
+        # so drop rows that fell below T1 and restore ascending-support order
+        keep = torch.nonzero(counts1 >= max(t1, 1)).reshape(-1)
+        order = torch.argsort(counts1[keep], stable=True)
+        src = keep[order].to(torch.int32)
+        n_rows = int(src.numel())
+        if n_rows == 0:
+            return Prepared(n_total, t1, row_words, 0, e32, e32, e32, e32, occ, None, None)
+        bitmap2 = dev.empty(n_rows * row_words, torch.int32)
+        _lib.call("kmls_gather_rows", bitmap, src, n_rows, row_words, bitmap2, s)
+        same = counts1_local is counts1
+        bitmap, counts1, cand = bitmap2, counts1[src.long()].contiguous(), cand[src.long()]
+        counts1_local = counts1 if same else counts1_local[src.long()].contiguous()
+    row_items = cand.to(torch.int32)
+    pair = pair_local = None
+    if with_pairs and n_rows >= 2:
+        pair = dev.empty(n_rows * n_rows, torch.int32)
+        if pair_impl == "auto":
+            # tensor cores once there are enough 128x256 tiles and playlists to feed them
+            pair_impl = "i8" if (n_rows >= 256 and row_words >= 512) else "popc"
+        if pair_impl == "popc":
+            _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
+        elif pair_impl == "i8":
+            gbytes = int(_lib.value("kmls_pair_gemm_scratch_bytes", n_rows, row_words))
+            gscratch = dev.empty((gbytes + 7) // 8, torch.int64)
+            _lib.call("kmls_pair_counts_i8", bitmap, n_rows, row_words, pair, gscratch, gbytes, s,
+                      algo_bytes=n_rows * (n_rows + 1) * n_local)   # = int8 ops: 2 * N * F(F+1)/2
+            del gscratch
+        else:
+            raise ValueError(f"unknown pair_impl {pair_impl!r}")
+        pair_local = pair.clone() if group is not None else pair
+        _allreduce(pair, group)
+    return Prepared(n_total, t1, row_words, n_rows, bitmap, counts1, counts1_local, row_items, occ,
+                    pair, pair_local)
+
+
 def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
              n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
              pair_impl: str = "auto", count_impl: str = "projected",
              prune: Optional[bool] = None, first_projection: str = "gather",
-             keep_words: Optional[int] = None) -> MineResult:
+             keep_words: Optional[int] = None, prepared: Optional["Prepared"] = None) -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
@@ -177,66 +270,37 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     if n_total == 0 or n_items == 0:
         return result(empty_i32, [])
 
-    # ---- level 1 -------------------------------------------------------------------------
-    occ = dev.empty(n_items, torch.int32)
-    _lib.call("kmls_item_histogram", items, nnz, n_items, occ, s, algo_bytes=4 * nnz)
-    _allreduce(occ, group)
-    cand = torch.nonzero(occ >= max(t1, 1)).reshape(-1)              # ascending track id
-    if cand.numel() == 0:
+    # ---- levels 1 and 2 up to the pair counts (reusable across thresholds, see prepare()) ---
+    if prepared is None:
+        prepared = prepare(offsets, items, n_items, min_support, n_playlists_total=n_total,
+                           group=group, pair_impl=pair_impl, with_pairs=max_len is None or max_len > 1)
+    elif prepared.t1 > t1 or prepared.n_playlists != n_total:
+        raise ValueError("`prepared` was built for a higher min_support or another playlist set")
+    stats["row_words"] = row_words = prepared.row_words
+    # rows are in ascending-support order: the rows frequent at this threshold are a suffix
+    r0 = int(torch.searchsorted(prepared.counts1, torch.tensor([max(t1, 1)], dtype=torch.int32,
+                                                               device=dev.device)).item())
+    n_rows = prepared.n_rows - r0
+    if n_rows <= 0:
         return result(empty_i32, [])
-    order = torch.argsort(occ[cand], stable=True)                    # by (occ, id)
-    cand = cand[order]
-    n_rows = int(cand.numel())
-    row_of_item = torch.full((n_items,), -1, dtype=torch.int32, device=dev.device)
-    row_of_item[cand] = torch.arange(n_rows, dtype=torch.int32, device=dev.device)
-    row_words = int(_lib.value("kmls_bitmap_row_words", n_local))
-    bitmap = dev.empty(n_rows * row_words, torch.int32)
-    _lib.call("kmls_encode_bitmap", offsets, items, n_local, row_of_item, n_items, n_rows,
-              bitmap, row_words, s, algo_bytes=4 * nnz + 8 * n_local + 4 * n_rows * row_words)
-    counts1 = dev.empty(n_rows, torch.int32)
-    _lib.call("kmls_row_popcount", bitmap, n_rows, row_words, counts1, s,
-              algo_bytes=4 * n_rows * row_words)
-    counts1_local_box = [counts1.clone() if group is not None else counts1]
-    _allreduce(counts1, group)
-    if not bool(torch.equal(counts1, occ[cand])):
-        # some playlist repeated a track: exact supports differ from the occurrence counts,
-        # so drop rows that fell below T1 and restore ascending-support order
-        keep = torch.nonzero(counts1 >= max(t1, 1)).reshape(-1)
-        order = torch.argsort(counts1[keep], stable=True)
-        src = keep[order].to(torch.int32)
-        n_rows = int(src.numel())
-        if n_rows == 0:
-            return result(empty_i32, [])
-        bitmap2 = dev.empty(n_rows * row_words, torch.int32)
-        _lib.call("kmls_gather_rows", bitmap, src, n_rows, row_words, bitmap2, s)
-        bitmap, counts1, cand = bitmap2, counts1[src.long()].contiguous(), cand[src.long()]
-        counts1_local_box[0] = counts1_local_box[0][src.long()].contiguous()
-    row_items = cand.to(torch.int32)
+    bitmap = prepared.bitmap[r0 * row_words:]
+    counts1 = prepared.counts1[r0:]
+    counts1_local = prepared.counts1_local[r0:]
+    row_items = prepared.row_items[r0:]
     lvl1_items = torch.arange(n_rows, dtype=torch.int32, device=dev.device).reshape(-1, 1)
     levels = [(lvl1_items, counts1)]
     stats["levels"].append({"k": 1, "candidates": n_items, "frequent": n_rows})
-    stats["row_words"] = row_words
     if n_rows < 2 or (max_len is not None and max_len <= 1):
         return result(row_items, levels)
-
-    # ---- level 2 -------------------------------------------------------------------------
-    counts1_local = counts1_local_box[0]
-    pair = dev.empty(n_rows * n_rows, torch.int32)
-    if pair_impl == "auto":
-        # tensor cores once there are enough 128x256 tiles and playlists to feed them
-        pair_impl = "i8" if (n_rows >= 256 and row_words >= 512) else "popc"
-    if pair_impl == "popc":
-        _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
-    elif pair_impl == "i8":
-        gbytes = int(_lib.value("kmls_pair_gemm_scratch_bytes", n_rows, row_words))
-        gscratch = dev.empty((gbytes + 7) // 8, torch.int64)
-        _lib.call("kmls_pair_counts_i8", bitmap, n_rows, row_words, pair, gscratch, gbytes, s,
-                  algo_bytes=n_rows * (n_rows + 1) * n_local)   # = int8 ops: 2 * N * F(F+1)/2
-        del gscratch
+    if prepared.pair is None:
+        raise ValueError("`prepared` holds no pair counts (built with with_pairs=False)")
+    if r0 == 0:
+        pair, pair_local = prepared.pair, prepared.pair_local
     else:
-        raise ValueError(f"unknown pair_impl {pair_impl!r}")
-    pair_local = pair.clone() if group is not None else pair
-    _allreduce(pair, group)
+        full = prepared.n_rows
+        pair = prepared.pair.view(full, full)[r0:, r0:].contiguous().view(-1)
+        pair_local = pair if prepared.pair_local is prepared.pair else \
+            prepared.pair_local.view(full, full)[r0:, r0:].contiguous().view(-1)
     thr = tk
     if t1 < tk:
         # mlxtend's root single-path shortcut applies no Tk test:
