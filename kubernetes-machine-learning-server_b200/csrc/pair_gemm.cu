@@ -122,10 +122,17 @@ k_bits_kblock_major(const uint32_t* __restrict__ bitmap, int32_t n_rows, int32_t
 // The GEMM. grid = (tiles of 256 B-rows, tiles of 128 A-rows); one tile per CTA, one CTA per SM.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kGThreads, 1)
-k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_pad, int64_t n_kb,
-               int32_t* __restrict__ C) {
+k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_pad, int64_t n_kb_total,
+               int64_t kb_per_split, int32_t* __restrict__ C) {
   const int tj = blockIdx.x, ti = blockIdx.y;
   if (tj * kGN + (kGN - 1) < ti * kGM) return;  // tile entirely below the diagonal
+  // blockIdx.z selects a slice of the playlist dimension; with more than one slice the
+  // epilogue accumulates into a zeroed C with atomic adds
+  const int64_t kb0 = (int64_t)blockIdx.z * kb_per_split;
+  const int64_t n_kb = min(kb_per_split, n_kb_total - kb0);
+  if (n_kb <= 0) return;
+  const bool split = gridDim.z > 1;
+  bits_km += kb0 * rows_pad;
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -267,7 +274,10 @@ k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_p
           const int col0 = tj * kGN + c0;
 #pragma unroll
           for (int t = 0; t < 32; ++t)
-            if (col0 + t < n_rows) crow[col0 + t] = (int32_t)v[t];
+            if (col0 + t < n_rows) {
+              if (split) atomicAdd(crow + col0 + t, (int32_t)v[t]);
+              else crow[col0 + t] = (int32_t)v[t];
+            }
         }
       }
       tc_fence_before();
@@ -312,8 +322,25 @@ extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int
     KMLS_LAUNCHED("k_bits_kblock_major");
   }
   KMLS_CUDA(cudaFuncSetAttribute(k_pair_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
-  dim3 grid((unsigned)(rows_pad / kGN), (unsigned)(rows_pad / kGM));
-  k_pair_gemm_i8<<<grid, kGThreads, kGSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb, d_pair);
+  // One tile per CTA and one CTA per SM: split the playlist dimension when the last wave of
+  // tiles would leave most SMs idle (or when there are fewer tiles than SMs).
+  const int tx = rows_pad / kGN, ty = rows_pad / kGM;
+  int64_t tiles = 0;
+  for (int i = 0; i < ty; ++i)
+    for (int j = 0; j < tx; ++j) tiles += (j * kGN + (kGN - 1) >= i * kGM);
+  const int sms = num_sms();
+  int ksplit = 1;
+  for (int ks = 1; ks <= 16; ks *= 2) {
+    if (n_kb / ks < 128 && ks > 1) break;
+    ksplit = ks;
+    const int64_t units = tiles * ks, waves = (units + sms - 1) / sms;
+    if ((double)units / (double)(waves * sms) >= 0.93) break;
+  }
+  const int64_t kb_per_split = (n_kb + ksplit - 1) / ksplit;
+  if (ksplit > 1) KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
+  dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)ksplit);
+  k_pair_gemm_i8<<<grid, kGThreads, kGSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb,
+                                                      kb_per_split, d_pair);
   KMLS_LAUNCHED("k_pair_gemm_i8");
   return 0;
 }

@@ -148,7 +148,10 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
       const int32_t* x = itemset_ptr(a, k, lvl_first + lvl_begin + j);
       int d = 0;
       if (head != nullptr) {
-        while (d < k - 1 && __ldg(x + d) == __ldg(head + d)) ++d;
+        // first prefix position that differs from the table owner's: one parallel compare
+        const bool ne = lane < k - 1 && __ldg(x + lane) != __ldg(head + lane);
+        const uint32_t nm = __ballot_sync(0xffffffffu, ne);
+        d = nm ? __ffs(nm) - 1 : k - 1;
       }
       if (head == nullptr || d < k - 1) {
         for (int h = d; h < k - 1; ++h) {
