@@ -209,11 +209,13 @@ int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_words, const 
  * unused). d_par[g - level_sizes[1]] = index, inside level k-1, of the parent (itemset
  * without its last member) of the itemset with global id g (sizes >= 2 only).
  *
- * Exact subset index: (parent global id, last member) -> (global id, count), 16-byte slots,
- * capacity a power of two >= 2 * (number of itemsets of size >= 2), 16-byte aligned. */
+ * Exact subset index: one 16-byte node per itemset (all levels, indexed by global id):
+ * {global id of its first child, number of children, last member, count}. The children of an
+ * itemset (it plus one later member) are contiguous in the next level because the tables are
+ * sorted. d_nodes: (total number of itemsets) * 16 bytes, 16-byte aligned. */
 int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
-                          const int64_t* level_sizes, int32_t max_k, void* d_slots,
-                          int64_t capacity, kmls_stream_t stream);
+                          const int64_t* level_sizes, int32_t max_k, void* d_nodes,
+                          kmls_stream_t stream);
 /* (antecedent, consequent) splits examined per k-itemset = 2^(k-1) - 1 (each yields up to
  * two rules); -1 if k is not supported (k > 15). */
 int64_t kmls_rules_parts_per_itemset(int32_t k);
@@ -223,9 +225,8 @@ int64_t kmls_rules_parts_per_itemset(int32_t k);
  * counts failed subset lookups (0 for a downward-closed table; caller zeroes it). */
 int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
                      int32_t max_k, int32_t k, int64_t lvl_begin, int64_t lvl_count,
-                     const void* d_slots, int64_t capacity, int64_t n_playlists_total,
-                     double min_confidence, void* d_part, int32_t* d_rule_cnt, int32_t* d_missing,
-                     kmls_stream_t stream);
+                     const void* d_nodes, int64_t n_playlists_total, double min_confidence,
+                     void* d_part, int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
 /* Pass 2: d_rule_off[lvl_count] = first output slot of each itemset (exclusive scan of the
  * kept counts over everything this rank emits). Rule r: itemset d_out_itemset[r] (global
  * id), antecedent = members selected by the bits of d_out_antecedent[r] (bit t = t-th

@@ -46,9 +46,9 @@ SIGNATURES = {
     "kmls_project_rows": (ctypes.c_int, [_P, _P, _P, _P, _P, _I64, _P, _P, _P, _I32, _P]),
     "kmls_row_tidlists": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _P]),
     "kmls_project_rows_gather": (ctypes.c_int, [_P, _I64, _P, _P, _I64, _P, _P, _P, _P, _I64, _P]),
-    "kmls_trie_index_build": (ctypes.c_int, [_P, _P, _P, _P, _I32, _P, _I64, _P]),
+    "kmls_trie_index_build": (ctypes.c_int, [_P, _P, _P, _P, _I32, _P, _P]),
     "kmls_rules_parts_per_itemset": (_I64, [_I32]),
-    "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _I64, _I64, _P, _I64, _I64, _F64, _P, _P,
+    "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _I64, _I64, _P, _I64, _F64, _P, _P,
                                         _P, _P]),
     "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P,
                                         _P, _P, _P]),

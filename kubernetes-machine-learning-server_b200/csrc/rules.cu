@@ -10,12 +10,15 @@
 // rounded supports), so the doubles are bit-identical, not merely within 1e-12.
 //
 // Subset counts come from an EXACT index, not from fingerprints: the level tables form a
-// trie (an itemset's parent is the itemset without its last member), and the index maps the
-// 64-bit key (parent global id, last member) to (global id, count) - one 16-byte slot, one
-// 32-byte sector per probe, nothing to verify. A warp that owns a class (siblings sharing
-// the prefix P) first resolves all 2^(k-1) subsets of P by dynamic programming over that
-// index (subset = smaller subset + its largest member) into shared memory, then needs ONE
-// probe per (sibling, antecedent): the consequent's count.
+// trie (an itemset's parent is the itemset without its last member) and, the tables being
+// sorted, the children of a node are CONTIGUOUS in the next level. The index is one 16-byte
+// node per itemset, {first child's global id, number of children, last member, count};
+// "child of p with last member x" = read node[p], then search x among its few children.
+// Unlike a hash table this keeps everything a class needs close together: siblings (P, x_1),
+// (P, x_2), ... walk the SAME child lists of the subsets of P, so their reads hit L1/L2.
+// A warp that owns a class first resolves all 2^(k-1) subsets of P by dynamic programming
+// over that index (subset = smaller subset + its largest member) into shared memory, then
+// needs ONE lookup per (sibling, antecedent): the consequent's count.
 //
 // All levels' tables live in one arena: items of level k start at item_off[k], its itemsets
 // have global ids id_off[k] .. id_off[k+1]-1, counts are indexed by global id; `par` holds,
@@ -43,47 +46,54 @@ __device__ __forceinline__ const int32_t* itemset_ptr(const Arena& a, int k, int
   return a.items + a.item_off[k] + (gid - a.id_off[k]) * k;
 }
 
-__device__ __forceinline__ uint64_t edge_key(int32_t parent_gid, int32_t item) {
-  return ((uint64_t)(uint32_t)parent_gid << 32) | (uint32_t)item;
-}
-constexpr unsigned long long kEmptyEdge = ~0ull;
-// slot of a key; `mask` = capacity - 1 (capacity a power of two). A full 64-bit mixer: the
-// keys are highly structured (small item ids, dense parent ids) and linear probing needs a
-// hash without clustering (a plain multiplicative hash made probe chains 7x longer).
-__device__ __forceinline__ uint64_t edge_slot(uint64_t key, uint64_t mask) {
-  return mix64(key) & mask;
-}
-
-// slot = {key lo, key hi, child global id, child count}
-__global__ void __launch_bounds__(256) k_trie_build(Arena a, uint4* __restrict__ slots, uint64_t mask) {
-  const int64_t first = a.id_off[2], n = a.id_off[a.max_k + 1];
-  for (int64_t gid = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < n;
+// node = {first child gid, number of children, last member, count}
+__global__ void __launch_bounds__(256) k_trie_build(Arena a, int4* __restrict__ node) {
+  const int64_t n = a.id_off[a.max_k + 1];
+  for (int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < n;
        gid += (int64_t)gridDim.x * blockDim.x) {
-    int k = 2;
+    int k = 1;
     while (gid >= a.id_off[k + 1]) ++k;
-    const int32_t parent = (int32_t)(a.id_off[k - 1] + __ldg(a.par + (gid - first)));
     const int32_t last = __ldg(itemset_ptr(a, k, gid) + (k - 1));
-    const uint64_t key = edge_key(parent, last);
-    uint64_t h = edge_slot(key, mask);
-    while (atomicCAS(reinterpret_cast<unsigned long long*>(slots + h), kEmptyEdge,
-                     (unsigned long long)key) != kEmptyEdge)
-      h = (h + 1) & mask;
-    reinterpret_cast<int2*>(slots + h)[1] = make_int2((int32_t)gid, __ldg(a.counts + gid));
+    // children: the run of level k+1 whose parent index is this itemset's index in level k;
+    // found by a binary search for the run's start in the (sorted) parent column
+    int32_t first = 0, cnt = 0;
+    if (k < a.max_k) {
+      const int64_t me = gid - a.id_off[k];
+      const int32_t* par = a.par + (a.id_off[k + 1] - a.id_off[2]);
+      const int64_t m = a.id_off[k + 2] - a.id_off[k + 1];
+      int64_t lo = 0, hi = m;
+      while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(par + mid) < me) lo = mid + 1; else hi = mid;
+      }
+      int64_t e = lo;
+      while (e < m && __ldg(par + e) == me) ++e;
+      first = (int32_t)(a.id_off[k + 1] + lo);
+      cnt = (int32_t)(e - lo);
+    }
+    node[gid] = make_int4(first, cnt, last, __ldg(a.counts + gid));
   }
 }
 
-// (child gid, child count) of the edge (parent_gid, item); gid = -1 if absent.
-__device__ __forceinline__ int2 trie_child(const uint4* __restrict__ slots, uint64_t mask,
-                                           int32_t parent_gid, int32_t item) {
-  const uint64_t key = edge_key(parent_gid, item);
-  uint64_t h = edge_slot(key, mask);
-  while (true) {
-    const uint4 s = __ldg(slots + h);
-    const uint64_t sk = ((uint64_t)s.y << 32) | s.x;
-    if (sk == key) return make_int2((int32_t)s.z, (int32_t)s.w);
-    if (sk == kEmptyEdge) return make_int2(-1, -1);
-    h = (h + 1) & mask;
+// (child gid, child count) of the child of `parent_gid` whose last member is `item`;
+// gid = -1 if absent. Children are sorted by last member.
+__device__ __forceinline__ int2 trie_child(const int4* __restrict__ node, int32_t parent_gid,
+                                           int32_t item) {
+  if (parent_gid < 0) return make_int2(-1, -1);
+  const int4 p = __ldg(node + parent_gid);
+  int lo = 0, hi = p.y;
+  while (hi - lo > 4) {                      // long child lists: bisect down to 4 candidates
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(node + p.x + mid).z <= item) lo = mid; else hi = mid;
   }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (lo + i < hi) {
+      const int4 c = __ldg(node + p.x + lo + i);
+      if (c.z == item) return make_int2(p.x + lo + i, c.w);
+    }
+  }
+  return make_int2(-1, -1);
 }
 
 struct RuleVals {
@@ -125,8 +135,8 @@ __device__ __forceinline__ bool conf_keep(int32_t cx, int32_t ca, double s_x, do
 constexpr int kRuleChunkMax = 64;   // consecutive itemsets handled by one warp (at most)
 
 __global__ void __launch_bounds__(256, 4)
-k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4* __restrict__ slots,
-              uint64_t mask, double n_total, double min_conf, int chunk, int2* __restrict__ part,
+k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* __restrict__ node,
+              double n_total, double min_conf, int chunk, int2* __restrict__ part,
               int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
   extern __shared__ int32_t smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -143,34 +153,46 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
   for (int64_t ch = (int64_t)blockIdx.x * nwarps + warp; ch < n_chunks;
        ch += (int64_t)gridDim.x * nwarps) {
     const int64_t j_end = min(lvl_count, (ch + 1) * chunk);
-    const int32_t* head = nullptr;         // prefix owner whose subsets are in the table
-    for (int64_t j = ch * chunk; j < j_end; ++j) {
-      const int32_t* x = itemset_ptr(a, k, lvl_first + lvl_begin + j);
+    // Lane t holds member t of the current itemset; the next itemset's members and count are
+    // fetched one iteration ahead so that only the index probes expose memory latency.
+    const int64_t j0 = ch * chunk;
+    const int32_t* items_lvl = a.items + a.item_off[k] + lvl_begin * k;
+    const int32_t* counts_lvl = a.counts + lvl_first + lvl_begin;
+    int32_t nx_item = lane < k ? __ldg(items_lvl + j0 * k + lane) : 0;
+    int32_t nx_cnt = __ldg(counts_lvl + j0);
+    int32_t head_item = -1;                // member `lane` of the prefix whose subsets are in the table
+    bool have_head = false;
+    for (int64_t j = j0; j < j_end; ++j) {
+      const int32_t my_item = nx_item;
+      const int32_t c_x = nx_cnt;
+      if (j + 1 < j_end) {
+        nx_item = lane < k ? __ldg(items_lvl + (j + 1) * k + lane) : 0;
+        nx_cnt = __ldg(counts_lvl + j + 1);
+      }
       int d = 0;
-      if (head != nullptr) {
+      if (have_head) {
         // first prefix position that differs from the table owner's: one parallel compare
-        const bool ne = lane < k - 1 && __ldg(x + lane) != __ldg(head + lane);
-        const uint32_t nm = __ballot_sync(0xffffffffu, ne);
+        const uint32_t nm = __ballot_sync(0xffffffffu, lane < k - 1 && my_item != head_item);
         d = nm ? __ffs(nm) - 1 : k - 1;
       }
-      if (head == nullptr || d < k - 1) {
+      if (!have_head || d < k - 1) {
         for (int h = d; h < k - 1; ++h) {
-          const int32_t ph = __ldg(x + h);
+          const int32_t ph = __shfl_sync(0xffffffffu, my_item, h);
           for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
             const int rest = m ^ (1 << h);
             int2 gc;
             if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));   // level-1 id = row index
-            else gc = trie_child(slots, mask, tab_gid[rest], ph);
+            else gc = trie_child(node, tab_gid[rest], ph);
             if (gc.x < 0) atomicAdd(missing, 1);
             tab_gid[m] = gc.x;
             tab_cnt[m] = gc.y;
           }
           __syncwarp();
         }
-        head = x;
+        head_item = my_item;
+        have_head = true;
       }
-      const int32_t last = __ldg(x + (k - 1));
-      const int32_t c_x = __ldg(a.counts + lvl_first + lvl_begin + j);
+      const int32_t last = __shfl_sync(0xffffffffu, my_item, k - 1);
       const double s_x = __ddiv_rn((double)c_x, n_total);
       int kept = 0;
       // kRuleIlp antecedent masks per lane and iteration: their first index probes are all
@@ -178,9 +200,9 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
       for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
         int am[kRuleIlp];
         int32_t cc[kRuleIlp];
-        uint64_t key[kRuleIlp], h[kRuleIlp];
-        uint4 slot[kRuleIlp];
+        int4 pn[kRuleIlp];
         bool probe[kRuleIlp];
+        // phase 1: the parents' nodes of kRuleIlp lookups (independent loads)
 #pragma unroll
         for (int u = 0; u < kRuleIlp; ++u) {
           am[u] = a0 + u * 32 + lane;
@@ -190,24 +212,28 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const uint4*
             const int rest = (n_sub - 1) ^ am[u];
             if (rest == 0) {
               cc[u] = __ldg(a.counts + last);
-            } else {
-              key[u] = edge_key(tab_gid[rest], last);
-              h[u] = edge_slot(key[u], mask);
-              slot[u] = __ldg(slots + h[u]);
+            } else if (tab_gid[rest] >= 0) {
+              pn[u] = __ldg(node + tab_gid[rest]);
               probe[u] = true;
             }
           }
         }
+        // phase 2: search `last` among each parent's children
 #pragma unroll
         for (int u = 0; u < kRuleIlp; ++u) {
           if (probe[u]) {
-            while (true) {
-              const uint64_t sk = ((uint64_t)slot[u].y << 32) | slot[u].x;
-              if (sk == key[u]) { cc[u] = (int32_t)slot[u].w; break; }
-              if (sk == kEmptyEdge) break;
-              h[u] = (h[u] + 1) & mask;
-              slot[u] = __ldg(slots + h[u]);
+            int lo = 0, hi = pn[u].y;
+            while (hi - lo > 4) {
+              const int mid = (lo + hi) >> 1;
+              if (__ldg(node + pn[u].x + mid).z <= last) lo = mid; else hi = mid;
             }
+            int4 c[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              c[i] = lo + i < hi ? __ldg(node + pn[u].x + lo + i) : make_int4(0, 0, -1, -1);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (c[i].z == last) cc[u] = c[i].w;
           }
         }
 #pragma unroll
@@ -300,21 +326,16 @@ using namespace kmls;
 
 extern "C" int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_counts,
                                      const int32_t* d_par, const int64_t* level_sizes,
-                                     int32_t max_k, void* d_slots, int64_t capacity,
-                                     kmls_stream_t stream) {
+                                     int32_t max_k, void* d_nodes, kmls_stream_t stream) {
   Arena a;
   int rc = make_arena(a, d_items, d_counts, d_par, level_sizes, max_k);
   if (rc) return rc;
-  const int64_t n = a.id_off[max_k + 1] - a.id_off[2];
-  KMLS_REQUIRE(capacity >= 2 * n && capacity > 0 && (capacity & (capacity - 1)) == 0,
-               "kmls_trie_index_build: capacity must be a power of two >= 2n");
-  KMLS_REQUIRE(d_slots && ((uintptr_t)d_slots & 15) == 0, "kmls_trie_index_build: d_slots must be 16-byte aligned");
-  cudaStream_t s = (cudaStream_t)stream;
-  KMLS_CUDA(cudaMemsetAsync(d_slots, 0xFF, sizeof(uint4) * (size_t)capacity, s));
-  if (max_k < 2 || n <= 0) return 0;
-  KMLS_REQUIRE(d_par, "kmls_trie_index_build: d_par is null");
+  const int64_t n = a.id_off[max_k + 1];
+  if (n <= 0) return 0;
+  KMLS_REQUIRE(d_nodes && ((uintptr_t)d_nodes & 15) == 0, "kmls_trie_index_build: d_nodes must be 16-byte aligned");
+  KMLS_REQUIRE(max_k < 2 || d_par, "kmls_trie_index_build: d_par is null");
   int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
-  k_trie_build<<<grid, 256, 0, s>>>(a, (uint4*)d_slots, (uint64_t)capacity - 1);
+  k_trie_build<<<grid, 256, 0, (cudaStream_t)stream>>>(a, (int4*)d_nodes);
   KMLS_LAUNCHED("k_trie_build");
   return 0;
 }
@@ -325,8 +346,8 @@ extern "C" int64_t kmls_rules_parts_per_itemset(int32_t k) {
 
 extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
                                 const int64_t* level_sizes, int32_t max_k, int32_t k,
-                                int64_t lvl_begin, int64_t lvl_count, const void* d_slots,
-                                int64_t capacity, int64_t n_playlists_total, double min_confidence,
+                                int64_t lvl_begin, int64_t lvl_count, const void* d_nodes,
+                                int64_t n_playlists_total, double min_confidence,
                                 void* d_part, int32_t* d_rule_cnt, int32_t* d_missing,
                                 kmls_stream_t stream) {
   Arena a;
@@ -338,8 +359,7 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
   KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
                "kmls_rules_count: itemset range out of bounds");
   if (lvl_count == 0) return 0;
-  KMLS_REQUIRE(d_slots && capacity > 0 && (capacity & (capacity - 1)) == 0 && d_part && d_rule_cnt && d_missing,
-               "kmls_rules_count: bad index or null pointer");
+  KMLS_REQUIRE(d_nodes && d_part && d_rule_cnt && d_missing, "kmls_rules_count: null pointer");
   const size_t per_warp = sizeof(int32_t) * 2 * ((size_t)1 << (k - 1));
   int warps = (int)std::min<size_t>(8, (200 * 1024) / per_warp);
   KMLS_REQUIRE(warps >= 1, "kmls_rules_count: subset table does not fit in shared memory");
@@ -350,8 +370,8 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
   const int64_t n_chunks = (lvl_count + chunk - 1) / chunk;
   int grid = (int)std::min<int64_t>((n_chunks + warps - 1) / warps, (int64_t)num_sms() * 32);
   k_rules_count<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(
-      a, k, lvl_begin, lvl_count, (const uint4*)d_slots, (uint64_t)capacity - 1,
-      (double)n_playlists_total, min_confidence, chunk, (int2*)d_part, d_rule_cnt, d_missing);
+      a, k, lvl_begin, lvl_count, (const int4*)d_nodes, (double)n_playlists_total, min_confidence,
+      chunk, (int2*)d_part, d_rule_cnt, d_missing);
   KMLS_LAUNCHED("k_rules_count");
   return 0;
 }

@@ -483,11 +483,10 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     arena_counts = torch.cat([ct for _, ct in res.levels])
     arena_par = torch.cat(res.parents)
     n_x_all = n_all - int(sizes[1])
-    cap = int(_lib.value("kmls_set_capacity", n_x_all))
-    slots = dev.empty(cap * 2, torch.int64)
+    nodes = dev.empty(n_all * 2, torch.int64)          # 16 bytes per itemset
     sizes_ptr = sizes.ctypes.data
     _lib.call("kmls_trie_index_build", arena_items, arena_counts, arena_par, sizes_ptr, max_k,
-              slots, cap, s)
+              nodes, s)
     # slice boundaries by work (2^(k-1) splits per k-itemset), not by itemset count, so
     # that the ranks of a multi-GPU job get rule tables of similar size
     def boundary(frac_num, frac_den):
@@ -518,7 +517,7 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
         lvl_start += int(sizes[k])
     for k, lvl_begin, cnt, out0, part_buf in plan:
         _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
-                  slots, cap, res.n_playlists, float(min_confidence), part_buf, rule_cnt[out0:],
+                  nodes, res.n_playlists, float(min_confidence), part_buf, rule_cnt[out0:],
                   missing, s)
     scratch, sbytes = dev.scan_scratch(n_x)
     rule_off = dev.empty(n_x + 1, torch.int64)
