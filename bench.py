@@ -329,7 +329,7 @@ def run_gpu(args):
     peak, peak_src = (peaks["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs") if "hbm_gbs" in peaks else \
         (6650.0, "fallback of B200_PROFILING.md")
     # Roofline objects. Algorithmic work per launch:
-    #   k_rules_count  16 B per index probe + 8 B per (itemset, antecedent) split written
+    #   k_rules_count  32 B per index lookup (parent node + child entry) + 8 B per (itemset, antecedent) split written
     #   k_rules_write  8 B per split read + 32 B per rule written
     #   k_pair_gemm_i8 2 * N * F(F+1)/2 int8 ops (upper triangle incl. diagonal)
     #   others         the bytes the caller annotates (miner.py, algo_bytes=...)
@@ -340,7 +340,7 @@ def run_gpu(args):
     probes = sum(classes[k] * max((1 << (k - 1)) - k, 0) + n * max((1 << (k - 1)) - 2, 0)
                  for k, n in enumerate(lv_sizes, start=1) if k >= 2 and k < len(classes) + 0)
     algo = {
-        "kmls_rules_count": (16 * probes + 8 * splits) / max(world, 1),
+        "kmls_rules_count": (32 * probes + 8 * splits) / max(world, 1),
         "kmls_rules_write": (8 * splits) / max(world, 1) + 32 * (info.get("rules_this_rank") or 0),
     }
 
