@@ -18,6 +18,8 @@
 // Operand traffic: the bit slices come from a K-block-major copy of the bitmap made by
 // k_bits_kblock_major (one pass, 2 * F * W bytes), so every stage is two contiguous bulk
 // copies. Useful work: 2 * N * F(F+1)/2 int8 ops.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kmls_b200.h"
 
@@ -290,6 +292,222 @@ k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_p
   }
 }
 
+
+// ---------------------------------------------------------------------------------------
+// Variant with the A operand in tensor memory ("TS"). In the kernel above every stage writes
+// 48 KB of int8 into shared memory and the tensor core reads the same 48 KB back: 96 KB per
+// 524-cycle stage against a 128 B/cycle shared-memory port, i.e. the port, not the tensor
+// pipe, sets the pace. Here the 128 A rows are expanded into REGISTERS and stored to TMEM
+// with tcgen05.st (lane = row, 32 columns of 4 int8 per stage); only the 256 B rows go through
+// shared memory (32 KB written + 32 KB read per stage).
+//   warp 0        TMA producer (bit slices)          warp 1      MMA issuer (A from TMEM)
+//   warps 4-7     A expanders (quadrant = warp % 4) and, at the end, the epilogue
+//   warps 2,3,8-13  B expanders (as above)
+// TMEM: columns 0-255 accumulators, 256 + 32*stage: the stage's A tile.
+// ---------------------------------------------------------------------------------------
+constexpr int kTBWarps = 8;                                  // B expander warps
+constexpr int kTThreads = 32 * 14;
+constexpr int kTStages = 4;
+constexpr int kTOpBytes = kGN * kGKBytes;                    // 32 KB of int8 (B only) per stage
+constexpr int kTSmemBytes = kTStages * (kTOpBytes + kGBitBytes) + 1024 + 256;
+
+__device__ __forceinline__ void tc_mma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+__global__ void __launch_bounds__(kTThreads, 1)
+k_pair_gemm_i8_ts(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_pad, int64_t n_kb_total,
+                  int64_t kb_per_split, int32_t* __restrict__ C) {
+  const int tj = blockIdx.x, ti = blockIdx.y;
+  if (tj * kGN + (kGN - 1) < ti * kGM) return;
+  const int64_t kb0 = (int64_t)blockIdx.z * kb_per_split;
+  const int64_t n_kb = min(kb_per_split, n_kb_total - kb0);
+  if (n_kb <= 0) return;
+  const bool split = gridDim.z > 1;
+  bits_km += kb0 * rows_pad;
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t op_base = base;                                  // stages of B (32 KB)
+  const uint32_t bit_base = base + kTStages * kTOpBytes;          // stages of [A 2 KB | B 4 KB] bits
+  const uint32_t bar_base = bit_base + kTStages * kGBitBytes;
+  uint8_t* gen_base = smem_raw + (base - smem_u32(smem_raw));
+  auto bits_full = [&](int s) { return bar_base + 8u * s; };
+  auto bits_empty = [&](int s) { return bar_base + 8u * (kTStages + s); };
+  auto op_full = [&](int s) { return bar_base + 8u * (2 * kTStages + s); };
+  auto op_empty = [&](int s) { return bar_base + 8u * (3 * kTStages + s); };
+  const uint32_t tmem_full = bar_base + 8u * (4 * kTStages);
+  const uint32_t tmem_slot = bar_base + 8u * (4 * kTStages + 1);
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen_base + (tmem_slot - base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < kTStages; ++s) {
+      mbar_init(bits_full(s), 1);
+      mbar_init(bits_empty(s), kTBWarps + 4);
+      mbar_init(op_full(s), kTBWarps + 4);
+      mbar_init(op_empty(s), 1);
+    }
+    mbar_init(tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(512) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_acc = *tmem_slot_gen;
+  const uint32_t tmem_a0 = tmem_acc + 256;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int64_t i = 0; i < n_kb; ++i) {
+        const int s = (int)(i % kTStages);
+        const uint32_t ph = (uint32_t)((i / kTStages) & 1);
+        mbar_wait(bits_empty(s), ph ^ 1u);
+        mbar_expect_tx(bits_full(s), kGBitBytes);
+        const uint4* src = bits_km + i * rows_pad;
+        const uint32_t dst = bit_base + s * kGBitBytes;
+        tma_bulk_g2s(dst, src + (int64_t)ti * kGM, kGM * 16, bits_full(s));
+        tma_bulk_g2s(dst + kGM * 16, src + (int64_t)tj * kGN, kGN * 16, bits_full(s));
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      for (int64_t i = 0; i < n_kb; ++i) {
+        const int s = (int)(i % kTStages);
+        const uint32_t ph = (uint32_t)((i / kTStages) & 1);
+        mbar_wait(op_full(s), ph);
+        tc_fence_after();
+        const uint64_t b_desc = smem_desc_k_sw128(op_base + s * kTOpBytes);
+#pragma unroll
+        for (int k = 0; k < kGKBytes / 32; ++k)   // 32 int8 of K = 8 TMEM columns of A = 32 bytes of B
+          tc_mma_i8_ts(tmem_acc, tmem_a0 + (uint32_t)(s * 32 + k * 8), b_desc + (uint64_t)(k * 2), kIdescI8,
+                       (i > 0 || k > 0) ? 1u : 0u);
+        tc_commit(op_empty(s));
+      }
+      tc_commit(tmem_full);
+    }
+  } else if (warp >= 4 && warp < 8) {
+    // ===== A expanders: row = 32 * quadrant + lane; 128 bits -> 32 columns of 4 int8 =====
+    const int q = warp & 3;
+    for (int64_t i = 0; i < n_kb; ++i) {
+      const int s = (int)(i % kTStages);
+      const uint32_t ph = (uint32_t)((i / kTStages) & 1);
+      mbar_wait(bits_full(s), ph);
+      mbar_wait(op_empty(s), ph ^ 1u);
+      const uint4 b = *reinterpret_cast<const uint4*>(gen_base + (bit_base - base) + s * kGBitBytes +
+                                                      (q * 32 + lane) * 16);
+      uint32_t v[32];
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        const uint32_t w = c < 8 ? b.x : c < 16 ? b.y : c < 24 ? b.z : b.w;
+        v[c] = (((w >> (4 * (c & 7))) & 0xFu) * 0x00204081u) & 0x01010101u;
+      }
+      const uint32_t taddr = tmem_a0 + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * 32);
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+          "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+          "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+          ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+            "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+            "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+            "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+          : "memory");
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(op_full(s));
+        mbar_arrive(bits_empty(s));
+      }
+    }
+    // ===== epilogue =====
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    const int row = ti * kGM + q * 32 + lane;
+    for (int c0 = 0; c0 < kGN; c0 += 32) {
+      uint32_t v[32];
+      const uint32_t taddr = tmem_acc + ((uint32_t)(q * 32) << 16) + (uint32_t)c0;
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+          "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+          : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+            "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+            "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+            "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+          : "r"(taddr) : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+      if (row < n_rows) {
+        int32_t* crow = C + (int64_t)row * n_rows;
+        const int col0 = tj * kGN + c0;
+#pragma unroll
+        for (int t = 0; t < 32; ++t)
+          if (col0 + t < n_rows) {
+            if (split) atomicAdd(crow + col0 + t, (int32_t)v[t]);
+            else crow[col0 + t] = (int32_t)v[t];
+          }
+      }
+    }
+    tc_fence_before();
+  } else {
+    // ===== B expanders: bits -> int8 operand tile in shared memory =====
+    const int bt = warp < 4 ? (warp - 2) * 32 + lane : 64 + (warp - 8) * 32 + lane;   // 0 .. 255
+    for (int64_t i = 0; i < n_kb; ++i) {
+      const int s = (int)(i % kTStages);
+      const uint32_t ph = (uint32_t)((i / kTStages) & 1);
+      mbar_wait(bits_full(s), ph);
+      mbar_wait(op_empty(s), ph ^ 1u);
+      const uint8_t* bits = gen_base + (bit_base - base) + s * kGBitBytes + kGM * 16;   // B rows' bits
+      uint8_t* ops = gen_base + s * kTOpBytes;
+      constexpr int kUnits = kGN * 2 / (kTBWarps * 32);   // 2 per thread
+      uint2 in[kUnits];
+#pragma unroll
+      for (int it = 0; it < kUnits; ++it) {
+        const int u = it * (kTBWarps * 32) + bt;
+        const int r = ((u >> 4) << 3) + (u & 7), half = (u >> 3) & 1;
+        in[it] = *reinterpret_cast<const uint2*>(bits + r * 16 + half * 8);
+      }
+#pragma unroll
+      for (int it = 0; it < kUnits; ++it) {
+        const int u = it * (kTBWarps * 32) + bt;
+        const int r = ((u >> 4) << 3) + (u & 7), half = (u >> 3) & 1;
+        uint8_t* orow = ops + r * kGKBytes;
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+          const uint32_t h = ((jj & 2) ? in[it].y : in[it].x) >> ((jj & 1) * 16);
+          uint4 v;
+          v.x = ((h & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.y = (((h >> 4) & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.z = (((h >> 8) & 0xFu) * 0x00204081u) & 0x01010101u;
+          v.w = (((h >> 12) & 0xFu) * 0x00204081u) & 0x01010101u;
+          const int j = half * 4 + jj;
+          *reinterpret_cast<uint4*>(orow + ((j ^ (r & 7)) << 4)) = v;
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(op_full(s));
+        mbar_arrive(bits_empty(s));
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(512) : "memory");
+  }
+}
+
 }  // namespace kmls
 
 using namespace kmls;
@@ -339,6 +557,16 @@ extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int
   const int64_t kb_per_split = (n_kb + ksplit - 1) / ksplit;
   if (ksplit > 1) KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
   dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)ksplit);
+  // default: the variant with the A operand in tensor memory; KMLS_PAIR_GEMM=ss selects the
+  // one that stages both operands in shared memory
+  const char* variant = getenv("KMLS_PAIR_GEMM");
+  if (!(variant && variant[0] == 's')) {
+    KMLS_CUDA(cudaFuncSetAttribute(k_pair_gemm_i8_ts, cudaFuncAttributeMaxDynamicSharedMemorySize, kTSmemBytes));
+    k_pair_gemm_i8_ts<<<grid, kTThreads, kTSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb,
+                                                           kb_per_split, d_pair);
+    KMLS_LAUNCHED("k_pair_gemm_i8_ts");
+    return 0;
+  }
   k_pair_gemm_i8<<<grid, kGThreads, kGSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb,
                                                       kb_per_split, d_pair);
   KMLS_LAUNCHED("k_pair_gemm_i8");

@@ -134,9 +134,12 @@ def test_pair_counts_and_select(rows, n):
         assert sup.cpu().numpy().tolist() == [int(c) / n for c in want[ii, jj]]
 
 
+@pytest.mark.parametrize("variant", ["ss", "ts"])
 @pytest.mark.parametrize("rows,n", [(64, 256), (129, 3000), (300, 70000), (1000, 200000), (257, 1024)])
-def test_pair_counts_tensor_core_matches_cuda_core(rows, n):
-    """tcgen05 int8 GEMM vs the AND+popc kernel: bit-equal on the upper triangle."""
+def test_pair_counts_tensor_core_matches_cuda_core(rows, n, variant, monkeypatch):
+    """tcgen05 int8 GEMM (A operand from shared memory / from tensor memory) vs the AND+popc
+    kernel: bit-equal on the upper triangle."""
+    monkeypatch.setenv("KMLS_PAIR_GEMM", variant)
     rng = np.random.default_rng(rows + n)
     W = int(_lib.value("kmls_bitmap_row_words", n))
     dense = rng.random((rows, n)) < rng.uniform(0.01, 0.7, (rows, 1))
