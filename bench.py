@@ -266,7 +266,8 @@ def run_gpu(args):
                              prune=False if args.no_prune else None, pair_impl=args.pair_impl,
                              count_impl=args.count_impl)
         if args.no_rules:
-            return res, miner.RuleTable(*[torch.empty(0, device=device)] * 6, [])
+            e = torch.empty(0, device=device)
+            return res, miner.RuleTable(e.view(0, 2), e, e, e, [])
         rules = miner.generate_rules(res, conf, part=(rank, world))
         return res, rules
 
@@ -330,7 +331,7 @@ def run_gpu(args):
         (6650.0, "fallback of B200_PROFILING.md")
     # Roofline objects. Algorithmic work per launch:
     #   k_rules_count  32 B per index lookup (parent node + child entry) + 8 B per (itemset, antecedent) split written
-    #   k_rules_write  8 B per split read + 32 B per rule written
+    #   k_rules_write  8 B per split read + 24 B per rule written
     #   k_pair_gemm_i8 2 * N * F(F+1)/2 int8 ops (upper triangle incl. diagonal)
     #   others         the bytes the caller annotates (miner.py, algo_bytes=...)
     int8_peak = 2.0 * peaks.get("bf16_tflops", 1590.0)   # TOP/s: int8 dense = 2x the measured bf16 GEMM peak
@@ -341,7 +342,7 @@ def run_gpu(args):
                  for k, n in enumerate(lv_sizes, start=1) if k >= 2 and k < len(classes) + 0)
     algo = {
         "kmls_rules_count": (32 * probes + 8 * splits) / max(world, 1),
-        "kmls_rules_write": (8 * splits) / max(world, 1) + 32 * (info.get("rules_this_rank") or 0),
+        "kmls_rules_write": (8 * splits) / max(world, 1) + 24 * (info.get("rules_this_rank") or 0),
     }
 
     def roof_of(nm, kernel, bound):

@@ -228,14 +228,19 @@ int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int6
                      const void* d_nodes, int64_t n_playlists_total, double min_confidence,
                      void* d_part, int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
 /* Pass 2: d_rule_off[lvl_count] = first output slot of each itemset (exclusive scan of the
- * kept counts over everything this rank emits). Rule r: itemset d_out_itemset[r] (global
- * id), antecedent = members selected by the bits of d_out_antecedent[r] (bit t = t-th
- * member), consequent = the rest. */
+ * kept counts over everything this rank emits). Rule r: d_out_rule[2r] = itemset (global id),
+ * d_out_rule[2r+1] = antecedent mask (bit t = t-th member; the consequent is the rest),
+ * d_out_confidence[r], d_out_lift[r]. */
 int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
                      int32_t k, int64_t lvl_begin, int64_t lvl_count, int64_t n_playlists_total,
                      double min_confidence, const void* d_part, const int64_t* d_rule_off,
-                     int32_t* d_out_itemset, uint32_t* d_out_antecedent, double* d_out_support,
-                     double* d_out_confidence, double* d_out_lift, kmls_stream_t stream);
+                     int32_t* d_out_rule, double* d_out_confidence, double* d_out_lift,
+                     kmls_stream_t stream);
+/* The support column of the rule table, on demand: d_out[r] = count of rule r's itemset / N
+ * (d_counts = the arena's counts). Not written by pass 2: it would be a quarter of its bytes
+ * and is one gather away. */
+int kmls_rule_supports(const int32_t* d_rule, int64_t n_rules, const int32_t* d_counts,
+                       int64_t n_playlists_total, double* d_out, kmls_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -50,8 +50,8 @@ SIGNATURES = {
     "kmls_rules_parts_per_itemset": (_I64, [_I32]),
     "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _I64, _I64, _P, _I64, _F64, _P, _P,
                                         _P, _P]),
-    "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P,
-                                        _P, _P, _P]),
+    "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P]),
+    "kmls_rule_supports": (ctypes.c_int, [_P, _I64, _P, _I64, _P, _P]),
 }
 
 _lib = None
@@ -86,7 +86,7 @@ KERNELS_PER_CALL = {
     "kmls_exclusive_scan_i32_noalloc": 3,
     "kmls_itemset_set_build": 1, "kmls_join_count": 4, "kmls_join_write": 4, "kmls_count_candidates": 1,
     "kmls_emit_count": 3, "kmls_emit_level": 1, "kmls_trie_index_build": 1, "kmls_rules_count": 1,
-    "kmls_rules_write": 1, "kmls_count_pairs": 1, "kmls_emit_level_px": 1, "kmls_row_alloc": 1,
+    "kmls_rules_write": 1, "kmls_rule_supports": 1, "kmls_count_pairs": 1, "kmls_emit_level_px": 1, "kmls_row_alloc": 1,
     "kmls_project_rows": 1, "kmls_row_tidlists": 1, "kmls_project_rows_gather": 1,
 }
 

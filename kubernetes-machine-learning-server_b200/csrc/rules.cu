@@ -264,8 +264,7 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
 __global__ void __launch_bounds__(256)
 k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
               const int2* __restrict__ part, const int64_t* __restrict__ rule_off,
-              int32_t* __restrict__ out_itemset, uint32_t* __restrict__ out_antecedent,
-              double* __restrict__ out_support, double* __restrict__ out_confidence,
+              int2* __restrict__ out_rule, double* __restrict__ out_confidence,
               double* __restrict__ out_lift) {
   const int lane = threadIdx.x & 31;
   const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
@@ -288,17 +287,29 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
       const uint32_t below = (1u << lane) - 1u;
       int64_t o = pos + __popc(m1 & below) + __popc(m2 & below);
       if (r.k1) {
-        out_itemset[o] = (int32_t)gid; out_antecedent[o] = (uint32_t)am; out_support[o] = s_x;
-        out_confidence[o] = r.c1; out_lift[o] = r.l1;
+        out_rule[o] = make_int2((int32_t)gid, am);
+        out_confidence[o] = r.c1;
+        out_lift[o] = r.l1;
         ++o;
       }
       if (r.k2) {
-        out_itemset[o] = (int32_t)gid; out_antecedent[o] = full ^ (uint32_t)am; out_support[o] = s_x;
-        out_confidence[o] = r.c2; out_lift[o] = r.l2;
+        out_rule[o] = make_int2((int32_t)gid, (int32_t)(full ^ (uint32_t)am));
+        out_confidence[o] = r.c2;
+        out_lift[o] = r.l2;
       }
       pos += __popc(m1) + __popc(m2);
     }
   }
+}
+
+// support column of the rule table, on demand: support[r] = count(itemset of rule r) / N
+// (kept out of pass 2 because it is 8 of every 32 bytes the pass would write)
+__global__ void __launch_bounds__(256)
+k_rule_supports(const int2* __restrict__ rule, int64_t n, const int32_t* __restrict__ counts,
+                double n_total, double* __restrict__ out) {
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n;
+       r += (int64_t)gridDim.x * blockDim.x)
+    out[r] = __ddiv_rn((double)__ldg(counts + rule[r].x), n_total);
 }
 
 static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
@@ -379,10 +390,8 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
 extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
                                 int32_t k, int64_t lvl_begin, int64_t lvl_count,
                                 int64_t n_playlists_total, double min_confidence,
-                                const void* d_part, const int64_t* d_rule_off,
-                                int32_t* d_out_itemset, uint32_t* d_out_antecedent,
-                                double* d_out_support, double* d_out_confidence, double* d_out_lift,
-                                kmls_stream_t stream) {
+                                const void* d_part, const int64_t* d_rule_off, int32_t* d_out_rule,
+                                double* d_out_confidence, double* d_out_lift, kmls_stream_t stream) {
   Arena a;
   int rc = make_arena(a, nullptr, d_counts, nullptr, level_sizes, max_k);
   if (rc) return rc;
@@ -390,12 +399,24 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
   KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
                "kmls_rules_write: itemset range out of bounds");
   if (lvl_count == 0) return 0;
-  KMLS_REQUIRE(d_part && d_rule_off && d_out_itemset && d_out_antecedent && d_out_support &&
-                   d_out_confidence && d_out_lift, "kmls_rules_write: null pointer");
+  KMLS_REQUIRE(d_part && d_rule_off && d_out_rule && d_out_confidence && d_out_lift &&
+                   ((uintptr_t)d_out_rule & 7) == 0, "kmls_rules_write: null or misaligned pointer");
   int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int2*)d_part,
-      d_rule_off, d_out_itemset, d_out_antecedent, d_out_support, d_out_confidence, d_out_lift);
+      d_rule_off, (int2*)d_out_rule, d_out_confidence, d_out_lift);
   KMLS_LAUNCHED("k_rules_write");
+  return 0;
+}
+
+extern "C" int kmls_rule_supports(const int32_t* d_rule, int64_t n_rules, const int32_t* d_counts,
+                                  int64_t n_playlists_total, double* d_out, kmls_stream_t stream) {
+  KMLS_REQUIRE(n_rules >= 0 && n_playlists_total > 0, "kmls_rule_supports: bad size");
+  if (n_rules == 0) return 0;
+  KMLS_REQUIRE(d_rule && d_counts && d_out, "kmls_rule_supports: null pointer");
+  int grid = (int)std::min<int64_t>((n_rules + 255) / 256, (int64_t)num_sms() * 16);
+  k_rule_supports<<<grid, 256, 0, (cudaStream_t)stream>>>((const int2*)d_rule, n_rules, d_counts,
+                                                          (double)n_playlists_total, d_out);
+  KMLS_LAUNCHED("k_rule_supports");
   return 0;
 }

@@ -446,18 +446,38 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
 class RuleTable:
     """Rules as device columns: rule r is about itemset ``itemset[r]`` (global id: level
     tables concatenated in level order); bit t of ``antecedent[r]`` selects its t-th member
-    (row order) into the antecedent, the rest is the consequent."""
-    itemset: torch.Tensor      # int32[R]
-    antecedent: torch.Tensor   # int32[R] (bit mask)
-    support: torch.Tensor      # float64[R]
+    (row order) into the antecedent, the rest is the consequent. ``support`` is not stored by
+    the generating pass (it is the itemset's own support): it is gathered on first use."""
+    rule: torch.Tensor         # int32[R, 2]: (itemset global id, antecedent bit mask)
     confidence: torch.Tensor   # float64[R]
     lift: torch.Tensor         # float64[R]
     arena_items: torch.Tensor  # int32: all level tables' members (rows), level after level
     level_sizes: List[int]     # index k -> number of k-itemsets (index 0 unused)
+    arena_counts: Optional[torch.Tensor] = None
+    n_playlists: int = 0
+    _support: Optional[torch.Tensor] = None
 
     @property
     def n_rules(self) -> int:
-        return int(self.itemset.numel())
+        return int(self.confidence.numel())
+
+    @property
+    def itemset(self) -> torch.Tensor:
+        return self.rule[:, 0]
+
+    @property
+    def antecedent(self) -> torch.Tensor:
+        return self.rule[:, 1]
+
+    @property
+    def support(self) -> torch.Tensor:
+        if self._support is None:
+            out = torch.empty(max(self.n_rules, 1), dtype=torch.float64, device=self.rule.device)[:self.n_rules]
+            if self.n_rules:
+                _lib.call("kmls_rule_supports", self.rule, self.n_rules, self.arena_counts,
+                          self.n_playlists, out, _stream())
+            self._support = out
+        return self._support
 
 
 def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_000_000_000,
@@ -478,7 +498,7 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     e_f64 = dev.empty(0, torch.float64)
     if max_k < 2 or n_all == 0 or int(sizes[2:].sum()) == 0:
         arena = torch.cat([it.reshape(-1) for it, _ in res.levels]) if res.levels else e_i32
-        return RuleTable(e_i32, e_i32, e_f64, e_f64, e_f64, arena, sizes.tolist())
+        return RuleTable(e_i32.view(0, 2), e_f64, e_f64, arena, sizes.tolist(), None, res.n_playlists)
     arena_items = torch.cat([it.reshape(-1) for it, _ in res.levels])
     arena_counts = torch.cat([ct for _, ct in res.levels])
     arena_par = torch.cat(res.parents)
@@ -528,17 +548,16 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
                              "itemset table (table not downward closed)")
     if n_rules > max_rules:
         raise _lib.KmlsError(f"{n_rules} rules exceed max_rules={max_rules} (never truncated)")
-    o_set = dev.empty(n_rules, torch.int32)
-    o_ante = dev.empty(n_rules, torch.int32)
-    o_sup = dev.empty(n_rules, torch.float64)
+    o_rule = dev.empty(n_rules * 2, torch.int32)
     o_conf = dev.empty(n_rules, torch.float64)
     o_lift = dev.empty(n_rules, torch.float64)
     if n_rules:
         for k, lvl_begin, cnt, out0, part_buf in plan:
             _lib.call("kmls_rules_write", arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
-                      res.n_playlists, float(min_confidence), part_buf, rule_off[out0:], o_set,
-                      o_ante, o_sup, o_conf, o_lift, s)
-    return RuleTable(o_set, o_ante, o_sup, o_conf, o_lift, arena_items, sizes.tolist())
+                      res.n_playlists, float(min_confidence), part_buf, rule_off[out0:], o_rule,
+                      o_conf, o_lift, s)
+    return RuleTable(o_rule.view(n_rules, 2), o_conf, o_lift, arena_items, sizes.tolist(), arena_counts,
+                     res.n_playlists)
 
 
 def rules_to_host(res: MineResult, rules: RuleTable):
