@@ -57,7 +57,8 @@ def test_item_histogram():
 
 
 @pytest.mark.parametrize("n,t,dup", [(1, 1, False), (255, 40, True), (256, 40, False), (257, 9000, True),
-                                     (5000, 300, True), (70001, 64, False)])
+                                     (5000, 300, True), (70001, 64, False),
+                                     (600, 20000, False)])   # 10,000 rows: two row tiles in shared memory
 def test_encode_popcount_roundtrip(n, t, dup):
     rng = np.random.default_rng(n)
     lens = rng.integers(0, min(t, 60) + 1, n)
