@@ -364,6 +364,14 @@ def run_gpu(args):
                  "kmls_count_candidates": ("k_count_candidates", "hbm"), "kmls_encode_bitmap": ("k_encode_bitmap", "hbm"),
                  "kmls_row_popcount": ("k_row_popcount", "hbm"), "kmls_item_histogram": ("k_item_histogram", "hbm")}
     rooflines = {k: roof_of(k, *v) for k, v in kernel_of.items() if k in per}
+    try:   # DRAM traffic of one ncu-captured launch per kernel (workload zipf_1Mx100k_s0.001, 1 GPU)
+        ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        for k_, r_ in rooflines.items():
+            if r_ and k_ in ncu_traffic and name == "zipf_1Mx100k_s0.001" and world == 1:
+                r_["traffic"] = ncu_traffic[k_]["traffic_bytes"]
+                r_["traffic_launch"] = ncu_traffic[k_]["launch"]
+    except (OSError, ValueError):
+        pass
     roof = rooflines.get(top) or next((r for r in rooflines.values() if r), None)
 
     # ---- e2e: pinned host CSR in, tables back on the host ---------------------------------
