@@ -278,6 +278,31 @@ extern "C" int kmls_itemset_set_build(const int32_t* d_items, int64_t n, int32_t
   return 0;
 }
 
+// Join without pruning when the parent column is known: the candidates of p are simply its
+// later siblings, so a thread per itemset is enough - pass 1 counts them (a forward scan of
+// the parent column), pass 2 writes (p, p+1), (p, p+2), ...
+__global__ void __launch_bounds__(256)
+k_join_siblings(const int32_t* __restrict__ par, int64_t n, int write, int32_t* __restrict__ kept_cnt,
+                const int64_t* __restrict__ kept_off, int32_t* __restrict__ cand_p,
+                int32_t* __restrict__ cand_q) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n;
+       p += (int64_t)gridDim.x * blockDim.x) {
+    if (!write) {
+      const int32_t mine = __ldg(par + p);
+      int64_t e = p + 1;
+      while (e < n && __ldg(par + e) == mine) ++e;
+      kept_cnt[p] = (int32_t)(e - p - 1);
+    } else {
+      const int64_t o = kept_off[p];
+      const int32_t m = kept_cnt[p];
+      for (int32_t i = 0; i < m; ++i) {
+        cand_p[o + i] = (int32_t)p;
+        cand_q[o + i] = (int32_t)(p + 1 + i);
+      }
+    }
+  }
+}
+
 static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint64_t* d_slots,
                        int64_t capacity, const int32_t* d_pair, int32_t n_rows, int32_t thr,
                        const int32_t* d_par, int write, int32_t* d_kept_cnt, uint32_t* d_kept_mask,
@@ -290,6 +315,12 @@ static int launch_join(const int32_t* d_items, int64_t n, int32_t k, const uint6
                                       "kmls_join: fingerprint set capacity must be a power of two");
   if (!d_slots) capacity = 1;
   if (n == 0) return 0;
+  if (d_par && ((k == 2 && !d_pair) || (k >= 3 && !d_slots))) {
+    int g = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 32);
+    k_join_siblings<<<g, 256, 0, s>>>(d_par, n, write, d_kept_cnt, d_kept_off, d_cand_p, d_cand_q);
+    KMLS_LAUNCHED("k_join_siblings");
+    return 0;
+  }
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 32);
   k_join<<<grid, 256, 0, s>>>(d_items, n, k, (const unsigned long long*)d_slots,
                               (uint64_t)capacity - 1, d_pair, n_rows, thr, d_par, write, d_kept_cnt,
