@@ -1,7 +1,7 @@
 """Small end-to-end case for compute-sanitizer (memcheck / racecheck / synccheck):
 every kernel of the default path runs once, including the tcgen05 pair GEMM."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))  # repo root
 import kmls_b200
 from kmls_b200 import synth
 from oracle import fpgrowth_c, mlxtend_restated as M
