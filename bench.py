@@ -385,20 +385,27 @@ def run_gpu(args):
         dst.copy_(t.reshape(-1), non_blocking=True)
         return dst
 
+    host_tables = kmls_b200.api.HostTables(device)
+
     def e2e_step():
+        # pinned host CSR up, mine + rules, every level table streamed back to pinned host
+        # memory on a side stream while the next levels are mined (kmls_b200.api.HostTables)
         o = h_off.to(device, non_blocking=True)
         i = h_items.to(device, non_blocking=True)
-        res, rules = step(o, i)
-        outs = [to_host(0, res.row_items)]
-        for lv, (it, ct) in enumerate(res.levels):
-            outs.append(to_host(2 * lv + 1, it))
-            outs.append(to_host(2 * lv + 2, ct))
+        host_tables.begin()
+        res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group,
+                             prune=False if args.no_prune else None, pair_impl=args.pair_impl,
+                             count_impl=args.count_impl, on_level=host_tables.on_level)
+        n_rules = 0
+        if not args.no_rules:
+            n_rules = miner.generate_rules(res, conf, part=(rank, world)).n_rules
+        host_tables.finish(res)
         torch.cuda.synchronize()
-        d2h = sum(x.numel() * x.element_size() for x in outs)
-        return d2h, rules.n_rules
+        return host_tables.nbytes, n_rules
 
-    e2e_note = ("host CSR -> device -> mine + rules -> itemset tables back on the host; the rule table "
-                "stays on the device (sharded by rank)")
+    e2e_note = ("pinned host CSR -> device -> mine + rules; every level table is streamed back to pinned host "
+                "memory while mining continues (kmls_b200.api.HostTables); the rule table stays on the device "
+                "(sharded by rank)")
     if name.startswith("mpd_standin") and world == 1:
         # the reference-facing plugin call itself: dict of lists of names in, dict of dicts out
         from kmls_b200 import synth

@@ -69,22 +69,85 @@ def _dist_group():
     return None, 0, 1
 
 
+class HostTables:
+    """Level tables streamed to pinned host memory while the GPU keeps mining: every level is
+    copied on a side stream as soon as it is final. ``levels[k-1] = (items[n_k, k] as bitmap
+    ROW indices, counts[n_k])`` as numpy views of the pinned buffers (valid until the next
+    use of the same HostTables), ``row_items`` maps rows to track ids."""
+
+    def __init__(self, device):
+        self.device = device
+        self.stream = torch.cuda.Stream(device=device)
+        self._pinned = {}
+        self._pending = []
+        self.row_items = None
+
+    def _buf(self, key, t):
+        b = self._pinned.get(key)
+        if b is None or b.numel() < t.numel():
+            b = torch.empty(max(int(t.numel()), 1), dtype=t.dtype).pin_memory()
+            self._pinned[key] = b
+        return b[:t.numel()]
+
+    def begin(self):
+        self._pending = []
+        self.row_items = None
+
+    def on_level(self, k, items, counts):
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(self.device))
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_event(ev)
+            hi = self._buf(("i", k), items)
+            hc = self._buf(("c", k), counts)
+            hi.copy_(items.reshape(-1), non_blocking=True)
+            hc.copy_(counts, non_blocking=True)
+        items.record_stream(self.stream)
+        counts.record_stream(self.stream)
+        self._pending.append((k, hi, hc))
+
+    def finish(self, res):
+        with torch.cuda.stream(self.stream):
+            self.stream.wait_stream(torch.cuda.current_stream(self.device))
+            hr = self._buf(("r", 0), res.row_items)
+            hr.copy_(res.row_items, non_blocking=True)
+        self.stream.synchronize()
+        self.row_items = hr.numpy()
+        self.levels = [(hi.numpy().reshape(-1, k), hc.numpy()) for k, hi, hc in self._pending]
+        self.nbytes = hr.numel() * 4 + sum(hi.numel() * 4 + hc.numel() * 4 for _, hi, hc in self._pending)
+        return self
+
+
 def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: float,
-             min_confidence: Optional[float] = None, max_len: Optional[int] = None, **mine_kwargs):
+             min_confidence: Optional[float] = None, max_len: Optional[int] = None,
+             host_tables: Optional[HostTables] = None, split_rules: bool = False, **mine_kwargs):
     """Host CSR of track ids in, device tables out: (MineResult, RuleTable or None).
-    Under torchrun each rank keeps a contiguous range of the playlists."""
+    Under torchrun each rank keeps a contiguous range of the playlists. With ``host_tables``
+    the level tables are also streamed to pinned host memory during the mining (see
+    HostTables); ``offsets``/``ids`` may be pinned torch tensors to make the upload async.
+    ``split_rules``: under torchrun, each rank generates only its share of the rule table."""
     device = _device()
     group, rank, world = _dist_group()
     n_total = len(offsets) - 1
     if world > 1:
+        if torch.is_tensor(offsets):
+            offsets, ids = offsets.numpy(), ids.numpy()
         offsets, ids = _shard(offsets, ids, rank, world)
-    d_off = torch.from_numpy(np.ascontiguousarray(offsets)).to(device, non_blocking=True)
-    d_ids = torch.from_numpy(np.ascontiguousarray(ids)).to(device, non_blocking=True)
+    if torch.is_tensor(offsets):
+        d_off, d_ids = offsets.to(device, non_blocking=True), ids.to(device, non_blocking=True)
+    else:
+        d_off = torch.from_numpy(np.ascontiguousarray(offsets)).to(device, non_blocking=True)
+        d_ids = torch.from_numpy(np.ascontiguousarray(ids)).to(device, non_blocking=True)
+    if host_tables is not None:
+        host_tables.begin()
+        mine_kwargs["on_level"] = host_tables.on_level
     res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
                          group=group, max_len=max_len, **mine_kwargs)
     rules = None
     if min_confidence is not None:
-        rules = miner.generate_rules(res, min_confidence)
+        rules = miner.generate_rules(res, min_confidence, part=(rank, world) if split_rules else (0, 1))
+    if host_tables is not None:
+        host_tables.finish(res)
     return res, rules
 
 

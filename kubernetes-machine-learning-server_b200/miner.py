@@ -224,7 +224,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
              pair_impl: str = "auto", count_impl: str = "projected",
              prune: Optional[bool] = None, first_projection: str = "gather",
-             keep_words: Optional[int] = None, prepared: Optional["Prepared"] = None) -> MineResult:
+             keep_words: Optional[int] = None, prepared: Optional["Prepared"] = None,
+             on_level=None) -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
@@ -289,6 +290,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     row_items = prepared.row_items[r0:]
     lvl1_items = torch.arange(n_rows, dtype=torch.int32, device=dev.device).reshape(-1, 1)
     levels = [(lvl1_items, counts1)]
+    if on_level is not None:
+        on_level(1, lvl1_items, counts1)
     stats["levels"].append({"k": 1, "candidates": n_items, "frequent": n_rows})
     if n_rows < 2 or (max_len is not None and max_len <= 1):
         return result(row_items, levels)
@@ -321,6 +324,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     counts_k = dev.empty(n2, torch.int32)
     _lib.call("kmls_pair_select", pair, n_rows, thr, n2, row_off, items_k, counts_k, s)
     levels.append((items_k.view(n2, 2), counts_k))
+    if on_level is not None:
+        on_level(2, items_k, counts_k)
     parents.append(items_k.view(n2, 2)[:, 0].contiguous())
     total = n_rows + n2
     projected = count_impl == "projected"
@@ -439,6 +444,8 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         k += 1
         items_k, counts_k = items_n, counts_n
         levels.append((items_k.view(n_next, k), counts_k))
+        if on_level is not None:
+            on_level(k, items_k, counts_k)
     return result(row_items, levels, pair.view(n_rows, n_rows) if keep_pair_counts else None)
 
 

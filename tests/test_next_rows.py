@@ -68,3 +68,16 @@ def test_sweep_reuses_levels_1_and_2_and_matches_independent_runs():
         assert shared == fresh
     with pytest.raises(ValueError):
         miner.mine_csr(d_off, d_ids, len(cols), 0.01, prepared=prep)
+
+
+@pytest.mark.gpu
+def test_host_tables_stream_equals_device_tables():
+    off, items = synth.zipf_playlists(5000, 400, mean_draws=25, alpha=0.9, seed=8)
+    ht = api.HostTables(torch.device("cuda", 0))
+    for _ in range(2):                      # second use reuses the pinned buffers
+        res, rules = kmls_b200.mine_ids(torch.from_numpy(off).pin_memory(), torch.from_numpy(items).pin_memory(),
+                                        400, 0.02, 0.5, host_tables=ht)
+        assert len(ht.levels) == len(res.levels)
+        assert (ht.row_items == res.row_items.cpu().numpy()).all()
+        for (hi, hc), (di, dc) in zip(ht.levels, res.levels):
+            assert (hi == di.cpu().numpy()).all() and (hc == dc.cpu().numpy()).all()
