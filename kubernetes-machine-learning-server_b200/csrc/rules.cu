@@ -270,6 +270,44 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
   const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
   const uint32_t full = (1u << k) - 1u;
   const int64_t lvl_first = a.id_off[k];
+  if (n_sub <= 16) {
+    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, antecedent
+    // mask), so that the lanes are not left idle by the few splits a small itemset has
+    const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
+    const uint32_t gmask = (n_sub == 32 ? 0xffffffffu : ((1u << n_sub) - 1u)) << (g * n_sub);
+    const uint32_t below = gmask & ((1u << lane) - 1u);
+    const int64_t n_groups = (lvl_count + per_warp - 1) / per_warp;
+    for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < n_groups;
+         w += (int64_t)gridDim.x * 8) {
+      const int64_t j = w * per_warp + g;
+      RuleVals r;
+      r.k1 = r.k2 = false;
+      int64_t gid = 0;
+      double s_x = 0;
+      if (j < lvl_count && am >= 1) {
+        gid = lvl_first + lvl_begin + j;
+        s_x = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
+        const int2 cc = __ldg(part + j * n_part + (am - 1));
+        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, min_conf);
+      }
+      const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
+      if (r.k1 || r.k2) {
+        int64_t o = rule_off[j] + __popc(m1 & below) + __popc(m2 & below);
+        if (r.k1) {
+          out_rule[o] = make_int2((int32_t)gid, am);
+          out_confidence[o] = r.c1;
+          out_lift[o] = r.l1;
+          ++o;
+        }
+        if (r.k2) {
+          out_rule[o] = make_int2((int32_t)gid, (int32_t)(full ^ (uint32_t)am));
+          out_confidence[o] = r.c2;
+          out_lift[o] = r.l2;
+        }
+      }
+    }
+    return;
+  }
   for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < lvl_count;
        j += (int64_t)gridDim.x * 8) {
     const int64_t gid = lvl_first + lvl_begin + j;

@@ -532,6 +532,20 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     n_x = x_end - x_begin
     rule_cnt = dev.empty(n_x, torch.int32)
     missing = torch.zeros(1, dtype=torch.int32, device=device)
+    # never truncate, never die half-way: refuse up front what cannot fit
+    splits = 0
+    lvl_start = 0
+    for k in range(2, max_k + 1):
+        lo, hi = max(x_begin, lvl_start), min(x_end, lvl_start + int(sizes[k]))
+        if hi > lo:
+            splits += (hi - lo) * ((1 << (k - 1)) - 1)
+        lvl_start += int(sizes[k])
+    free_bytes = torch.cuda.mem_get_info(device)[0] + torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+    if splits * 8 > free_bytes:
+        raise _lib.KmlsError(
+            f"rule generation would examine {splits} (itemset, antecedent) splits and needs {splits * 8 / 1e9:.1f} GB "
+            f"of scratch for them, more than the {free_bytes / 1e9:.1f} GB free on this GPU: raise min_support, "
+            "shard over more GPUs, or skip the rule table (results are never truncated)")
     # per level: the slice of this part that falls into the level
     plan, lvl_start = [], 0
     for k in range(2, max_k + 1):

@@ -419,3 +419,13 @@ def test_properties_at_scale():
     # rules: confidence >= threshold, support/lift consistent with the integer counts
     conf = rules.confidence.cpu().numpy()
     assert (conf >= 0.8).all() and (conf <= 1.0).all()
+
+
+def test_guards_fail_loudly_instead_of_truncating():
+    off, items = synth.zipf_playlists(4000, 300, mean_draws=25, alpha=0.8, seed=2)
+    with pytest.raises(_lib.KmlsError, match="max_itemsets"):
+        kmls_b200.mine_ids(off, items, 300, 0.01, max_itemsets=500)
+    res, _ = kmls_b200.mine_ids(off, items, 300, 0.01)
+    assert res.n_itemsets > 500
+    with pytest.raises(_lib.KmlsError, match="max_rules"):
+        kmls_b200.generate_rules(res, 0.1, max_rules=10)
