@@ -158,6 +158,71 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
     const int64_t j0 = ch * chunk;
     const int32_t* items_lvl = a.items + a.item_off[k] + lvl_begin * k;
     const int32_t* counts_lvl = a.counts + lvl_first + lvl_begin;
+    if (n_sub <= 16) {
+      // Short itemsets (k <= 5): lane = (sibling in the group, antecedent mask). The group is a
+      // run of up to 32 / n_sub siblings of ONE class, so that all of them use the same
+      // subset table; a class boundary simply ends the run early.
+      const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
+      const uint32_t gmask = ((1u << n_sub) - 1u) << (g * n_sub);
+      int32_t head_item = -1;
+      bool have_head = false;
+      int64_t j = j0;
+      while (j < j_end) {
+        const int32_t my_item = lane < k ? __ldg(items_lvl + j * k + lane) : 0;
+        int d = 0;
+        if (have_head) {
+          const uint32_t nm = __ballot_sync(0xffffffffu, lane < k - 1 && my_item != head_item);
+          d = nm ? __ffs(nm) - 1 : k - 1;
+        }
+        if (!have_head || d < k - 1) {
+          for (int h = d; h < k - 1; ++h) {
+            const int32_t ph = __shfl_sync(0xffffffffu, my_item, h);
+            for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
+              const int rest = m ^ (1 << h);
+              int2 gc;
+              if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));
+              else gc = trie_child(node, tab_gid[rest], ph);
+              if (gc.x < 0) atomicAdd(missing, 1);
+              tab_gid[m] = gc.x;
+              tab_cnt[m] = gc.y;
+            }
+            __syncwarp();
+          }
+          head_item = my_item;
+          have_head = true;
+        }
+        // which of the next per_warp itemsets are siblings of j (same first k-1 members)?
+        const int64_t sib = j + g;
+        bool ok = sib < j_end;
+        if (ok && am < k - 1) ok = __ldg(items_lvl + sib * k + am) == __ldg(items_lvl + j * k + am);
+        const uint32_t okm = __ballot_sync(0xffffffffu, ok);
+        int run = 0;
+        while (run < per_warp && ((okm >> (run * n_sub)) & ((1u << n_sub) - 1u)) == ((1u << n_sub) - 1u)) ++run;
+        // run >= 1: group 0 is itemset j itself
+        const bool active = g < run && am >= 1;
+        bool k1 = false, k2 = false;
+        if (active) {
+          const int32_t last = __ldg(items_lvl + sib * k + (k - 1));
+          const int32_t c_x = __ldg(counts_lvl + sib);
+          const double s_x = __ddiv_rn((double)c_x, n_total);
+          const int32_t ca = tab_cnt[am];
+          const int rest = (n_sub - 1) ^ am;
+          const int32_t cc = rest == 0 ? __ldg(a.counts + last) : trie_child(node, tab_gid[rest], last).y;
+          if (cc < 0 || ca < 0) {
+            atomicAdd(missing, 1);
+          } else {
+            k1 = conf_keep(c_x, ca, s_x, n_total, min_conf);
+            k2 = conf_keep(c_x, cc, s_x, n_total, min_conf);
+          }
+          part[sib * n_part + (am - 1)] = make_int2(ca, cc);
+        }
+        const uint32_t b1 = __ballot_sync(0xffffffffu, k1), b2 = __ballot_sync(0xffffffffu, k2);
+        if (active && am == 1) rule_cnt[sib] = __popc(b1 & gmask) + __popc(b2 & gmask);
+        j += run;
+      }
+      __syncwarp();
+      continue;
+    }
     int32_t nx_item = lane < k ? __ldg(items_lvl + j0 * k + lane) : 0;
     int32_t nx_cnt = __ldg(counts_lvl + j0);
     int32_t head_item = -1;                // member `lane` of the prefix whose subsets are in the table
