@@ -440,14 +440,16 @@ def run_gpu(args):
         res, rules = step(d_off, d_items)
         o_, i_, c_ = res.to_host()
         got = {"levels": [int(c.numel()) for _, c in res.levels], "checksum": fpgrowth_c.itemset_checksum(o_, i_, c_),
-               "n_rules": rules.n_rules}
+               "n_rules": rules.n_rules,
+               "rule_checksum": 0 if args.no_rules else miner.rule_checksum(res, rules)}
         del res, rules
         t1_, tk_ = M.thresholds(s, n_local)
         t0 = time.time()
         ref = fpgrowth_c.fpgrowth(off, items, n_tracks, t1_, tk_, store=True,
                                   rules_min_confidence=None if args.no_rules else conf)
         want = {"levels": ref.level_counts[1:len(got["levels"]) + 1].tolist(), "checksum": ref.checksum,
-                "n_rules": 0 if args.no_rules else ref.n_rules}
+                "n_rules": 0 if args.no_rules else ref.n_rules,
+                "rule_checksum": 0 if args.no_rules else ref.rule_checksum}
         verify = {"ok": got == want, "gpu": {k: str(v) for k, v in got.items()},
                   "oracle": {k: str(v) for k, v in want.items()}, "oracle_seconds": time.time() - t0,
                   "oracle_threads": os.cpu_count()}

@@ -242,6 +242,16 @@ int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_
 int kmls_rule_supports(const int32_t* d_rule, int64_t n_rules, const int32_t* d_counts,
                        int64_t n_playlists_total, double* d_out, kmls_stream_t stream);
 
+/* No counterpart in the reference (verification aid). Order-independent 64-bit checksum of a
+ * rule table over (antecedent track ids, consequent track ids, bits of confidence, lift and
+ * support) - the arithmetic is documented at k_rule_checksum in rules.cu and restated by the
+ * CPU oracle, so two implementations' full tables can be compared without moving them.
+ * d_row_items maps bitmap rows to track ids; *d_out is zeroed here. */
+int kmls_rule_checksum(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
+                       int32_t max_k, const int32_t* d_rule, const double* d_confidence,
+                       const double* d_lift, int64_t n_rules, const int32_t* d_row_items,
+                       int64_t n_playlists_total, uint64_t* d_out, kmls_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -8,7 +8,7 @@ the lower-level entry points it is built from. All compute runs in ``libkmls_b20
 from . import synth  # noqa: F401  (numpy only)
 from ._lib import KmlsError, LIB_PATH  # noqa: F401
 from .miner import (MineResult, Prepared, RuleTable, generate_rules, mine_csr, prepare,  # noqa: F401
-                    rules_to_host, thresholds)
+                    rule_checksum, rules_to_host, thresholds)
 from .api import (calculate_and_save_fp_growth_fast, encode_frame, encode_transactions,  # noqa: F401
                   itemsets_frame, mine_ids, most_frequent_tracks, recommendations_from_frame,
                   recommendations_from_result, rules_frame, save_rules, sweep_supports)

@@ -415,6 +415,36 @@ k_rule_supports(const int2* __restrict__ rule, int64_t n, const int32_t* __restr
     out[r] = __ddiv_rn((double)__ldg(counts + rule[r].x), n_total);
 }
 
+// Order-independent checksum of a rule table, for comparing a whole table with another
+// implementation's without moving it: sum over rules of
+//   mix(hA ^ mix(hC + 0x1234) ^ mix(bits(confidence)) ^ mix(bits(lift) + 1) ^ mix(bits(support) + 2)),
+// hA / hC = sum of mix(track id + 1) over the antecedent / consequent members.
+__global__ void __launch_bounds__(256)
+k_rule_checksum(Arena a, const int2* __restrict__ rule, const double* __restrict__ conf,
+                const double* __restrict__ lift, int64_t n, const int32_t* __restrict__ row_items,
+                double n_total, unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n;
+       r += (int64_t)gridDim.x * blockDim.x) {
+    const int2 ru = rule[r];
+    const int64_t gid = ru.x;
+    int k = 2;
+    while (gid >= a.id_off[k + 1]) ++k;
+    const int32_t* x = itemset_ptr(a, k, gid);
+    uint64_t ha = 0, hc = 0;
+    for (int t = 0; t < k; ++t) {
+      const uint64_t h = mix64((uint64_t)__ldg(row_items + __ldg(x + t)) + 1);
+      if ((uint32_t)ru.y >> t & 1u) ha += h; else hc += h;
+    }
+    const double sx = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
+    acc += mix64(ha ^ mix64(hc + 0x1234) ^ mix64((uint64_t)__double_as_longlong(conf[r])) ^
+                 mix64((uint64_t)__double_as_longlong(lift[r]) + 1) ^
+                 mix64((uint64_t)__double_as_longlong(sx) + 2));
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
 static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
                       const int64_t* level_sizes, int32_t max_k) {
   KMLS_REQUIRE(max_k >= 0 && max_k <= kMaxLevels - 2, "rules: too many levels");
@@ -521,5 +551,25 @@ extern "C" int kmls_rule_supports(const int32_t* d_rule, int64_t n_rules, const 
   k_rule_supports<<<grid, 256, 0, (cudaStream_t)stream>>>((const int2*)d_rule, n_rules, d_counts,
                                                           (double)n_playlists_total, d_out);
   KMLS_LAUNCHED("k_rule_supports");
+  return 0;
+}
+
+extern "C" int kmls_rule_checksum(const int32_t* d_items, const int32_t* d_counts,
+                                  const int64_t* level_sizes, int32_t max_k, const int32_t* d_rule,
+                                  const double* d_confidence, const double* d_lift, int64_t n_rules,
+                                  const int32_t* d_row_items, int64_t n_playlists_total,
+                                  uint64_t* d_out, kmls_stream_t stream) {
+  Arena a;
+  int rc = make_arena(a, d_items, d_counts, nullptr, level_sizes, max_k);
+  if (rc) return rc;
+  KMLS_REQUIRE(n_rules >= 0 && n_playlists_total > 0 && d_out, "kmls_rule_checksum: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  KMLS_CUDA(cudaMemsetAsync(d_out, 0, sizeof(uint64_t), s));
+  if (n_rules == 0) return 0;
+  KMLS_REQUIRE(d_rule && d_confidence && d_lift && d_row_items, "kmls_rule_checksum: null pointer");
+  int grid = (int)std::min<int64_t>((n_rules + 255) / 256, (int64_t)num_sms() * 16);
+  k_rule_checksum<<<grid, 256, 0, s>>>(a, (const int2*)d_rule, d_confidence, d_lift, n_rules, d_row_items,
+                                       (double)n_playlists_total, (unsigned long long*)d_out);
+  KMLS_LAUNCHED("k_rule_checksum");
   return 0;
 }

@@ -581,6 +581,18 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
                      res.n_playlists)
 
 
+def rule_checksum(res: MineResult, rules: RuleTable) -> int:
+    """Order-independent checksum of the whole rule table, computed on the device (same
+    arithmetic as the CPU oracle's): compares full-size tables without copying them."""
+    out = torch.zeros(1, dtype=torch.int64, device=res.row_items.device)
+    sizes = np.asarray(rules.level_sizes, dtype=np.int64)
+    if rules.n_rules:
+        _lib.call("kmls_rule_checksum", rules.arena_items, rules.arena_counts, sizes.ctypes.data,
+                  len(res.levels), rules.rule, rules.confidence, rules.lift, rules.n_rules,
+                  res.row_items, res.n_playlists, out, _stream())
+    return int(out.item()) & ((1 << 64) - 1)
+
+
 def rules_to_host(res: MineResult, rules: RuleTable):
     """[(antecedent frozenset, consequent frozenset, support, confidence, lift)] with TRACK
     ids as members — plain Python objects, for artifacts and tests (small tables only)."""

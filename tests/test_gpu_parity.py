@@ -370,6 +370,10 @@ def test_rules_against_oracle_medium():
     got = kmls_b200.rules_to_host(res, rules)
     assert len(got) == len(want)
     assert {(a, c): (x, y, z) for a, c, x, y, z in got} == {(a, c): (x, y, z) for a, c, x, y, z in want}
+    # the device-side checksum of the whole table = the C++ oracle's = the formula applied on the host
+    t1, tk = M.thresholds(s, n)
+    ref = fpgrowth_c.fpgrowth(off, items, 800, t1, tk, rules_min_confidence=conf)
+    assert kmls_b200.rule_checksum(res, rules) == ref.rule_checksum == fpgrowth_c.rule_checksum(want)
 
 
 def test_two_threshold_split_at_scale():
