@@ -21,21 +21,47 @@ namespace kmls {
 // loads and a warp-shuffle reduce. Both rows live in the class's compacted column space and
 // are roww[p] words wide. Algorithmic bytes: 2 * roww * 4 per candidate.
 // ---------------------------------------------------------------------------------------
+constexpr int kCountIlp = 4;   // candidates in flight per warp
+
 __global__ void __launch_bounds__(256)
 k_count_pairs(const uint32_t* __restrict__ arena, const int64_t* __restrict__ rowptr,
               const int32_t* __restrict__ roww, const int32_t* __restrict__ cand_p,
               const int32_t* __restrict__ cand_q, int64_t n_cand, int32_t* __restrict__ cand_cnt) {
   const int lane = threadIdx.x & 31;
-  for (int64_t c = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); c < n_cand;
-       c += (int64_t)gridDim.x * 8) {
-    const int32_t p = __ldg(cand_p + c), q = __ldg(cand_q + c);
-    const int nv = __ldg(roww + p) >> 2;
-    const uint4* rp = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + p));
-    const uint4* rq = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + q));
-    int acc = 0;
-    for (int v = lane; v < nv; v += 32) acc += popc4(and4(ldg4(rp + v), ldg4(rq + v)));
-    acc = warp_sum(acc);
-    if (lane == 0) cand_cnt[c] = acc;
+  const int64_t warp0 = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int64_t stride = (int64_t)gridDim.x * 8;
+  // Each candidate is a chain of dependent loads (ids -> row pointers -> row words), so a
+  // warp keeps kCountIlp candidates in flight: all ids first, then all pointers, then the
+  // first 128-bit word pair of every row, and only then the reductions.
+  for (int64_t c0 = warp0 * kCountIlp; c0 < n_cand; c0 += stride * kCountIlp) {
+    int32_t p[kCountIlp], q[kCountIlp];
+#pragma unroll
+    for (int u = 0; u < kCountIlp; ++u) {
+      const int64_t c = min(c0 + u, n_cand - 1);
+      p[u] = __ldg(cand_p + c);
+      q[u] = __ldg(cand_q + c);
+    }
+    int nv[kCountIlp];
+    const uint4 *rp[kCountIlp], *rq[kCountIlp];
+#pragma unroll
+    for (int u = 0; u < kCountIlp; ++u) {
+      nv[u] = __ldg(roww + p[u]) >> 2;
+      rp[u] = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + p[u]));
+      rq[u] = reinterpret_cast<const uint4*>(arena + __ldg(rowptr + q[u]));
+    }
+    uint4 a0[kCountIlp], b0[kCountIlp];
+#pragma unroll
+    for (int u = 0; u < kCountIlp; ++u) {
+      a0[u] = lane < nv[u] ? ldg4(rp[u] + lane) : make_uint4(0, 0, 0, 0);
+      b0[u] = lane < nv[u] ? ldg4(rq[u] + lane) : make_uint4(0, 0, 0, 0);
+    }
+#pragma unroll
+    for (int u = 0; u < kCountIlp; ++u) {
+      int acc = popc4(and4(a0[u], b0[u]));
+      for (int v = lane + 32; v < nv[u]; v += 32) acc += popc4(and4(ldg4(rp[u] + v), ldg4(rq[u] + v)));
+      acc = warp_sum(acc);
+      if (lane == 0 && c0 + u < n_cand) cand_cnt[c0 + u] = acc;
+    }
   }
 }
 
@@ -303,7 +329,7 @@ extern "C" int kmls_count_pairs(const uint32_t* d_arena, const int64_t* d_rowptr
   // d_arena may be NULL when no row of the level was materialised (all widths are 0)
   KMLS_REQUIRE(d_rowptr && d_roww && d_cand_p && d_cand_q && d_cand_cnt,
                "kmls_count_pairs: null pointer");
-  int grid = (int)std::min<int64_t>((n_cand + 7) / 8, (int64_t)num_sms() * 64);
+  int grid = (int)std::min<int64_t>((n_cand + 8 * kCountIlp - 1) / (8 * kCountIlp), (int64_t)num_sms() * 64);
   k_count_pairs<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena, d_rowptr, d_roww, d_cand_p,
                                                         d_cand_q, n_cand, d_cand_cnt);
   KMLS_LAUNCHED("k_count_pairs");
@@ -358,10 +384,10 @@ extern "C" int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_r
                "kmls_project_rows: source and destination arenas alias");
   if (d_arena_new == nullptr) return 0;
   int grid = (int)std::min<int64_t>((n + 7) / 8, (int64_t)num_sms() * 64);
+  if (keep_words < 0) keep_words = kKeepWordsDefault;
   k_project_rows<<<grid, 256, 0, (cudaStream_t)stream>>>(d_arena_old, d_rowptr_old, d_roww_old,
                                                          d_par_p, d_par_q, n, d_arena_new,
-                                                         d_rowptr_new, d_roww_new,
-                                                         keep_words < 0 ? kKeepWordsDefault : keep_words);
+                                                         d_rowptr_new, d_roww_new, keep_words);
   KMLS_LAUNCHED("k_project_rows");
   return 0;
 }
