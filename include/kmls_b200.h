@@ -252,6 +252,15 @@ int kmls_rule_checksum(const int32_t* d_items, const int32_t* d_counts, const in
                        const double* d_lift, int64_t n_rules, const int32_t* d_row_items,
                        int64_t n_playlists_total, uint64_t* d_out, kmls_stream_t stream);
 
+/* No counterpart in the reference (verification aid). Pass 2 computes support, confidence and
+ * lift without a division instruction sequence per quotient (reciprocal + FMA corrections,
+ * rules.cu div_by_rcp). This draws n_samples pseudo-random count triples cX <= cA, cC <= N
+ * from `seed`, evaluates the quotients of a split both ways (that path and __ddiv_rn) and
+ * adds the number of quotients whose bits differ to *d_mismatches (zeroed here); it must stay
+ * 0. */
+int kmls_rule_division_selftest(int64_t n_playlists_total, int64_t n_samples, uint64_t seed,
+                                uint64_t* d_mismatches, kmls_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,6 +32,7 @@ namespace kmls {
 constexpr int kMaxLevels = 32;
 constexpr int kMaxRuleK = 15;  // 2^(k-1) subset table per warp must fit in shared memory
 constexpr int kRuleIlp = 2;    // independent index probes in flight per lane
+constexpr int kWriteIlp = 2;   // groups of 32 splits whose pass-1 pairs are loaded ahead in pass 2
 
 struct Arena {
   const int32_t* items;
@@ -75,53 +76,83 @@ __global__ void __launch_bounds__(256) k_trie_build(Arena a, int4* __restrict__ 
   }
 }
 
-// (child gid, child count) of the child of `parent_gid` whose last member is `item`;
-// gid = -1 if absent. Children are sorted by last member.
-__device__ __forceinline__ int2 trie_child(const int4* __restrict__ node, int32_t parent_gid,
-                                           int32_t item) {
-  if (parent_gid < 0) return make_int2(-1, -1);
-  const int4 p = __ldg(node + parent_gid);
-  int lo = 0, hi = p.y;
+// The child of a node whose last member is `item`, searched among the node's children
+// node[first .. first + n) (sorted by last member); n < 0 = the node itself is missing. Returns
+// the child's node, .y = -1 if absent. Indices are below 2^31, so unsigned 32-bit offsets
+// address the index with one instruction.
+__device__ __forceinline__ void trie_bisect(const int4* __restrict__ node, int32_t first, int32_t n,
+                                            int32_t item, int& lo, int& hi) {
+  lo = 0;
+  hi = n;
   while (hi - lo > 4) {                      // long child lists: bisect down to 4 candidates
     const int mid = (lo + hi) >> 1;
-    if (__ldg(node + p.x + mid).z <= item) lo = mid; else hi = mid;
+    if (__ldg(&node[(uint32_t)(first + mid)].z) <= item) lo = mid; else hi = mid;
   }
+}
+
+__device__ __forceinline__ int4 trie_find(const int4* __restrict__ node, int32_t first, int32_t n,
+                                          int32_t item) {
+  int lo, hi;
+  trie_bisect(node, first, n, item, lo, hi);
+  int4 r = make_int4(-1, -1, -1, -1);
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     if (lo + i < hi) {
-      const int4 c = __ldg(node + p.x + lo + i);
-      if (c.z == item) return make_int2(p.x + lo + i, c.w);
+      const int4 c = __ldg(node + (uint32_t)(first + lo + i));
+      if (c.z == item) r = c;
     }
   }
-  return make_int2(-1, -1);
+  return r;
 }
 
 struct RuleVals {
   bool k1, k2;
   double c1, c2, l1, l2;
 };
+
+// RN(a / b) from y = RN(1 / b) without a division: q = RN(a y), then twice
+//   r = a - b q (exact, one FMA), q = RN(q + r y).
+// Markstein's theorem (Markstein 1990; Muller et al., Handbook of Floating-Point Arithmetic,
+// "division with an FMA"): if y approximates 1/b with relative error < 2^-53 and q is a
+// faithful rounding of a/b, one such correction returns the correctly rounded quotient.
+// RN(1/b) has relative error <= u/(1+u) < 2^-53; RN(a y) is within 1.5 ulp of a/b, not always
+// faithful, but the first correction rounds a value within 2^-52 ulp of a/b and therefore IS
+// faithful, so the second one meets the theorem's conditions for every normal a, b (all
+// quantities here are between 2^-31 and 2^31). __ddiv_rn computes its own reciprocal for
+// every quotient (about 30 instructions); pass 2 divides six times per split by only three
+// different divisors (N, cA/N, cC/N), which made it issue-bound, not HBM-bound.
+__device__ __forceinline__ double div_by_rcp(double a, double b, double y) {
+  double q = __dmul_rn(a, y);
+  double r = __fma_rn(-b, q, a);
+  q = __fma_rn(r, y, q);
+  r = __fma_rn(-b, q, a);
+  return __fma_rn(r, y, q);
+}
+
 __device__ __forceinline__ RuleVals rule_values(double s_x, int32_t ca, int32_t cc, double n_total,
-                                                double min_conf) {
+                                                double rcp_n, double min_conf) {
   RuleVals r;
-  const double s_a = __ddiv_rn((double)ca, n_total), s_c = __ddiv_rn((double)cc, n_total);
-  r.c1 = __ddiv_rn(s_x, s_a);
-  r.c2 = __ddiv_rn(s_x, s_c);
+  const double s_a = div_by_rcp((double)ca, n_total, rcp_n), s_c = div_by_rcp((double)cc, n_total, rcp_n);
+  const double y_a = __drcp_rn(s_a), y_c = __drcp_rn(s_c);
+  r.c1 = div_by_rcp(s_x, s_a, y_a);
+  r.c2 = div_by_rcp(s_x, s_c, y_c);
   r.k1 = r.c1 >= min_conf;
   r.k2 = r.c2 >= min_conf;
-  r.l1 = __ddiv_rn(r.c1, s_c);
-  r.l2 = __ddiv_rn(r.c2, s_a);
+  r.l1 = div_by_rcp(r.c1, s_c, y_c);
+  r.l2 = div_by_rcp(r.c2, s_a, y_a);
   return r;
 }
 
-// confidence >= min_conf for confidence = fl(fl(cx/N) / fl(ca/N)), decided from the float
-// ratio cx/ca whenever that is clearly (1e-5 relative, far above both the float and the
-// double rounding errors) on one side of the threshold; the exact doubles otherwise.
-__device__ __forceinline__ bool conf_keep(int32_t cx, int32_t ca, double s_x, double n_total,
-                                          double min_conf) {
-  const double r = (double)__fdividef((float)cx, (float)ca);
-  if (r > min_conf * 1.00001) return true;
-  if (r < min_conf * 0.99999) return false;
-  return __ddiv_rn(s_x, __ddiv_rn((double)ca, n_total)) >= min_conf;
+// confidence >= min_conf for confidence = fl(fl(cx/N) / fl(ca/N)), decided in fp32 whenever
+// cx is clearly (1e-5 relative, far above the four float roundings involved) on one side of
+// ca * min_conf; the exact doubles otherwise. thr_hi / thr_lo = (float)(min_conf * (1 +- 1e-5)).
+__device__ __forceinline__ bool conf_keep(float fx, int32_t cx, int32_t ca, float thr_hi, float thr_lo,
+                                          double n_total, double min_conf) {
+  const float fa = (float)ca;
+  if (fx > fa * thr_hi) return true;
+  if (fx < fa * thr_lo) return false;
+  asm volatile("" : "+r"(cx));   // keeps cx / N of this rare path from being hoisted out of the split loops
+  return __ddiv_rn(__ddiv_rn((double)cx, n_total), __ddiv_rn((double)ca, n_total)) >= min_conf;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -141,23 +172,43 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
   extern __shared__ int32_t smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
   const int n_sub = 1 << (k - 1);          // subsets of P (including the empty one)
-  int32_t* tab_gid = smem + (size_t)warp * 2 * n_sub;
-  int32_t* tab_cnt = tab_gid + n_sub;
+  // per warp, for every subset S of the class prefix P: its children in the index (first
+  // child's global id, how many; -1 = S is not in the index) and count(S)
+  int32_t* tab_first = smem + (size_t)warp * 3 * n_sub;
+  int32_t* tab_n = tab_first + n_sub;
+  int32_t* tab_cnt = tab_n + n_sub;
   const int64_t lvl_first = a.id_off[k];   // global id of the level's first itemset
   const int n_part = n_sub - 1;            // antecedent masks 1 .. n_sub-1
   const int64_t n_chunks = (lvl_count + chunk - 1) / chunk;
+  const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
+  const int32_t* items_lvl = a.items + a.item_off[k] + lvl_begin * k;
+  const int32_t* counts_lvl = a.counts + lvl_first + lvl_begin;
+  // Subsets of P by dynamic programming over the index: subset m with highest member h =
+  // child `member h` of subset m without h. Only masks >= 2^d are resolved, d = first prefix
+  // position that differs from the prefix the table was built for.
+  auto resolve = [&](int d, int32_t my_item) {
+    for (int h = d; h < k - 1; ++h) {
+      const int32_t ph = __shfl_sync(0xffffffffu, my_item, h);
+      for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
+        const int rest = m ^ (1 << h);
+        int4 c;
+        if (rest == 0) c = __ldg(node + (uint32_t)ph);          // level-1 id = row index
+        else c = trie_find(node, tab_first[rest], tab_n[rest], ph);
+        if (c.y < 0) atomicAdd(missing, 1);
+        tab_first[m] = c.x;
+        tab_n[m] = c.y;
+        tab_cnt[m] = c.w;
+      }
+      __syncwarp();
+    }
+  };
   // A warp walks `chunk` consecutive itemsets. Consecutive classes of the sorted table
   // usually differ only in the LAST member of their prefix, so the subsets of P that avoid
-  // the changed members are still in the table: only masks >= 2^d are resolved again, d =
-  // first prefix position that changed (d = 0 for the first class of the chunk).
+  // the changed members are still in the table (d = 0 for the first class of the chunk).
   for (int64_t ch = (int64_t)blockIdx.x * nwarps + warp; ch < n_chunks;
        ch += (int64_t)gridDim.x * nwarps) {
     const int64_t j_end = min(lvl_count, (ch + 1) * chunk);
-    // Lane t holds member t of the current itemset; the next itemset's members and count are
-    // fetched one iteration ahead so that only the index probes expose memory latency.
     const int64_t j0 = ch * chunk;
-    const int32_t* items_lvl = a.items + a.item_off[k] + lvl_begin * k;
-    const int32_t* counts_lvl = a.counts + lvl_first + lvl_begin;
     if (n_sub <= 16) {
       // Short itemsets (k <= 5): lane = (sibling in the group, antecedent mask). The group is a
       // run of up to 32 / n_sub siblings of ONE class, so that all of them use the same
@@ -175,19 +226,7 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
           d = nm ? __ffs(nm) - 1 : k - 1;
         }
         if (!have_head || d < k - 1) {
-          for (int h = d; h < k - 1; ++h) {
-            const int32_t ph = __shfl_sync(0xffffffffu, my_item, h);
-            for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
-              const int rest = m ^ (1 << h);
-              int2 gc;
-              if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));
-              else gc = trie_child(node, tab_gid[rest], ph);
-              if (gc.x < 0) atomicAdd(missing, 1);
-              tab_gid[m] = gc.x;
-              tab_cnt[m] = gc.y;
-            }
-            __syncwarp();
-          }
+          resolve(d, my_item);
           head_item = my_item;
           have_head = true;
         }
@@ -204,15 +243,16 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
         if (active) {
           const int32_t last = __ldg(items_lvl + sib * k + (k - 1));
           const int32_t c_x = __ldg(counts_lvl + sib);
-          const double s_x = __ddiv_rn((double)c_x, n_total);
           const int32_t ca = tab_cnt[am];
           const int rest = (n_sub - 1) ^ am;
-          const int32_t cc = rest == 0 ? __ldg(a.counts + last) : trie_child(node, tab_gid[rest], last).y;
+          const int32_t cc = rest == 0 ? __ldg(a.counts + last)
+                                       : trie_find(node, tab_first[rest], tab_n[rest], last).w;
           if (cc < 0 || ca < 0) {
             atomicAdd(missing, 1);
           } else {
-            k1 = conf_keep(c_x, ca, s_x, n_total, min_conf);
-            k2 = conf_keep(c_x, cc, s_x, n_total, min_conf);
+            const float fx = (float)c_x;
+            k1 = conf_keep(fx, c_x, ca, thr_hi, thr_lo, n_total, min_conf);
+            k2 = conf_keep(fx, c_x, cc, thr_hi, thr_lo, n_total, min_conf);
           }
           part[sib * n_part + (am - 1)] = make_int2(ca, cc);
         }
@@ -223,6 +263,8 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
       __syncwarp();
       continue;
     }
+    // Lane t holds member t of the current itemset; the next itemset's members and count are
+    // fetched one iteration ahead so that only the index probes expose memory latency.
     int32_t nx_item = lane < k ? __ldg(items_lvl + j0 * k + lane) : 0;
     int32_t nx_cnt = __ldg(counts_lvl + j0);
     int32_t head_item = -1;                // member `lane` of the prefix whose subsets are in the table
@@ -241,78 +283,59 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
         d = nm ? __ffs(nm) - 1 : k - 1;
       }
       if (!have_head || d < k - 1) {
-        for (int h = d; h < k - 1; ++h) {
-          const int32_t ph = __shfl_sync(0xffffffffu, my_item, h);
-          for (int m = (1 << h) + lane; m < (2 << h); m += 32) {
-            const int rest = m ^ (1 << h);
-            int2 gc;
-            if (rest == 0) gc = make_int2(ph, __ldg(a.counts + ph));   // level-1 id = row index
-            else gc = trie_child(node, tab_gid[rest], ph);
-            if (gc.x < 0) atomicAdd(missing, 1);
-            tab_gid[m] = gc.x;
-            tab_cnt[m] = gc.y;
-          }
-          __syncwarp();
-        }
+        resolve(d, my_item);
         head_item = my_item;
         have_head = true;
       }
       const int32_t last = __shfl_sync(0xffffffffu, my_item, k - 1);
-      const double s_x = __ddiv_rn((double)c_x, n_total);
+      const float fx = (float)c_x;
+      int2* pj = part + j * n_part - 1;    // indexed by antecedent mask 1 .. n_sub-1
       int kept = 0;
-      // kRuleIlp antecedent masks per lane and iteration: their first index probes are all
-      // issued before any is consumed
+      // kRuleIlp antecedent masks per lane and iteration: the candidate children of all of
+      // them are loaded before any is compared
       for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
-        int am[kRuleIlp];
-        int32_t cc[kRuleIlp];
-        int4 pn[kRuleIlp];
-        bool probe[kRuleIlp];
-        // phase 1: the parents' nodes of kRuleIlp lookups (independent loads)
+        int32_t cc[kRuleIlp], first[kRuleIlp];
+        int lo[kRuleIlp], hi[kRuleIlp];
 #pragma unroll
         for (int u = 0; u < kRuleIlp; ++u) {
-          am[u] = a0 + u * 32 + lane;
-          probe[u] = false;
+          const int am = a0 + u * 32 + lane;
           cc[u] = -1;
-          if (am[u] < n_sub) {
-            const int rest = (n_sub - 1) ^ am[u];
+          lo[u] = hi[u] = 0;
+          first[u] = 0;
+          if (am < n_sub) {
+            const int rest = (n_sub - 1) ^ am;
             if (rest == 0) {
               cc[u] = __ldg(a.counts + last);
-            } else if (tab_gid[rest] >= 0) {
-              pn[u] = __ldg(node + tab_gid[rest]);
-              probe[u] = true;
+            } else {
+              first[u] = tab_first[rest];
+              trie_bisect(node, first[u], tab_n[rest], last, lo[u], hi[u]);
             }
           }
         }
-        // phase 2: search `last` among each parent's children
+        int2 cand[kRuleIlp][4];              // (last member, count) of up to 4 candidate children
+#pragma unroll
+        for (int u = 0; u < kRuleIlp; ++u)
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            cand[u][i] = lo[u] + i < hi[u]
+                             ? __ldg(reinterpret_cast<const int2*>(node + (uint32_t)(first[u] + lo[u] + i)) + 1)
+                             : make_int2(-1, -1);
 #pragma unroll
         for (int u = 0; u < kRuleIlp; ++u) {
-          if (probe[u]) {
-            int lo = 0, hi = pn[u].y;
-            while (hi - lo > 4) {
-              const int mid = (lo + hi) >> 1;
-              if (__ldg(node + pn[u].x + mid).z <= last) lo = mid; else hi = mid;
-            }
-            int4 c[4];
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              c[i] = lo + i < hi ? __ldg(node + pn[u].x + lo + i) : make_int4(0, 0, -1, -1);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-              if (c[i].z == last) cc[u] = c[i].w;
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < kRuleIlp; ++u) {
+          for (int i = 0; i < 4; ++i)
+            if (cand[u][i].x == last) cc[u] = cand[u][i].y;
+          const int am = a0 + u * 32 + lane;
           bool k1 = false, k2 = false;
-          if (am[u] < n_sub) {
-            const int32_t ca = tab_cnt[am[u]];
+          if (am < n_sub) {
+            const int32_t ca = tab_cnt[am];
             if (cc[u] < 0 || ca < 0) {
               atomicAdd(missing, 1);
             } else {
-              k1 = conf_keep(c_x, ca, s_x, n_total, min_conf);
-              k2 = conf_keep(c_x, cc[u], s_x, n_total, min_conf);
+              k1 = conf_keep(fx, c_x, ca, thr_hi, thr_lo, n_total, min_conf);
+              k2 = conf_keep(fx, c_x, cc[u], thr_hi, thr_lo, n_total, min_conf);
             }
-            part[j * n_part + (am[u] - 1)] = make_int2(ca, cc[u]);
+            pj[am] = make_int2(ca, cc[u]);
           }
           kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
         }
@@ -325,7 +348,9 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
 
 // K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) pairs of pass 1,
 // recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
-// rank): ordered by antecedent mask, A -> C before C -> A.
+// rank). Order inside an itemset: per block of 32 antecedent masks (the whole itemset for
+// k <= 6), first the kept rules A -> C in mask order, then the kept rules C -> A in mask
+// order - so that every store instruction of the warp writes one contiguous run.
 __global__ void __launch_bounds__(256)
 k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
               const int2* __restrict__ part, const int64_t* __restrict__ rule_off,
@@ -335,11 +360,12 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
   const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
   const uint32_t full = (1u << k) - 1u;
   const int64_t lvl_first = a.id_off[k];
+  const double rcp_n = __drcp_rn(n_total);
   if (n_sub <= 16) {
     // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, antecedent
     // mask), so that the lanes are not left idle by the few splits a small itemset has
     const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
-    const uint32_t gmask = (n_sub == 32 ? 0xffffffffu : ((1u << n_sub) - 1u)) << (g * n_sub);
+    const uint32_t gmask = ((1u << n_sub) - 1u) << (g * n_sub);
     const uint32_t below = gmask & ((1u << lane) - 1u);
     const int64_t n_groups = (lvl_count + per_warp - 1) / per_warp;
     for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < n_groups;
@@ -348,23 +374,23 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
       RuleVals r;
       r.k1 = r.k2 = false;
       int64_t gid = 0;
-      double s_x = 0;
       if (j < lvl_count && am >= 1) {
         gid = lvl_first + lvl_begin + j;
-        s_x = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
         const int2 cc = __ldg(part + j * n_part + (am - 1));
-        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, min_conf);
+        const double s_x = div_by_rcp((double)__ldg(a.counts + gid), n_total, rcp_n);
+        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, rcp_n, min_conf);
       }
       const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
       if (r.k1 || r.k2) {
-        int64_t o = rule_off[j] + __popc(m1 & below) + __popc(m2 & below);
+        const int64_t base = rule_off[j];
         if (r.k1) {
+          const int64_t o = base + __popc(m1 & below);
           out_rule[o] = make_int2((int32_t)gid, am);
           out_confidence[o] = r.c1;
           out_lift[o] = r.l1;
-          ++o;
         }
         if (r.k2) {
+          const int64_t o = base + __popc(m1 & gmask) + __popc(m2 & below);
           out_rule[o] = make_int2((int32_t)gid, (int32_t)(full ^ (uint32_t)am));
           out_confidence[o] = r.c2;
           out_lift[o] = r.l2;
@@ -373,34 +399,52 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
     }
     return;
   }
+  const uint32_t below = (1u << lane) - 1u;
   for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < lvl_count;
        j += (int64_t)gridDim.x * 8) {
     const int64_t gid = lvl_first + lvl_begin + j;
-    const double s_x = __ddiv_rn((double)__ldg(a.counts + gid), n_total);
+    const int2* pj = part + j * n_part - 1;     // indexed by antecedent mask 1 .. n_sub-1
+    // the loads of kWriteIlp groups of 32 splits are issued before the first is consumed
+    int2 cc[kWriteIlp];
+#pragma unroll
+    for (int u = 0; u < kWriteIlp; ++u) {
+      const int am = 1 + u * 32 + lane;
+      cc[u] = am < n_sub ? __ldg(pj + am) : make_int2(-1, -1);
+    }
+    const double s_x = div_by_rcp((double)__ldg(a.counts + gid), n_total, rcp_n);
     int64_t pos = rule_off[j];
-    for (int a0 = 1; a0 < n_sub; a0 += 32) {
-      const int am = a0 + lane;
-      RuleVals r;
-      r.k1 = r.k2 = false;
-      if (am < n_sub) {
-        const int2 cc = __ldg(part + j * n_part + (am - 1));
-        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, min_conf);
+    for (int a0 = 1; a0 < n_sub; a0 += 32 * kWriteIlp) {
+      int2 nx[kWriteIlp];
+#pragma unroll
+      for (int u = 0; u < kWriteIlp; ++u) {     // next iteration's loads
+        const int am = a0 + (kWriteIlp + u) * 32 + lane;
+        nx[u] = am < n_sub ? __ldg(pj + am) : make_int2(-1, -1);
       }
-      const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
-      const uint32_t below = (1u << lane) - 1u;
-      int64_t o = pos + __popc(m1 & below) + __popc(m2 & below);
-      if (r.k1) {
-        out_rule[o] = make_int2((int32_t)gid, am);
-        out_confidence[o] = r.c1;
-        out_lift[o] = r.l1;
-        ++o;
+#pragma unroll
+      for (int u = 0; u < kWriteIlp; ++u) {
+        const int am = a0 + u * 32 + lane;
+        if (a0 + u * 32 < n_sub) {              // warp-uniform
+          RuleVals r;
+          r.k1 = r.k2 = false;
+          if (cc[u].x >= 0 && cc[u].y >= 0) r = rule_values(s_x, cc[u].x, cc[u].y, n_total, rcp_n, min_conf);
+          const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
+          if (r.k1) {
+            const int64_t o = pos + __popc(m1 & below);
+            out_rule[o] = make_int2((int32_t)gid, am);
+            out_confidence[o] = r.c1;
+            out_lift[o] = r.l1;
+          }
+          if (r.k2) {
+            const int64_t o = pos + __popc(m1) + __popc(m2 & below);
+            out_rule[o] = make_int2((int32_t)gid, (int32_t)(full ^ (uint32_t)am));
+            out_confidence[o] = r.c2;
+            out_lift[o] = r.l2;
+          }
+          pos += __popc(m1) + __popc(m2);
+        }
       }
-      if (r.k2) {
-        out_rule[o] = make_int2((int32_t)gid, (int32_t)(full ^ (uint32_t)am));
-        out_confidence[o] = r.c2;
-        out_lift[o] = r.l2;
-      }
-      pos += __popc(m1) + __popc(m2);
+#pragma unroll
+      for (int u = 0; u < kWriteIlp; ++u) cc[u] = nx[u];
     }
   }
 }
@@ -443,6 +487,31 @@ k_rule_checksum(Arena a, const int2* __restrict__ rule, const double* __restrict
   }
   for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
   if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
+// every quotient of a split through div_by_rcp and through __ddiv_rn; counts differing bits
+__global__ void __launch_bounds__(256)
+k_division_selftest(double n_total, int64_t n_samples, uint64_t seed, unsigned long long* __restrict__ out) {
+  const double rcp_n = __drcp_rn(n_total);
+  const uint64_t n = (uint64_t)n_total;
+  unsigned long long bad = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_samples;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t h0 = mix64(seed + 3 * (uint64_t)i), h1 = mix64(h0 + 1), h2 = mix64(h1 + 2);
+    // cX in [1, N], skewed to small counts every other sample; cA, cC in [cX, N]
+    uint64_t cx = 1 + h0 % n;
+    if (i & 1) cx = 1 + cx % (1 + n / 1000);
+    const uint64_t ca = cx + h1 % (n - cx + 1), cc = cx + h2 % (n - cx + 1);
+    const double s_x = div_by_rcp((double)cx, n_total, rcp_n);
+    const RuleVals r = rule_values(s_x, (int32_t)ca, (int32_t)cc, n_total, rcp_n, 0.0);
+    const double e_x = __ddiv_rn((double)cx, n_total), e_a = __ddiv_rn((double)ca, n_total),
+                 e_c = __ddiv_rn((double)cc, n_total);
+    const double e_c1 = __ddiv_rn(e_x, e_a), e_c2 = __ddiv_rn(e_x, e_c);
+    bad += (s_x != e_x) + (r.c1 != e_c1) + (r.c2 != e_c2) + (r.l1 != __ddiv_rn(e_c1, e_c)) +
+           (r.l2 != __ddiv_rn(e_c2, e_a));
+  }
+  for (int o = 16; o > 0; o >>= 1) bad += __shfl_xor_sync(0xffffffffu, bad, o);
+  if ((threadIdx.x & 31) == 0 && bad) atomicAdd(out, bad);
 }
 
 static int make_arena(Arena& a, const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
@@ -504,7 +573,7 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
                "kmls_rules_count: itemset range out of bounds");
   if (lvl_count == 0) return 0;
   KMLS_REQUIRE(d_nodes && d_part && d_rule_cnt && d_missing, "kmls_rules_count: null pointer");
-  const size_t per_warp = sizeof(int32_t) * 2 * ((size_t)1 << (k - 1));
+  const size_t per_warp = sizeof(int32_t) * 3 * ((size_t)1 << (k - 1));
   int warps = (int)std::min<size_t>(8, (200 * 1024) / per_warp);
   KMLS_REQUIRE(warps >= 1, "kmls_rules_count: subset table does not fit in shared memory");
   const size_t smem = per_warp * warps;
@@ -571,5 +640,19 @@ extern "C" int kmls_rule_checksum(const int32_t* d_items, const int32_t* d_count
   k_rule_checksum<<<grid, 256, 0, s>>>(a, (const int2*)d_rule, d_confidence, d_lift, n_rules, d_row_items,
                                        (double)n_playlists_total, (unsigned long long*)d_out);
   KMLS_LAUNCHED("k_rule_checksum");
+  return 0;
+}
+
+extern "C" int kmls_rule_division_selftest(int64_t n_playlists_total, int64_t n_samples, uint64_t seed,
+                                           uint64_t* d_mismatches, kmls_stream_t stream) {
+  KMLS_REQUIRE(n_playlists_total > 0 && n_playlists_total <= 0x7fffffff && n_samples >= 0 && d_mismatches,
+               "kmls_rule_division_selftest: bad arguments");
+  cudaStream_t s = (cudaStream_t)stream;
+  KMLS_CUDA(cudaMemsetAsync(d_mismatches, 0, sizeof(uint64_t), s));
+  if (n_samples == 0) return 0;
+  int grid = (int)std::min<int64_t>((n_samples + 255) / 256, (int64_t)num_sms() * 16);
+  k_division_selftest<<<grid, 256, 0, s>>>((double)n_playlists_total, n_samples, seed,
+                                           (unsigned long long*)d_mismatches);
+  KMLS_LAUNCHED("k_division_selftest");
   return 0;
 }

@@ -376,6 +376,35 @@ def test_rules_against_oracle_medium():
     assert kmls_b200.rule_checksum(res, rules) == ref.rule_checksum == fpgrowth_c.rule_checksum(want)
 
 
+@pytest.mark.parametrize("n", [97, 127, 255, 1021, 4099, 16381])
+def test_rule_doubles_bit_exact_for_awkward_playlist_counts(n):
+    """Pass 2 replaces the six IEEE divisions per split by reciprocal + FMA corrections
+    (rules.cu, div_by_rcp); every confidence and lift must still be the correctly rounded
+    quotient the oracle gets from the CPU's divider. Odd / prime / 2^k-1 playlist counts give
+    1/N the largest rounding errors."""
+    off, items = synth.zipf_playlists(n, 24, mean_draws=12, alpha=0.3, seed=n)
+    s, conf = 0.05, 0.05
+    res, rules = kmls_b200.mine_ids(off, items, 24, s, conf)
+    t1, tk = M.thresholds(s, n)
+    ref = fpgrowth_c.fpgrowth(off, items, 24, t1, tk, rules_min_confidence=conf)
+    assert res.n_itemsets == ref.n and rules.n_rules == ref.n_rules > 5000
+    assert kmls_b200.rule_checksum(res, rules) == ref.rule_checksum
+    if n <= 255:
+        want = M.association_rules([(v / n, k) for k, v in ref.as_dict().items()], conf)
+        got = kmls_b200.rules_to_host(res, rules)
+        assert {(a, c): (x, y, z) for a, c, x, y, z in got} == {(a, c): (x, y, z) for a, c, x, y, z in want}
+
+
+@pytest.mark.parametrize("n", [3, 97, 255, 65535, 999983, 1000000, 2262292, 10000000, 2**31 - 1])
+def test_rule_division_selftest(n):
+    """2^28 pseudo-random splits per playlist count: the reciprocal + FMA quotients of pass 2
+    are bit-identical to those of __ddiv_rn (s_a and s_c are covered through the confidences
+    and lifts computed from them)."""
+    out = torch.ones(1, dtype=torch.int64, device=dev())
+    _lib.call("kmls_rule_division_selftest", n, 1 << 28, 12345 + n, out, stream())
+    assert int(out.item()) == 0
+
+
 def test_two_threshold_split_at_scale():
     # s = 0.07, N = 100k: T1 and Tk differ for many N (SURVEY.md F9); counts near both must
     # land on the right side at level 1 (T1) and at levels >= 2 (Tk)
