@@ -343,6 +343,10 @@ def run_gpu(args):
     algo = {
         "kmls_rules_count": (32 * probes + 8 * splits) / max(world, 1),
         "kmls_rules_write": (8 * splits) / max(world, 1) + 24 * (info.get("rules_this_rank") or 0),
+        # gather route of pass 1 (one GPU): two 4-byte counts read + 8 bytes written per split;
+        # one index lookup (32 B) + 4 bytes written per (itemset, dropped member)
+        "kmls_rules_count_gather": 16 * splits,
+        "kmls_rules_subsets": 36 * sum(n * (k - 1) for k, n in enumerate(lv_sizes, start=1) if k >= 2),
     }
 
     def roof_of(nm, kernel, bound):
@@ -360,6 +364,7 @@ def run_gpu(args):
                 "algorithmic_work_per_step": work}
 
     kernel_of = {"kmls_rules_count": ("k_rules_count", "hbm"), "kmls_rules_write": ("k_rules_write", "hbm"),
+                 "kmls_rules_count_gather": ("k_rules_gather", "hbm"), "kmls_rules_subsets": ("k_rules_subsets", "hbm"),
                  "kmls_pair_counts_i8": ("k_pair_gemm_i8", "tensor"), "kmls_project_rows": ("k_project_rows", "hbm"),
                  "kmls_count_candidates": ("k_count_candidates", "hbm"), "kmls_encode_bitmap": ("k_encode_bitmap", "hbm"),
                  "kmls_row_popcount": ("k_row_popcount", "hbm"), "kmls_item_histogram": ("k_item_histogram", "hbm")}

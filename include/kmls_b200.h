@@ -227,6 +227,24 @@ int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int6
                      int32_t max_k, int32_t k, int64_t lvl_begin, int64_t lvl_count,
                      const void* d_nodes, int64_t n_playlists_total, double min_confidence,
                      void* d_part, int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
+/* Pass 1 without a search per split, for a caller that runs pass 1 over WHOLE levels in
+ * ascending order on one stream (one GPU holding the whole table). Two calls per level k:
+ *  kmls_rules_subsets: d_sub[level_sizes[k] * (k-1)]: entry (x, i) = index inside level k-1 of
+ *    itemset x without its i-th member (i < k-1, i.e. the subsets that keep the last member);
+ *    d_sub_prev = the same array of level k-1 (unused for k = 2). One search per entry.
+ *  kmls_rules_count_gather: fills d_part / d_rule_cnt of the whole level k like
+ *    kmls_rules_count, reading every subset count from d_part_prev = the d_part of the whole
+ *    level k-1 (unused for k = 2): count(A) from the parent's row, count(C) from the row of
+ *    the subset that drops A's first member.
+ * Same results as kmls_rules_count; *d_missing as there. */
+int kmls_rules_subsets(const int32_t* d_items, const int32_t* d_par, const int64_t* level_sizes,
+                       int32_t max_k, int32_t k, const void* d_nodes, const int32_t* d_sub_prev,
+                       int32_t* d_sub, int32_t* d_missing, kmls_stream_t stream);
+int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
+                            const int64_t* level_sizes, int32_t max_k, int32_t k,
+                            const int32_t* d_sub, const void* d_part_prev,
+                            int64_t n_playlists_total, double min_confidence, void* d_part,
+                            int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
 /* Pass 2: d_rule_off[lvl_count] = first output slot of each itemset (exclusive scan of the
  * kept counts over everything this rank emits). Rule r: d_out_rule[2r] = itemset (global id),
  * d_out_rule[2r+1] = antecedent mask (bit t = t-th member; the consequent is the rest),

@@ -91,7 +91,7 @@ __device__ __forceinline__ void trie_bisect(const int4* __restrict__ node, int32
 }
 
 __device__ __forceinline__ int4 trie_find(const int4* __restrict__ node, int32_t first, int32_t n,
-                                          int32_t item) {
+                                          int32_t item, int32_t* gid = nullptr) {
   int lo, hi;
   trie_bisect(node, first, n, item, lo, hi);
   int4 r = make_int4(-1, -1, -1, -1);
@@ -99,7 +99,10 @@ __device__ __forceinline__ int4 trie_find(const int4* __restrict__ node, int32_t
   for (int i = 0; i < 4; ++i) {
     if (lo + i < hi) {
       const int4 c = __ldg(node + (uint32_t)(first + lo + i));
-      if (c.z == item) r = c;
+      if (c.z == item) {
+        r = c;
+        if (gid) *gid = first + lo + i;
+      }
     }
   }
   return r;
@@ -346,6 +349,163 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
   }
 }
 
+// ---------------------------------------------------------------------------------------
+// K5 pass 1 without searching per split ("gather" route, used when one GPU holds the whole
+// previous level's output). Every subset count a k-itemset X = P + {x} needs was already
+// produced by level k-1:
+//   count(A), A a subset of P: P is X's parent, a (k-1)-itemset with prefix P' and last member
+//     q. Its row holds, for every antecedent mask a' over P', (count(A'), count(P' \ A' + {q})):
+//     A without q is an A', A with q is a consequent.
+//   count(C), C = R + {x}, R a proper subset of P: with p_i the first member of P not in R, C
+//     is a consequent of X_i = X \ {p_i}, which has the same last member x.
+// What remains to be searched are the k-1 rows X_i per itemset (k_rules_subsets, one thread
+// per (itemset, i)); X_i = child x of P \ {p_i}, and P \ {p_i} is what the parent's own
+// k_rules_subsets output names (or the parent's parent for i = k-2).
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_rules_subsets(Arena a, int k, const int4* __restrict__ node, const int32_t* __restrict__ sub_prev,
+                int32_t* __restrict__ sub, int32_t* __restrict__ missing) {
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k];
+  const int i = blockIdx.y;                  // which member is dropped
+  const int32_t* items_k = a.items + a.item_off[k];
+  const int32_t* par_k = a.par + (a.id_off[k] - a.id_off[2]);
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_k;
+       j += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t x = __ldg(items_k + j * k + (k - 1));
+    int32_t out;
+    if (k == 2) {
+      out = x;                               // {p0, x} \ {p0} = {x}: level-1 index = row
+    } else {
+      const int32_t row_p = __ldg(par_k + j);
+      // P \ {p_i} as an index into level k-2
+      int32_t pi;
+      if (i == k - 2) pi = __ldg(a.par + (a.id_off[k - 1] - a.id_off[2]) + row_p);
+      else pi = __ldg(sub_prev + (int64_t)row_p * (k - 2) + i);
+      out = -1;
+      if (pi >= 0) {
+        const int4 nd = __ldg(node + (uint32_t)(a.id_off[k - 2] + pi));
+        int32_t gid = -1;
+        trie_find(node, nd.x, nd.y, x, &gid);
+        if (gid >= 0) out = gid - (int32_t)a.id_off[k - 1];
+      }
+      if (out < 0) atomicAdd(missing, 1);
+    }
+    sub[j * (k - 1) + i] = out;
+  }
+}
+
+// (count(A), count(C)) of the split `am` of an itemset: see the comment above.
+//   row_p / c_p: the parent's index in level k-1 and its count; row_i: index in level k-1 of
+//   X \ {p_i}, i = first member of A; npp = entries per row of part_prev = 2^(k-2) - 1.
+__device__ __forceinline__ int2 split_counts(const Arena& a, int k, int am, int32_t row_p, int32_t c_p,
+                                             int32_t row_i, int i, int32_t last,
+                                             const int2* __restrict__ part_prev) {
+  const int n_sub = 1 << (k - 1), top = n_sub >> 1, npp = top - 1;
+  int2 r;
+  if (am == n_sub - 1) {
+    r.x = c_p;                                             // A = P
+  } else if (!(am & top)) {
+    r.x = row_p < 0 ? -1 : __ldg(&part_prev[(int64_t)row_p * npp + (am - 1)].x);
+  } else {
+    const int ap = (top - 1) ^ (am ^ top);                 // P' \ (A \ {q})
+    r.x = row_p < 0 ? -1 : __ldg(&part_prev[(int64_t)row_p * npp + (ap - 1)].y);
+  }
+  const int rest = (n_sub - 1) ^ am;
+  if (rest == 0) {
+    r.y = __ldg(a.counts + last);                          // C = {x}
+  } else if (row_i < 0) {
+    r.y = -1;
+  } else {
+    const int ap = (am >> (i + 1)) << i;                   // A \ {p_i} as a mask over P \ {p_i}
+    if (ap == 0) r.y = __ldg(a.counts + a.id_off[k - 1] + row_i);   // C = X_i itself
+    else r.y = __ldg(&part_prev[(int64_t)row_i * npp + (ap - 1)].y);
+  }
+  return r;
+}
+
+__global__ void __launch_bounds__(256)
+k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int2* __restrict__ part_prev,
+               double n_total, double min_conf, int2* __restrict__ part,
+               int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
+  const int lane = threadIdx.x & 31;
+  const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k];
+  const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
+  const int32_t* items_k = a.items + a.item_off[k];
+  const int32_t* counts_k = a.counts + a.id_off[k];
+  const int32_t* par_k = a.par + (a.id_off[k] - a.id_off[2]);
+  const int32_t* counts_p = a.counts + a.id_off[k - 1];
+  if (n_sub <= 16) {
+    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, antecedent mask)
+    const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
+    const uint32_t gmask = ((1u << n_sub) - 1u) << (g * n_sub);
+    const int64_t n_groups = (n_k + per_warp - 1) / per_warp;
+    for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < n_groups;
+         w += (int64_t)gridDim.x * 8) {
+      const int64_t j = w * per_warp + g;
+      const bool active = j < n_k && am >= 1;
+      bool k1 = false, k2 = false;
+      if (active) {
+        const int32_t last = __ldg(items_k + j * k + (k - 1));
+        const int32_t c_x = __ldg(counts_k + j);
+        const int32_t row_p = __ldg(par_k + j);
+        const int i = __ffs(am) - 1;
+        const int32_t row_i = __ldg(sub + j * (k - 1) + i);
+        const int2 cc = split_counts(a, k, am, row_p, __ldg(counts_p + row_p), row_i, i, last, part_prev);
+        if (cc.x < 0 || cc.y < 0) {
+          atomicAdd(missing, 1);
+        } else {
+          const float fx = (float)c_x;
+          k1 = conf_keep(fx, c_x, cc.x, thr_hi, thr_lo, n_total, min_conf);
+          k2 = conf_keep(fx, c_x, cc.y, thr_hi, thr_lo, n_total, min_conf);
+        }
+        part[j * n_part + (am - 1)] = cc;
+      }
+      const uint32_t b1 = __ballot_sync(0xffffffffu, k1), b2 = __ballot_sync(0xffffffffu, k2);
+      if (active && am == 1) rule_cnt[j] = __popc(b1 & gmask) + __popc(b2 & gmask);
+    }
+    return;
+  }
+  // long itemsets: one warp per itemset, lane = antecedent mask (blocks of 32)
+  for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < n_k; j += (int64_t)gridDim.x * 8) {
+    const int32_t last = __ldg(items_k + j * k + (k - 1));
+    const int32_t c_x = __ldg(counts_k + j);
+    const int32_t row_p = __ldg(par_k + j);
+    const int32_t c_p = __ldg(counts_p + row_p);
+    const int32_t my_sub = lane < k - 1 ? __ldg(sub + j * (k - 1) + lane) : -1;
+    const float fx = (float)c_x;
+    int2* pj = part + j * n_part - 1;        // indexed by antecedent mask 1 .. n_sub-1
+    int kept = 0;
+    for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
+      int2 cc[kRuleIlp];
+#pragma unroll
+      for (int u = 0; u < kRuleIlp; ++u) {
+        const int am = a0 + u * 32 + lane;
+        const int i = __ffs(am < n_sub ? am : 1) - 1;
+        const int32_t row_i = __shfl_sync(0xffffffffu, my_sub, i);
+        cc[u] = make_int2(0, 0);
+        if (am < n_sub) cc[u] = split_counts(a, k, am, row_p, c_p, row_i, i, last, part_prev);
+      }
+#pragma unroll
+      for (int u = 0; u < kRuleIlp; ++u) {
+        const int am = a0 + u * 32 + lane;
+        bool k1 = false, k2 = false;
+        if (am < n_sub) {
+          if (cc[u].x < 0 || cc[u].y < 0) {
+            atomicAdd(missing, 1);
+          } else {
+            k1 = conf_keep(fx, c_x, cc[u].x, thr_hi, thr_lo, n_total, min_conf);
+            k2 = conf_keep(fx, c_x, cc[u].y, thr_hi, thr_lo, n_total, min_conf);
+          }
+          pj[am] = cc[u];
+        }
+        kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
+      }
+    }
+    if (lane == 0) rule_cnt[j] = kept;
+  }
+}
+
 // K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) pairs of pass 1,
 // recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
 // rank). Order inside an itemset: per block of 32 antecedent masks (the whole itemset for
@@ -586,6 +746,50 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
       a, k, lvl_begin, lvl_count, (const int4*)d_nodes, (double)n_playlists_total, min_confidence,
       chunk, (int2*)d_part, d_rule_cnt, d_missing);
   KMLS_LAUNCHED("k_rules_count");
+  return 0;
+}
+
+extern "C" int kmls_rules_subsets(const int32_t* d_items, const int32_t* d_par,
+                                  const int64_t* level_sizes, int32_t max_k, int32_t k,
+                                  const void* d_nodes, const int32_t* d_sub_prev, int32_t* d_sub,
+                                  int32_t* d_missing, kmls_stream_t stream) {
+  Arena a;
+  int rc = make_arena(a, d_items, nullptr, d_par, level_sizes, max_k);
+  if (rc) return rc;
+  KMLS_REQUIRE(k >= 2 && k <= max_k && k <= kMaxRuleK, "kmls_rules_subsets: level out of range");
+  const int64_t n_k = level_sizes[k];
+  if (n_k == 0) return 0;
+  KMLS_REQUIRE(d_items && d_par && d_nodes && d_sub && d_missing && (k == 2 || d_sub_prev),
+               "kmls_rules_subsets: null pointer");
+  dim3 grid((unsigned)std::min<int64_t>((n_k + 255) / 256, (int64_t)num_sms() * 8), (unsigned)(k - 1));
+  k_rules_subsets<<<grid, 256, 0, (cudaStream_t)stream>>>(a, k, (const int4*)d_nodes, d_sub_prev, d_sub,
+                                                          d_missing);
+  KMLS_LAUNCHED("k_rules_subsets");
+  return 0;
+}
+
+extern "C" int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_counts,
+                                       const int32_t* d_par, const int64_t* level_sizes,
+                                       int32_t max_k, int32_t k, const int32_t* d_sub,
+                                       const void* d_part_prev, int64_t n_playlists_total,
+                                       double min_confidence, void* d_part, int32_t* d_rule_cnt,
+                                       int32_t* d_missing, kmls_stream_t stream) {
+  Arena a;
+  int rc = make_arena(a, d_items, d_counts, d_par, level_sizes, max_k);
+  if (rc) return rc;
+  KMLS_REQUIRE(k >= 2 && k <= max_k && k <= kMaxRuleK, "kmls_rules_count_gather: level out of range");
+  KMLS_REQUIRE(n_playlists_total > 0, "kmls_rules_count_gather: n_playlists_total must be positive");
+  const int64_t n_k = level_sizes[k];
+  if (n_k == 0) return 0;
+  KMLS_REQUIRE(d_items && d_counts && d_par && d_sub && d_part && d_rule_cnt && d_missing &&
+                   (k == 2 || d_part_prev), "kmls_rules_count_gather: null pointer");
+  const int per_warp = k <= 5 ? 32 >> (k - 1) : 1;
+  const int64_t warps = (n_k + per_warp - 1) / per_warp;
+  int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 32);
+  k_rules_gather<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      a, k, d_sub, (const int2*)d_part_prev, (double)n_playlists_total, min_confidence, (int2*)d_part,
+      d_rule_cnt, d_missing);
+  KMLS_LAUNCHED("k_rules_gather");
   return 0;
 }
 

@@ -488,11 +488,14 @@ class RuleTable:
 
 
 def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_000_000_000,
-                   part: Tuple[int, int] = (0, 1)) -> RuleTable:
+                   part: Tuple[int, int] = (0, 1), pass1: str = "auto") -> RuleTable:
     """fp64 confidence/lift for every (itemset, antecedent) split, kept iff
     confidence >= min_confidence (mlxtend ``association_rules`` semantics).
     ``part = (i, n)`` generates only the rules of the i-th of n contiguous slices of the
-    itemset table (how ranks of a multi-GPU job divide the rule table among themselves)."""
+    itemset table (how ranks of a multi-GPU job divide the rule table among themselves).
+    ``pass1``: how the subset counts of a split are found - "gather" (from the previous level's
+    pass-1 output; needs the whole table, i.e. ``part == (0, 1)``), "search" (in the subset
+    index; works on any slice), "auto" = gather when possible."""
     device = res.row_items.device
     dev = _Dev(device)
     s = _stream()
@@ -556,10 +559,29 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
                 raise _lib.KmlsError(f"rule generation supports itemsets of at most 15 members, got {k}")
             plan.append((k, lo - lvl_start, hi - lo, lo - x_begin, dev.empty((hi - lo) * ppi, torch.int64)))
         lvl_start += int(sizes[k])
-    for k, lvl_begin, cnt, out0, part_buf in plan:
-        _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
-                  nodes, res.n_playlists, float(min_confidence), part_buf, rule_cnt[out0:],
-                  missing, s)
+    if pass1 == "auto":
+        pass1 = "gather" if part == (0, 1) else "search"
+    if pass1 == "gather":
+        # whole levels in ascending order: every subset count is read from the previous
+        # level's output; only the k-1 subsets that keep the last member are searched
+        if part != (0, 1):
+            raise ValueError("pass1='gather' needs the whole table on this GPU (part=(0, 1))")
+        sub_prev, part_prev = 0, 0
+        for k, lvl_begin, cnt, out0, part_buf in plan:
+            sub = dev.empty(cnt * (k - 1), torch.int32)
+            _lib.call("kmls_rules_subsets", arena_items, arena_par, sizes_ptr, max_k, k, nodes,
+                      sub_prev, sub, missing, s)
+            _lib.call("kmls_rules_count_gather", arena_items, arena_counts, arena_par, sizes_ptr, max_k,
+                      k, sub, part_prev, res.n_playlists, float(min_confidence), part_buf,
+                      rule_cnt[out0:], missing, s)
+            sub_prev, part_prev = sub, part_buf
+    elif pass1 == "search":
+        for k, lvl_begin, cnt, out0, part_buf in plan:
+            _lib.call("kmls_rules_count", arena_items, arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
+                      nodes, res.n_playlists, float(min_confidence), part_buf, rule_cnt[out0:],
+                      missing, s)
+    else:
+        raise ValueError(f"unknown pass1 {pass1!r}")
     scratch, sbytes = dev.scan_scratch(n_x)
     rule_off = dev.empty(n_x + 1, torch.int64)
     _lib.call("kmls_exclusive_scan_i32", rule_cnt, n_x, rule_off, scratch, sbytes, s)

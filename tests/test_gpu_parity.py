@@ -405,6 +405,40 @@ def test_rule_division_selftest(n):
     assert int(out.item()) == 0
 
 
+def _rule_rows(*tables):
+    """All rules of the given tables as a lexicographically sorted int64[R, 4] array
+    (itemset, antecedent mask, bits of confidence, bits of lift)."""
+    rows = np.concatenate([np.stack([r.rule[:, 0].cpu().numpy().astype(np.int64),
+                                     r.rule[:, 1].cpu().numpy().astype(np.int64),
+                                     r.confidence.cpu().numpy().view(np.int64),
+                                     r.lift.cpu().numpy().view(np.int64)], 1) for r in tables])
+    return rows[np.lexsort(rows.T[::-1])]
+
+
+def test_pass1_gather_route_equals_index_search():
+    """Pass 1 has two routes: subset counts gathered from the previous level's output (one GPU,
+    whole levels) or searched in the subset index (any slice of the table, what the ranks of a
+    multi-GPU job run). Both, and slices that cut levels at arbitrary places, give the same
+    table, which equals the oracle's."""
+    n, t, s, conf = 2500, 22, 0.02, 0.3
+    off, items = synth.zipf_playlists(n, t, mean_draws=19, alpha=0.2, seed=5)
+    res = kmls_b200.mine_csr(torch.from_numpy(off).to(dev()), torch.from_numpy(items).to(dev()), t, s)
+    assert len(res.levels) >= 8                      # k = 6, 7, 8: the long-itemset path, chained
+    full = kmls_b200.generate_rules(res, conf)
+    search = kmls_b200.generate_rules(res, conf, pass1="search")
+    want = _rule_rows(full)
+    assert len(want) == full.n_rules > 1000000
+    assert (_rule_rows(search) == want).all()
+    t1, tk = M.thresholds(s, n)
+    ref = fpgrowth_c.fpgrowth(off, items, t, t1, tk, rules_min_confidence=conf)
+    assert full.n_rules == ref.n_rules
+    assert kmls_b200.rule_checksum(res, full) == ref.rule_checksum == kmls_b200.rule_checksum(res, search)
+    for n_parts in (2, 3, 7):
+        parts = [kmls_b200.generate_rules(res, conf, part=(i, n_parts)) for i in range(n_parts)]
+        assert sum(p.n_rules for p in parts) == full.n_rules
+        assert (_rule_rows(*parts) == want).all()
+
+
 def test_two_threshold_split_at_scale():
     # s = 0.07, N = 100k: T1 and Tk differ for many N (SURVEY.md F9); counts near both must
     # land on the right side at level 1 (T1) and at levels >= 2 (Tk)
