@@ -91,6 +91,13 @@ int kmls_pair_select(const int32_t* d_pair, int32_t n_rows, int32_t thr, int64_t
 int kmls_supports_f64(const int32_t* d_counts, int64_t n, int64_t n_playlists_total,
                       double* d_out, kmls_stream_t stream);
 
+/* No counterpart in the reference (plumbing). Copies n_words (<= 4096) 32-bit words from
+ * device memory to pinned host memory that the device can address (cudaHostAlloc /
+ * cudaHostRegister memory under unified addressing), with a kernel rather than the copy
+ * engine: level sizes read back by the host between levels then never wait behind a bulk
+ * device-to-host transfer. The host reads h_mapped_dst after synchronising the stream. */
+int kmls_words_to_host(const void* d_src, int32_t n_words, void* h_mapped_dst, kmls_stream_t stream);
+
 /* ---- levels k >= 3 (fpgrowth.fpg_step recursion, restated level-wise) ------------------- */
 
 size_t kmls_scan_scratch_bytes(int64_t n);

@@ -220,3 +220,25 @@ extern "C" int kmls_gather_rows(const uint32_t* d_src, const int32_t* d_src_row,
   KMLS_LAUNCHED("k_gather_rows");
   return 0;
 }
+
+// A few bytes from device memory to MAPPED (pinned, device-visible) host memory, written by
+// a kernel instead of the copy engine: the sizes the host reads back between levels then do
+// not queue behind bulk device-to-host transfers of earlier levels' tables.
+namespace kmls {
+__global__ void k_words_to_host(const uint32_t* __restrict__ src, int n_words, volatile uint32_t* dst) {
+  for (int i = threadIdx.x; i < n_words; i += blockDim.x) dst[i] = src[i];
+  __threadfence_system();
+}
+}  // namespace kmls
+
+extern "C" int kmls_words_to_host(const void* d_src, int32_t n_words, void* h_mapped_dst,
+                                  kmls_stream_t stream) {
+  KMLS_REQUIRE(n_words >= 0 && n_words <= 4096, "kmls_words_to_host: at most 4096 words");
+  if (n_words == 0) return 0;
+  KMLS_REQUIRE(d_src && h_mapped_dst && ((uintptr_t)d_src & 3) == 0 && ((uintptr_t)h_mapped_dst & 3) == 0,
+               "kmls_words_to_host: null or misaligned pointer");
+  kmls::k_words_to_host<<<1, 64, 0, (cudaStream_t)stream>>>((const uint32_t*)d_src, n_words,
+                                                            (volatile uint32_t*)h_mapped_dst);
+  KMLS_LAUNCHED("k_words_to_host");
+  return 0;
+}

@@ -102,6 +102,21 @@ class _Dev:
     def empty(self, n, dtype):
         return torch.empty(max(int(n), 1), dtype=dtype, device=self.device)[:int(n)]
 
+    _host_words = {}
+
+    def scalar(self, t: torch.Tensor) -> int:
+        """One int32 / int64 element of a device tensor, read back through a kernel that writes
+        pinned host memory (kmls_words_to_host) instead of ``.item()``: a copy-engine read-back
+        queues behind every bulk device-to-host transfer in flight (the level tables a caller
+        streams out while mining), which serialises the whole loop behind PCIe."""
+        key = (self.device.type, self.device.index)
+        h = _Dev._host_words.get(key)
+        if h is None:
+            h = _Dev._host_words[key] = torch.zeros(8, dtype=torch.int64).pin_memory()
+        _lib.call("kmls_words_to_host", t, t.element_size() // 4, h, _stream())
+        torch.cuda.current_stream().synchronize()
+        return int(h.view(t.dtype)[0])
+
     def scan_scratch(self, n):
         need = int(_lib.value("kmls_scan_scratch_bytes", int(n)))
         if self.scratch.numel() < need:
@@ -316,7 +331,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     stats["thr_k"] = thr
     row_off = dev.empty(n_rows + 1, torch.int64)
     _lib.call("kmls_pair_select", pair, n_rows, thr, 0, row_off, 0, 0, s)
-    n2 = int(row_off[n_rows].item())
+    n2 = dev.scalar(row_off[n_rows])
     stats["levels"].append({"k": 2, "candidates": n_rows * (n_rows - 1) // 2, "frequent": n2})
     if n2 == 0:
         return result(row_items, levels, pair.view(n_rows, n_rows) if keep_pair_counts else None)
@@ -341,13 +356,13 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         scratch, sbytes = dev.scan_scratch(n_new)
         rowptr = dev.empty(n_new + 1, torch.int64)
         _lib.call("kmls_exclusive_scan_i32", roww, n_new, rowptr, scratch, sbytes, s)
-        words = int(rowptr[n_new].item())
+        words = dev.scalar(rowptr[n_new])
         arena = dev.empty(words, torch.int32)
         if first and first_projection == "gather":
             scratch, sbytes = dev.scan_scratch(n_rows)
             tid_off = dev.empty(n_rows + 1, torch.int64)
             _lib.call("kmls_exclusive_scan_i32", parent_cnt_local, n_rows, tid_off, scratch, sbytes, s)
-            tids = dev.empty(int(tid_off[n_rows].item()), torch.int32)
+            tids = dev.empty(dev.scalar(tid_off[n_rows]), torch.int32)
             _lib.call("kmls_row_tidlists", bitmap, n_rows, row_words, tid_off, tids, s,
                       algo_bytes=4 * n_rows * row_words + 4 * int(tids.numel()))
             _lib.call("kmls_project_rows_gather", bitmap, row_words, par_p, par_q, n_new, tids,
@@ -388,7 +403,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         par_k = parents[-1]
         _lib.call("kmls_join_count", items_k, n, k, slots, cap, pair_arg, n_rows, thr, par_k, kept_cnt,
                   kept_mask, kept_off, scratch, sbytes, s)
-        n_cand = int(kept_off[n].item())
+        n_cand = dev.scalar(kept_off[n])
         if n_cand == 0:
             break
         if total + n_cand > max_itemsets * 4:
@@ -408,7 +423,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
             n_groups_d = dev.empty(1, torch.int64)
             _lib.call("kmls_join_write", items_k, n, k, slots, cap, pair_arg, n_rows, thr, par_k,
                       kept_cnt, kept_mask, kept_off, cand_p, cand_q, grp_p, n_groups_d, scratch, sbytes, s)
-            n_groups = int(n_groups_d.item())
+            n_groups = dev.scalar(n_groups_d)
             _lib.call("kmls_count_candidates", bitmap, row_words, items_k, k, grp_p, n_groups,
                       kept_off, cand_q, n_cand, cand_cnt, s,
                       algo_bytes=(n_cand + n_groups * k) * row_words * 4)
@@ -416,7 +431,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
         scratch, sbytes = dev.scan_scratch(n_cand)
         out_off = dev.empty(n_cand + 1, torch.int64)
         _lib.call("kmls_emit_count", cand_cnt, n_cand, thr, out_off, scratch, sbytes, s)
-        n_next = int(out_off[n_cand].item())
+        n_next = dev.scalar(out_off[n_cand])
         stats["levels"].append({"k": k + 1, "candidates": n_cand, "groups": n_groups,
                                 "frequent": n_next})
         if n_next == 0:
@@ -585,8 +600,8 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     scratch, sbytes = dev.scan_scratch(n_x)
     rule_off = dev.empty(n_x + 1, torch.int64)
     _lib.call("kmls_exclusive_scan_i32", rule_cnt, n_x, rule_off, scratch, sbytes, s)
-    n_rules = int(rule_off[n_x].item())
-    if int(missing.item()) != 0:
+    n_rules = dev.scalar(rule_off[n_x])
+    if dev.scalar(missing) != 0:
         raise _lib.KmlsError("rule generation: a subset of a frequent itemset is missing from the "
                              "itemset table (table not downward closed)")
     if n_rules > max_rules:
