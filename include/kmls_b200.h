@@ -223,13 +223,18 @@ int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_words, const 
 int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
                           const int64_t* level_sizes, int32_t max_k, void* d_nodes,
                           kmls_stream_t stream);
-/* (antecedent, consequent) splits examined per k-itemset = 2^(k-1) - 1 (each yields up to
- * two rules); -1 if k is not supported (k > 15). */
+/* Slots per k-itemset in pass 1's output = 2^(k-1): slot 0 plus one per (antecedent,
+ * consequent) split (each split yields up to two rules); -1 if k is not supported (k > 15).
+ * Pass 1's output for n itemsets of level k, S = that number: two int32 planes, d_part[0 ..
+ * n*S) = count(A), d_part[n*S .. 2*n*S) = count(C); slot s >= 1 of an itemset is the split whose
+ * antecedent mask over the itemset's first k-1 members is the bit reversal (over k-1 bits) of
+ * s, C = the rest of the itemset (it always holds the last member); slot 0 = the itemset's own
+ * count in both planes. So d_part needs n * S * 8 bytes. */
 int64_t kmls_rules_parts_per_itemset(int32_t k);
 /* Pass 1 for the itemsets lvl_begin .. lvl_begin+lvl_count-1 of level k (ranks may split a
- * level): d_part[lvl_count * parts_per_itemset(k)] (8 bytes each) receives the subset counts
- * of every split, d_rule_cnt[lvl_count] the number of kept rules per itemset; *d_missing
- * counts failed subset lookups (0 for a downward-closed table; caller zeroes it). */
+ * level): d_part (layout above, n = lvl_count) receives the subset counts of every split,
+ * d_rule_cnt[lvl_count] the number of kept rules per itemset; *d_missing counts failed subset
+ * lookups (0 for a downward-closed table; caller zeroes it). */
 int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts, const int64_t* level_sizes,
                      int32_t max_k, int32_t k, int64_t lvl_begin, int64_t lvl_count,
                      const void* d_nodes, int64_t n_playlists_total, double min_confidence,

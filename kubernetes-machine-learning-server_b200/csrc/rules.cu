@@ -32,6 +32,7 @@ namespace kmls {
 constexpr int kMaxLevels = 32;
 constexpr int kMaxRuleK = 15;  // 2^(k-1) subset table per warp must fit in shared memory
 constexpr int kRuleIlp = 2;    // independent index probes in flight per lane
+constexpr int kGatherIlp = 2;  // blocks of 32 slots in flight per warp in the gather route of pass 1
 constexpr int kWriteIlp = 2;   // groups of 32 splits whose pass-1 pairs are loaded ahead in pass 2
 
 struct Arena {
@@ -170,7 +171,7 @@ constexpr int kRuleChunkMax = 64;   // consecutive itemsets handled by one warp 
 
 __global__ void __launch_bounds__(256, 4)
 k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* __restrict__ node,
-              double n_total, double min_conf, int chunk, int2* __restrict__ part,
+              double n_total, double min_conf, int chunk, int32_t* __restrict__ part,
               int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
   extern __shared__ int32_t smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -181,7 +182,8 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
   int32_t* tab_n = tab_first + n_sub;
   int32_t* tab_cnt = tab_n + n_sub;
   const int64_t lvl_first = a.id_off[k];   // global id of the level's first itemset
-  const int n_part = n_sub - 1;            // antecedent masks 1 .. n_sub-1
+  int32_t* pa = part;                      // planes of count(A) / count(C), see "Layout" below
+  int32_t* pc = part + lvl_count * n_sub;
   const int64_t n_chunks = (lvl_count + chunk - 1) / chunk;
   const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
   const int32_t* items_lvl = a.items + a.item_off[k] + lvl_begin * k;
@@ -257,7 +259,10 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
             k1 = conf_keep(fx, c_x, ca, thr_hi, thr_lo, n_total, min_conf);
             k2 = conf_keep(fx, c_x, cc, thr_hi, thr_lo, n_total, min_conf);
           }
-          part[sib * n_part + (am - 1)] = make_int2(ca, cc);
+          const int sl = (int)(__brev((unsigned)am) >> (33 - k));
+          pa[sib * n_sub + sl] = ca;
+          pc[sib * n_sub + sl] = cc;
+          if (am == 1) pa[sib * n_sub] = pc[sib * n_sub] = c_x;      // slot 0 = count(X)
         }
         const uint32_t b1 = __ballot_sync(0xffffffffu, k1), b2 = __ballot_sync(0xffffffffu, k2);
         if (active && am == 1) rule_cnt[sib] = __popc(b1 & gmask) + __popc(b2 & gmask);
@@ -292,7 +297,9 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
       }
       const int32_t last = __shfl_sync(0xffffffffu, my_item, k - 1);
       const float fx = (float)c_x;
-      int2* pj = part + j * n_part - 1;    // indexed by antecedent mask 1 .. n_sub-1
+      int32_t* pa_j = pa + j * n_sub;      // indexed by slot = bit-reversed antecedent mask
+      int32_t* pc_j = pc + j * n_sub;
+      if (lane == 0) pa_j[0] = pc_j[0] = c_x;
       int kept = 0;
       // kRuleIlp antecedent masks per lane and iteration: the candidate children of all of
       // them are loaded before any is compared
@@ -338,7 +345,9 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
               k1 = conf_keep(fx, c_x, ca, thr_hi, thr_lo, n_total, min_conf);
               k2 = conf_keep(fx, c_x, cc[u], thr_hi, thr_lo, n_total, min_conf);
             }
-            pj[am] = make_int2(ca, cc[u]);
+            const int sl = (int)(__brev((unsigned)am) >> (33 - k));
+            pa_j[sl] = ca;
+            pc_j[sl] = cc[u];
           }
           kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
         }
@@ -350,14 +359,25 @@ k_rules_count(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, const int4* 
 }
 
 // ---------------------------------------------------------------------------------------
+// Layout of pass 1's output ("part") for level k, n rows (itemsets), S = 2^(k-1) slots per row:
+// two int32 planes, planeA = part, planeC = part + n * S. Slot s >= 1 of row X stands for the
+// antecedent mask am = bitreverse_{k-1}(s) over X's prefix P: planeA = count(A), planeC =
+// count(C), A = members of P selected by am, C = X \ A. Slot 0 of both planes = count(X).
+// Bit-REVERSED slots make everything the next level needs contiguous (see k_rules_gather).
+//
 // K5 pass 1 without searching per split ("gather" route, used when one GPU holds the whole
 // previous level's output). Every subset count a k-itemset X = P + {x} needs was already
-// produced by level k-1:
+// produced by level k-1 (row stride S' = S / 2 there):
 //   count(A), A a subset of P: P is X's parent, a (k-1)-itemset with prefix P' and last member
-//     q. Its row holds, for every antecedent mask a' over P', (count(A'), count(P' \ A' + {q})):
-//     A without q is an A', A with q is a consequent.
+//     q. A without q is an antecedent of P (planeA of P's row, slot s >> 1), A with q is a
+//     consequent of P (planeC, slot S' - 1 - (s >> 1); slot 0 when A = P). s even / odd decides.
 //   count(C), C = R + {x}, R a proper subset of P: with p_i the first member of P not in R, C
-//     is a consequent of X_i = X \ {p_i}, which has the same last member x.
+//     is a consequent of X_i = X \ {p_i}, which has the same last member x. In slot terms:
+//     h = highest set bit of s, i = k - 2 - h, and the slot inside X_i's row is s - 2^h
+//     (slot 0, count(X_i), when A = {p_i}).
+// So a block of 32 consecutive slots reads two half-blocks of the parent's row and one block
+// of ONE X_i row, all contiguous, and writes two contiguous blocks. Level 2 reads level 1's
+// counts as its planeC (S' = 1).
 // What remains to be searched are the k-1 rows X_i per itemset (k_rules_subsets, one thread
 // per (itemset, i)); X_i = child x of P \ {p_i}, and P \ {p_i} is what the parent's own
 // k_rules_subsets output names (or the parent's parent for i = k-2).
@@ -394,110 +414,97 @@ k_rules_subsets(Arena a, int k, const int4* __restrict__ node, const int32_t* __
   }
 }
 
-// (count(A), count(C)) of the split `am` of an itemset: see the comment above.
-//   row_p / c_p: the parent's index in level k-1 and its count; row_i: index in level k-1 of
-//   X \ {p_i}, i = first member of A; npp = entries per row of part_prev = 2^(k-2) - 1.
-__device__ __forceinline__ int2 split_counts(const Arena& a, int k, int am, int32_t row_p, int32_t c_p,
-                                             int32_t row_i, int i, int32_t last,
-                                             const int2* __restrict__ part_prev) {
-  const int n_sub = 1 << (k - 1), top = n_sub >> 1, npp = top - 1;
-  int2 r;
-  if (am == n_sub - 1) {
-    r.x = c_p;                                             // A = P
-  } else if (!(am & top)) {
-    r.x = row_p < 0 ? -1 : __ldg(&part_prev[(int64_t)row_p * npp + (am - 1)].x);
-  } else {
-    const int ap = (top - 1) ^ (am ^ top);                 // P' \ (A \ {q})
-    r.x = row_p < 0 ? -1 : __ldg(&part_prev[(int64_t)row_p * npp + (ap - 1)].y);
-  }
-  const int rest = (n_sub - 1) ^ am;
-  if (rest == 0) {
-    r.y = __ldg(a.counts + last);                          // C = {x}
-  } else if (row_i < 0) {
-    r.y = -1;
-  } else {
-    const int ap = (am >> (i + 1)) << i;                   // A \ {p_i} as a mask over P \ {p_i}
-    if (ap == 0) r.y = __ldg(a.counts + a.id_off[k - 1] + row_i);   // C = X_i itself
-    else r.y = __ldg(&part_prev[(int64_t)row_i * npp + (ap - 1)].y);
-  }
-  return r;
-}
+// antecedent mask of slot s (and back): bit reversal over the k-1 prefix positions
+__device__ __forceinline__ int slot_mask(int s, int k) { return (int)(__brev((unsigned)s) >> (33 - k)); }
 
 __global__ void __launch_bounds__(256)
-k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int2* __restrict__ part_prev,
-               double n_total, double min_conf, int2* __restrict__ part,
+k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* __restrict__ part_prev,
+               double n_total, double min_conf, int32_t* __restrict__ part,
                int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
   const int lane = threadIdx.x & 31;
-  const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
-  const int64_t n_k = a.id_off[k + 1] - a.id_off[k];
+  const int n_sub = 1 << (k - 1), top = n_sub >> 1;
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k], n_p = a.id_off[k] - a.id_off[k - 1];
   const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
-  const int32_t* items_k = a.items + a.item_off[k];
   const int32_t* counts_k = a.counts + a.id_off[k];
   const int32_t* par_k = a.par + (a.id_off[k] - a.id_off[2]);
-  const int32_t* counts_p = a.counts + a.id_off[k - 1];
+  const int32_t* pa_prev = part_prev;
+  const int32_t* pc_prev = k == 2 ? a.counts : part_prev + n_p * top;
+  int32_t* pa = part;
+  int32_t* pc = part + n_k * n_sub;
   if (n_sub <= 16) {
-    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, antecedent mask)
-    const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
+    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, slot)
+    const int per_warp = 32 / n_sub, g = lane / n_sub, s = lane % n_sub;
     const uint32_t gmask = ((1u << n_sub) - 1u) << (g * n_sub);
+    const int h = 31 - __clz(s | 1), i = k - 2 - h;
     const int64_t n_groups = (n_k + per_warp - 1) / per_warp;
     for (int64_t w = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); w < n_groups;
          w += (int64_t)gridDim.x * 8) {
       const int64_t j = w * per_warp + g;
-      const bool active = j < n_k && am >= 1;
+      const bool active = j < n_k;
       bool k1 = false, k2 = false;
       if (active) {
-        const int32_t last = __ldg(items_k + j * k + (k - 1));
         const int32_t c_x = __ldg(counts_k + j);
-        const int32_t row_p = __ldg(par_k + j);
-        const int i = __ffs(am) - 1;
-        const int32_t row_i = __ldg(sub + j * (k - 1) + i);
-        const int2 cc = split_counts(a, k, am, row_p, __ldg(counts_p + row_p), row_i, i, last, part_prev);
-        if (cc.x < 0 || cc.y < 0) {
-          atomicAdd(missing, 1);
-        } else {
-          const float fx = (float)c_x;
-          k1 = conf_keep(fx, c_x, cc.x, thr_hi, thr_lo, n_total, min_conf);
-          k2 = conf_keep(fx, c_x, cc.y, thr_hi, thr_lo, n_total, min_conf);
+        int32_t ca = c_x, cc = c_x;
+        if (s >= 1) {
+          const int64_t row_p = __ldg(par_k + j);
+          const int64_t row_i = __ldg(sub + j * (k - 1) + i);
+          ca = (s & 1) ? __ldg(pc_prev + row_p * top + (top - 1 - (s >> 1))) : __ldg(pa_prev + row_p * top + (s >> 1));
+          cc = row_i < 0 ? -1 : __ldg(pc_prev + row_i * top + (s - (1 << h)));
+          if (ca < 0 || cc < 0) {
+            atomicAdd(missing, 1);
+          } else {
+            const float fx = (float)c_x;
+            k1 = conf_keep(fx, c_x, ca, thr_hi, thr_lo, n_total, min_conf);
+            k2 = conf_keep(fx, c_x, cc, thr_hi, thr_lo, n_total, min_conf);
+          }
         }
-        part[j * n_part + (am - 1)] = cc;
+        pa[j * n_sub + s] = ca;
+        pc[j * n_sub + s] = cc;
       }
       const uint32_t b1 = __ballot_sync(0xffffffffu, k1), b2 = __ballot_sync(0xffffffffu, k2);
-      if (active && am == 1) rule_cnt[j] = __popc(b1 & gmask) + __popc(b2 & gmask);
+      if (active && s == 0) rule_cnt[j] = __popc(b1 & gmask) + __popc(b2 & gmask);
     }
     return;
   }
-  // long itemsets: one warp per itemset, lane = antecedent mask (blocks of 32)
+  // long itemsets: one warp per itemset, lane = slot (blocks of 32)
   for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < n_k; j += (int64_t)gridDim.x * 8) {
-    const int32_t last = __ldg(items_k + j * k + (k - 1));
     const int32_t c_x = __ldg(counts_k + j);
-    const int32_t row_p = __ldg(par_k + j);
-    const int32_t c_p = __ldg(counts_p + row_p);
+    const int64_t row_p = __ldg(par_k + j);
     const int32_t my_sub = lane < k - 1 ? __ldg(sub + j * (k - 1) + lane) : -1;
     const float fx = (float)c_x;
-    int2* pj = part + j * n_part - 1;        // indexed by antecedent mask 1 .. n_sub-1
+    const int32_t* pa_p = pa_prev + row_p * top;
+    const int32_t* pc_p = pc_prev + row_p * top;
+    int32_t* pa_j = pa + j * n_sub;
+    int32_t* pc_j = pc + j * n_sub;
     int kept = 0;
-    for (int a0 = 1; a0 < n_sub; a0 += 32 * kRuleIlp) {
-      int2 cc[kRuleIlp];
+    for (int s0 = 0; s0 < n_sub; s0 += 32 * kGatherIlp) {
+      int32_t ca[kGatherIlp], cc[kGatherIlp];
 #pragma unroll
-      for (int u = 0; u < kRuleIlp; ++u) {
-        const int am = a0 + u * 32 + lane;
-        const int i = __ffs(am < n_sub ? am : 1) - 1;
-        const int32_t row_i = __shfl_sync(0xffffffffu, my_sub, i);
-        cc[u] = make_int2(0, 0);
-        if (am < n_sub) cc[u] = split_counts(a, k, am, row_p, c_p, row_i, i, last, part_prev);
+      for (int u = 0; u < kGatherIlp; ++u) {
+        const int s = s0 + u * 32 + lane;
+        const int h = 31 - __clz(s | 1);
+        const int64_t row_i = __shfl_sync(0xffffffffu, my_sub, (k - 2 - h) & 31);
+        ca[u] = cc[u] = c_x;                               // slot 0
+        if (s >= 1 && s < n_sub) {
+          ca[u] = (s & 1) ? __ldg(pc_p + (top - 1 - (s >> 1))) : __ldg(pa_p + (s >> 1));
+          cc[u] = row_i < 0 ? -1 : __ldg(pc_prev + row_i * top + (s - (1 << h)));
+        }
       }
 #pragma unroll
-      for (int u = 0; u < kRuleIlp; ++u) {
-        const int am = a0 + u * 32 + lane;
+      for (int u = 0; u < kGatherIlp; ++u) {
+        const int s = s0 + u * 32 + lane;
         bool k1 = false, k2 = false;
-        if (am < n_sub) {
-          if (cc[u].x < 0 || cc[u].y < 0) {
-            atomicAdd(missing, 1);
-          } else {
-            k1 = conf_keep(fx, c_x, cc[u].x, thr_hi, thr_lo, n_total, min_conf);
-            k2 = conf_keep(fx, c_x, cc[u].y, thr_hi, thr_lo, n_total, min_conf);
+        if (s < n_sub) {
+          if (s >= 1) {
+            if (ca[u] < 0 || cc[u] < 0) {
+              atomicAdd(missing, 1);
+            } else {
+              k1 = conf_keep(fx, c_x, ca[u], thr_hi, thr_lo, n_total, min_conf);
+              k2 = conf_keep(fx, c_x, cc[u], thr_hi, thr_lo, n_total, min_conf);
+            }
           }
-          pj[am] = cc[u];
+          pa_j[s] = ca[u];
+          pc_j[s] = cc[u];
         }
         kept += __popc(__ballot_sync(0xffffffffu, k1)) + __popc(__ballot_sync(0xffffffffu, k2));
       }
@@ -506,25 +513,28 @@ k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int2* __re
   }
 }
 
-// K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) pairs of pass 1,
+// K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) planes of pass 1,
 // recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
-// rank). Order inside an itemset: per block of 32 antecedent masks (the whole itemset for
-// k <= 6), first the kept rules A -> C in mask order, then the kept rules C -> A in mask
-// order - so that every store instruction of the warp writes one contiguous run.
+// rank). Order inside an itemset: per block of 32 slots (the whole itemset for k <= 6),
+// first the kept rules A -> C in slot order, then the kept rules C -> A in slot order - so
+// that every store instruction of the warp writes one contiguous run.
 __global__ void __launch_bounds__(256)
 k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
-              const int2* __restrict__ part, const int64_t* __restrict__ rule_off,
+              const int32_t* __restrict__ part, const int64_t* __restrict__ rule_off,
               int2* __restrict__ out_rule, double* __restrict__ out_confidence,
               double* __restrict__ out_lift) {
   const int lane = threadIdx.x & 31;
-  const int n_sub = 1 << (k - 1), n_part = n_sub - 1;
+  const int n_sub = 1 << (k - 1);
   const uint32_t full = (1u << k) - 1u;
   const int64_t lvl_first = a.id_off[k];
   const double rcp_n = __drcp_rn(n_total);
+  const int32_t* pa = part;
+  const int32_t* pc = part + lvl_count * n_sub;
   if (n_sub <= 16) {
-    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, antecedent
-    // mask), so that the lanes are not left idle by the few splits a small itemset has
-    const int per_warp = 32 / n_sub, g = lane / n_sub, am = lane % n_sub;
+    // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, slot), so
+    // that the lanes are not left idle by the few splits a small itemset has
+    const int per_warp = 32 / n_sub, g = lane / n_sub, s = lane % n_sub;
+    const int am = slot_mask(s, k);
     const uint32_t gmask = ((1u << n_sub) - 1u) << (g * n_sub);
     const uint32_t below = gmask & ((1u << lane) - 1u);
     const int64_t n_groups = (lvl_count + per_warp - 1) / per_warp;
@@ -534,11 +544,11 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
       RuleVals r;
       r.k1 = r.k2 = false;
       int64_t gid = 0;
-      if (j < lvl_count && am >= 1) {
+      if (j < lvl_count && s >= 1) {
         gid = lvl_first + lvl_begin + j;
-        const int2 cc = __ldg(part + j * n_part + (am - 1));
+        const int32_t ca = __ldg(pa + j * n_sub + s), cc = __ldg(pc + j * n_sub + s);
         const double s_x = div_by_rcp((double)__ldg(a.counts + gid), n_total, rcp_n);
-        if (cc.x >= 0 && cc.y >= 0) r = rule_values(s_x, cc.x, cc.y, n_total, rcp_n, min_conf);
+        if (ca >= 0 && cc >= 0) r = rule_values(s_x, ca, cc, n_total, rcp_n, min_conf);
       }
       const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
       if (r.k1 || r.k2) {
@@ -563,30 +573,40 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
   for (int64_t j = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); j < lvl_count;
        j += (int64_t)gridDim.x * 8) {
     const int64_t gid = lvl_first + lvl_begin + j;
-    const int2* pj = part + j * n_part - 1;     // indexed by antecedent mask 1 .. n_sub-1
-    // the loads of kWriteIlp groups of 32 splits are issued before the first is consumed
-    int2 cc[kWriteIlp];
+    const int32_t* pa_j = pa + j * n_sub;
+    const int32_t* pc_j = pc + j * n_sub;
+    // the loads of kWriteIlp blocks of 32 slots are issued before the first is consumed
+    int32_t ca[kWriteIlp], cc[kWriteIlp];
 #pragma unroll
     for (int u = 0; u < kWriteIlp; ++u) {
-      const int am = 1 + u * 32 + lane;
-      cc[u] = am < n_sub ? __ldg(pj + am) : make_int2(-1, -1);
+      const int s = u * 32 + lane;
+      ca[u] = cc[u] = -1;
+      if (s >= 1 && s < n_sub) {
+        ca[u] = __ldg(pa_j + s);
+        cc[u] = __ldg(pc_j + s);
+      }
     }
     const double s_x = div_by_rcp((double)__ldg(a.counts + gid), n_total, rcp_n);
     int64_t pos = rule_off[j];
-    for (int a0 = 1; a0 < n_sub; a0 += 32 * kWriteIlp) {
-      int2 nx[kWriteIlp];
+    for (int s0 = 0; s0 < n_sub; s0 += 32 * kWriteIlp) {
+      int32_t na[kWriteIlp], nc[kWriteIlp];
 #pragma unroll
       for (int u = 0; u < kWriteIlp; ++u) {     // next iteration's loads
-        const int am = a0 + (kWriteIlp + u) * 32 + lane;
-        nx[u] = am < n_sub ? __ldg(pj + am) : make_int2(-1, -1);
+        const int s = s0 + (kWriteIlp + u) * 32 + lane;
+        na[u] = nc[u] = -1;
+        if (s < n_sub) {
+          na[u] = __ldg(pa_j + s);
+          nc[u] = __ldg(pc_j + s);
+        }
       }
 #pragma unroll
       for (int u = 0; u < kWriteIlp; ++u) {
-        const int am = a0 + u * 32 + lane;
-        if (a0 + u * 32 < n_sub) {              // warp-uniform
+        const int s = s0 + u * 32 + lane;
+        if (s0 + u * 32 < n_sub) {              // warp-uniform
+          const int am = slot_mask(s, k);
           RuleVals r;
           r.k1 = r.k2 = false;
-          if (cc[u].x >= 0 && cc[u].y >= 0) r = rule_values(s_x, cc[u].x, cc[u].y, n_total, rcp_n, min_conf);
+          if (ca[u] >= 0 && cc[u] >= 0) r = rule_values(s_x, ca[u], cc[u], n_total, rcp_n, min_conf);
           const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
           if (r.k1) {
             const int64_t o = pos + __popc(m1 & below);
@@ -604,7 +624,10 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
         }
       }
 #pragma unroll
-      for (int u = 0; u < kWriteIlp; ++u) cc[u] = nx[u];
+      for (int u = 0; u < kWriteIlp; ++u) {
+        ca[u] = na[u];
+        cc[u] = nc[u];
+      }
     }
   }
 }
@@ -714,7 +737,7 @@ extern "C" int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_co
 }
 
 extern "C" int64_t kmls_rules_parts_per_itemset(int32_t k) {
-  return k >= 2 && k <= kMaxRuleK ? ((int64_t)1 << (k - 1)) - 1 : -1;
+  return k >= 2 && k <= kMaxRuleK ? ((int64_t)1 << (k - 1)) : -1;
 }
 
 extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
@@ -744,7 +767,7 @@ extern "C" int kmls_rules_count(const int32_t* d_items, const int32_t* d_counts,
   int grid = (int)std::min<int64_t>((n_chunks + warps - 1) / warps, (int64_t)num_sms() * 32);
   k_rules_count<<<grid, warps * 32, smem, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (const int4*)d_nodes, (double)n_playlists_total, min_confidence,
-      chunk, (int2*)d_part, d_rule_cnt, d_missing);
+      chunk, (int32_t*)d_part, d_rule_cnt, d_missing);
   KMLS_LAUNCHED("k_rules_count");
   return 0;
 }
@@ -787,7 +810,7 @@ extern "C" int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_
   const int64_t warps = (n_k + per_warp - 1) / per_warp;
   int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_gather<<<grid, 256, 0, (cudaStream_t)stream>>>(
-      a, k, d_sub, (const int2*)d_part_prev, (double)n_playlists_total, min_confidence, (int2*)d_part,
+      a, k, d_sub, (const int32_t*)d_part_prev, (double)n_playlists_total, min_confidence, (int32_t*)d_part,
       d_rule_cnt, d_missing);
   KMLS_LAUNCHED("k_rules_gather");
   return 0;
@@ -809,7 +832,7 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
                    ((uintptr_t)d_out_rule & 7) == 0, "kmls_rules_write: null or misaligned pointer");
   int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
-      a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int2*)d_part,
+      a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int32_t*)d_part,
       d_rule_off, (int2*)d_out_rule, d_out_confidence, d_out_lift);
   KMLS_LAUNCHED("k_rules_write");
   return 0;

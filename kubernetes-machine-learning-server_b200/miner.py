@@ -556,7 +556,7 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     for k in range(2, max_k + 1):
         lo, hi = max(x_begin, lvl_start), min(x_end, lvl_start + int(sizes[k]))
         if hi > lo:
-            splits += (hi - lo) * ((1 << (k - 1)) - 1)
+            splits += (hi - lo) * (1 << (k - 1))       # slots of pass 1's output, 8 bytes each
         lvl_start += int(sizes[k])
     free_bytes = torch.cuda.mem_get_info(device)[0] + torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
     if splits * 8 > free_bytes:
