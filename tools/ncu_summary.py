@@ -64,6 +64,7 @@ def main():
     ap.add_argument("--launches")
     ap.add_argument("--full", nargs="*", default=[])
     ap.add_argument("--note", default="")
+    ap.add_argument("--only", default="", help="comma-separated launch indices to keep from each --full report")
     a = ap.parse_args()
     print(f"# {a.title}\n")
     if a.command:
@@ -77,7 +78,10 @@ def main():
             print(f"| {100 * ms / tot:.2f}% | {ms:.3f} | {c} | `{k.split('(')[0][:90]}` |")
         print()
     for path in a.full:
-        for d in full(path):
+        keep = {int(x) for x in a.only.split(",")} if a.only else None
+        for idx, d in enumerate(full(path)):
+            if keep is not None and idx not in keep:
+                continue
             print(f"## `ncu --set full`: `{d['Kernel Name'].split('(')[0]}` ({path.split('/')[-1]})\n")
             print("| metric | value |\n|---|---|")
             for m in METRICS:
