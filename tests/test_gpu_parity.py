@@ -191,7 +191,10 @@ def test_project_rows_and_count_pairs():
     roww1 = torch.full((n_rows,), W, dtype=torch.int32, device=dev())
     cnt1 = torch.from_numpy(dense.sum(1).astype(np.int32)).to(dev())
     # new "itemsets": (p, q) pairs sorted by p; p = 20 appears once only (gets no row)
-    pq = [(p, q) for p in range(0, 12) for q in range(p + 1, min(p + 4, n_rows))] + [(20, 30)]
+    # (runs of 3 with the same p, cut by the kernel's chunks of 8; p = 13: a run of 19, longer
+    # than a chunk)
+    pq = [(p, q) for p in range(0, 12) for q in range(p + 1, min(p + 4, n_rows))] + \
+        [(13, q) for q in range(14, 33)] + [(20, 30)]
     par_p = torch.tensor([a for a, _ in pq], dtype=torch.int32, device=dev())
     par_q = torch.tensor([b for _, b in pq], dtype=torch.int32, device=dev())
     n = len(pq)
