@@ -579,7 +579,7 @@ def main():
                     help="after the run, mine the FULL workload with the CPU oracle (minutes) and compare level "
                          "sizes, the itemset checksum and the number of rules")
     ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
-    ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc"])
+    ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc", "csr"])
     ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])
     args = ap.parse_args()
     global MIN_SUPPORT_OVERRIDE

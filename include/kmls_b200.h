@@ -69,6 +69,18 @@ int kmls_gather_rows(const uint32_t* d_src, const int32_t* d_src_row, int32_t n_
 int kmls_pair_counts(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
                      int32_t* d_pair, kmls_stream_t stream);
 
+/* The same counts from the playlists themselves (sparse form): every playlist adds 1 to the
+ * counter of each pair of distinct kept tracks it holds (a repeated track counts once) and to
+ * the diagonal. Cost = sum over playlists of m(m+1)/2 updates, m = kept tracks of the playlist,
+ * instead of n_rows^2 * n_playlists / 2 multiply-adds: the cheaper route when the one-hot
+ * matrix is sparse. d_row_of_item[track id] = row or -1 (track not kept). Writes the upper
+ * triangle and the diagonal of d_pair (zeroed here). *d_overflow (zeroed here) counts the
+ * playlists with more than 1024 distinct kept tracks, which are SKIPPED: if it is not 0 the
+ * result is incomplete and the caller must use one of the dense kernels. n_rows <= 16384. */
+int kmls_pair_counts_csr(const int64_t* d_offsets, const int32_t* d_items, int64_t n_playlists,
+                         const int32_t* d_row_of_item, int32_t n_rows, int32_t* d_pair,
+                         int32_t* d_overflow, kmls_stream_t stream);
+
 /* The same contraction on the tensor cores (tcgen05.mma kind::i8, int32 accumulators in
  * TMEM, bit slices fetched by TMA and expanded to int8 inside the SM). Only entries with
  * j >= i (upper triangle, diagonal included) are guaranteed to be written. d_scratch:

@@ -50,6 +50,7 @@ SIGNATURES = {
     "kmls_rules_parts_per_itemset": (_I64, [_I32]),
     "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _I64, _I64, _P, _I64, _F64, _P, _P,
                                         _P, _P]),
+    "kmls_pair_counts_csr": (ctypes.c_int, [_P, _P, _I64, _P, _I32, _P, _P, _P]),
     "kmls_words_to_host": (ctypes.c_int, [_P, _I32, _P, _P]),
     "kmls_rules_subsets": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P, _P, _P]),
     "kmls_rules_count_gather": (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _I64, _F64, _P, _P, _P, _P]),

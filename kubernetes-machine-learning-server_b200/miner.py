@@ -211,14 +211,32 @@ def prepare(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppor
         same = counts1_local is counts1
         bitmap, counts1, cand = bitmap2, counts1[src.long()].contiguous(), cand[src.long()]
         counts1_local = counts1 if same else counts1_local[src.long()].contiguous()
+        row_of_item.fill_(-1)
+        row_of_item[cand] = torch.arange(n_rows, dtype=torch.int32, device=dev.device)
     row_items = cand.to(torch.int32)
     pair = pair_local = None
     if with_pairs and n_rows >= 2:
         pair = dev.empty(n_rows * n_rows, torch.int32)
         if pair_impl == "auto":
-            # tensor cores once there are enough 128x256 tiles and playlists to feed them
+            # tensor cores once there are enough 128x256 tiles and playlists to feed them ...
             pair_impl = "i8" if (n_rows >= 256 and row_words >= 512) else "popc"
-        if pair_impl == "popc":
+            if pair_impl == "i8" and n_rows <= 16384 and n_local > 0:
+                # ... unless the one-hot matrix is so sparse that counting the pairs of each
+                # playlist is cheaper: ~0.65 m^2 counter updates per playlist (m = mean number
+                # of kept tracks; the factor covers the spread of playlist lengths) at about
+                # 2e11 updates/s, against F(F+1) N int8 operations at about 2.2e15/s
+                m_mean = dev.scalar(counts1_local.sum()) / n_local
+                if 0.65 * m_mean * m_mean * n_local / 2.0e11 < n_rows * (n_rows + 1) * n_local / 2.2e15:
+                    pair_impl = "csr"
+        if pair_impl == "csr":
+            overflow = torch.zeros(1, dtype=torch.int32, device=dev.device)
+            _lib.call("kmls_pair_counts_csr", offsets, items, n_local, row_of_item, n_rows, pair,
+                      overflow, s)
+            if dev.scalar(overflow) != 0:
+                pair_impl = "i8" if (n_rows >= 256 and row_words >= 512) else "popc"   # a very long playlist
+        if pair_impl == "csr":
+            pass
+        elif pair_impl == "popc":
             _lib.call("kmls_pair_counts", bitmap, n_rows, row_words, pair, s)
         elif pair_impl == "i8":
             gbytes = int(_lib.value("kmls_pair_gemm_scratch_bytes", n_rows, row_words))

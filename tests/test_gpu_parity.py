@@ -158,6 +158,62 @@ def test_pair_counts_tensor_core_matches_cuda_core(rows, n, variant, monkeypatch
     assert torch.equal(got.view(rows, rows)[iu], ref.view(rows, rows)[iu])
 
 
+@pytest.mark.parametrize("n,t,kept,max_len,dup", [(1, 5, 5, 4, False), (300, 50, 37, 30, True), (5000, 900, 700, 80, True),
+                                                  (20000, 3000, 2500, 120, False)])
+def test_pair_counts_from_playlists_match_bitmap_counts(n, t, kept, max_len, dup):
+    """Sparse route (one counter update per pair of a playlist) vs the AND+popc kernel on the
+    bitmap of the same playlists: equal on the upper triangle and the diagonal; repeated
+    tracks count once; tracks without a row are ignored."""
+    rng = np.random.default_rng(n + t)
+    lens = rng.integers(0, max_len + 1, n)
+    rows_ = [rng.choice(t, min(l, t), replace=False) for l in lens]
+    if dup:
+        rows_ = [np.concatenate([r, r[:3], r[:1]]) for r in rows_]
+    off = np.zeros(n + 1, np.int64)
+    np.cumsum([len(r) for r in rows_], out=off[1:])
+    items = (np.concatenate(rows_) if off[-1] else np.zeros(0)).astype(np.int32)
+    keep = rng.permutation(t)[:kept]
+    row_of = np.full(t, -1, np.int32)
+    row_of[keep] = np.arange(kept, dtype=np.int32)
+    d_off, d_items = torch.from_numpy(off).to(dev()), torch.from_numpy(items).to(dev())
+    d_row_of = torch.from_numpy(row_of).to(dev())
+    W = int(_lib.value("kmls_bitmap_row_words", n))
+    bm = torch.empty(kept * W, dtype=torch.int32, device=dev())
+    _lib.call("kmls_encode_bitmap", d_off, d_items, n, d_row_of, t, kept, bm, W, stream())
+    ref = torch.empty(kept * kept, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts", bm, kept, W, ref, stream())
+    got = torch.full((kept * kept,), -3, dtype=torch.int32, device=dev())
+    ov = torch.full((1,), 7, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts_csr", d_off, d_items, n, d_row_of, kept, got, ov, stream())
+    assert int(ov.item()) == 0
+    iu = torch.triu(torch.ones(kept, kept, dtype=torch.bool, device=dev()))
+    assert torch.equal(got.view(kept, kept)[iu], ref.view(kept, kept)[iu])
+
+
+def test_pair_counts_from_playlists_flag_overlong_playlists():
+    # one playlist with 1500 distinct kept tracks (> 1024): flagged and skipped, the others counted
+    t = 2000
+    lists = [np.arange(1500), np.array([1, 2, 3, 2]), np.array([3, 1])]
+    off = np.zeros(4, np.int64)
+    np.cumsum([len(r) for r in lists], out=off[1:])
+    items = np.concatenate(lists).astype(np.int32)
+    d_row_of = torch.arange(t, dtype=torch.int32, device=dev())
+    got = torch.empty(t * t, dtype=torch.int32, device=dev())
+    ov = torch.zeros(1, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts_csr", torch.from_numpy(off).to(dev()), torch.from_numpy(items).to(dev()), 3,
+              d_row_of, t, got, ov, stream())
+    assert int(ov.item()) == 1
+    g = got.view(t, t)
+    assert int(g[1, 3]) == 2 and int(g[1, 2]) == 1 and int(g[2, 3]) == 1 and int(g[3, 3]) == 2 and int(g.sum()) == 9
+    # and the miner falls back to a dense kernel for such an input
+    off2, items2 = synth.zipf_playlists(3000, 1400, mean_draws=20, alpha=0.6, seed=9)
+    off2 = np.concatenate([off2, [off2[-1] + 1300]])
+    items2 = np.concatenate([items2, np.arange(1300, dtype=np.int32)])
+    want = oracle_dict(off2, items2, 1400, 0.004)
+    res, _ = kmls_b200.mine_ids(off2, items2, 1400, 0.004, pair_impl="csr")
+    assert res.as_dict() == want
+
+
 def test_exclusive_scan():
     rng = np.random.default_rng(2)
     for n in [0, 1, 31, 1025, 3_000_001]:
@@ -231,13 +287,15 @@ def test_project_rows_and_count_pairs():
 
 @pytest.mark.parametrize("count_impl,prune,first,keep", [
     ("projected", True, "gather", None), ("projected", False, "gather", 0), ("projected", False, "pext", 8),
+    ("projected-csr", False, "gather", None), ("projected-i8", False, "gather", None),
     ("projected", False, "gather", 100000), ("fullwidth", True, "gather", None),
     ("fullwidth", False, "gather", None)])
 def test_counting_variants_agree(count_impl, prune, first, keep):
     off, items = synth.zipf_playlists(9000, 700, mean_draws=30, alpha=0.9, seed=31)
     want = oracle_dict(off, items, 700, 0.012)
+    count_impl, _, pair_impl = count_impl.partition("-")
     res, _ = kmls_b200.mine_ids(off, items, 700, 0.012, count_impl=count_impl, prune=prune,
-                                first_projection=first, keep_words=keep)
+                                first_projection=first, keep_words=keep, pair_impl=pair_impl or "auto")
     assert res.as_dict() == want
     assert len(res.levels) >= 5
 
