@@ -186,6 +186,9 @@ __global__ void k_supports(const int32_t* __restrict__ counts, int64_t n, double
 constexpr int kCsrMaxLen = 1024;     // distinct kept tracks of one playlist
 constexpr int kCsrMaxRows = 16384;   // rows the per-warp bit set covers
 
+constexpr int kCsrHot = 64;          // the kCsrHot most frequent rows' pairs are counted in shared memory
+
+template <bool HOT>
 __global__ void __launch_bounds__(256)
 k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict__ items, int64_t n,
                   const int32_t* __restrict__ row_of_item, int32_t n_rows, int32_t* __restrict__ pair,
@@ -197,6 +200,15 @@ k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict
   int32_t* rows = reinterpret_cast<int32_t*>(csr_smem + (size_t)8 * seen_words) + (size_t)warp * kCsrMaxLen;
   for (int i = lane; i < seen_words; i += 32) seen[i] = 0u;
   __syncwarp();
+  // Rows are in ascending-support order, so the last kCsrHot rows are the most frequent
+  // tracks; under a Zipf law their pairs take a large share of all updates and would
+  // serialise on a few L2 atomic units. They are counted per CTA here and flushed once.
+  __shared__ int32_t hot[HOT ? kCsrHot * kCsrHot : 1];
+  const int hot0 = n_rows - kCsrHot;        // first hot row (HOT only when n_rows >= kCsrHot)
+  if (HOT) {
+    for (int i = threadIdx.x; i < kCsrHot * kCsrHot; i += blockDim.x) hot[i] = 0;
+    __syncthreads();
+  }
   const uint32_t below = (1u << lane) - 1u;
   for (int64_t p = (int64_t)blockIdx.x * 8 + warp; p < n; p += (int64_t)gridDim.x * 8) {
     const int64_t b = __ldg(offsets + p), e = __ldg(offsets + p + 1);
@@ -243,11 +255,19 @@ k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict
     while (i < m - 1) {
       const int32_t ra = rows[i], rb = rows[i + 1 + c];
       const int64_t lo = min(ra, rb), hi = max(ra, rb);
-      atomicAdd(pair + lo * n_rows + hi, 1);
+      if (HOT && lo >= hot0) atomicAdd(hot + (lo - hot0) * kCsrHot + (hi - hot0), 1);
+      else atomicAdd(pair + lo * n_rows + hi, 1);
       c += 32;
       while (i < m - 1 && c >= m - 1 - i) { c -= m - 1 - i; ++i; }
     }
     __syncwarp();
+  }
+  if (HOT) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < kCsrHot * kCsrHot; i += blockDim.x) {
+      const int v = hot[i];
+      if (v) atomicAdd(pair + (int64_t)(hot0 + i / kCsrHot) * n_rows + (hot0 + i % kCsrHot), v);
+    }
   }
 }
 
@@ -294,10 +314,12 @@ extern "C" int kmls_pair_counts_csr(const int64_t* d_offsets, const int32_t* d_i
   if (n_playlists == 0) return 0;
   KMLS_REQUIRE(d_offsets && d_items && d_row_of_item, "kmls_pair_counts_csr: null pointer");
   const size_t smem = sizeof(uint32_t) * 8 * (size_t)((n_rows + 31) / 32) + sizeof(int32_t) * 8 * kCsrMaxLen;
-  KMLS_CUDA(cudaFuncSetAttribute(k_pair_counts_csr, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-  int grid = (int)std::min<int64_t>((n_playlists + 7) / 8, (int64_t)num_sms() * 16);
-  k_pair_counts_csr<<<grid, 256, smem, s>>>(d_offsets, d_items, n_playlists, d_row_of_item, n_rows, d_pair,
-                                            d_overflow);
+  static const bool no_hot = [] { const char* e = getenv("KMLS_PAIR_CSR_HOT"); return e && e[0] == '0'; }();
+  const bool use_hot = !no_hot && n_rows >= kCsrHot;
+  auto kern = use_hot ? k_pair_counts_csr<true> : k_pair_counts_csr<false>;
+  KMLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+  int grid = (int)std::min<int64_t>((n_playlists + 7) / 8, (int64_t)num_sms() * (use_hot ? 4 : 16));
+  kern<<<grid, 256, smem, s>>>(d_offsets, d_items, n_playlists, d_row_of_item, n_rows, d_pair, d_overflow);
   KMLS_LAUNCHED("k_pair_counts_csr");
   return 0;
 }
