@@ -269,15 +269,17 @@ int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_counts, con
                             const int32_t* d_sub, const void* d_part_prev,
                             int64_t n_playlists_total, double min_confidence, void* d_part,
                             int32_t* d_rule_cnt, int32_t* d_missing, kmls_stream_t stream);
-/* Pass 2: d_rule_off[lvl_count] = first output slot of each itemset (exclusive scan of the
- * kept counts over everything this rank emits). Rule r: d_out_rule[2r] = itemset (global id),
- * d_out_rule[2r+1] = antecedent mask (bit t = t-th member; the consequent is the rest),
- * d_out_confidence[r], d_out_lift[r]. */
+/* Pass 2: d_rule_off[lvl_count + 1] = first output slot of each itemset (exclusive scan of the
+ * kept counts over everything this rank emits; the entry after the last itemset is read too).
+ * Rule r: d_out_rule[2r] = itemset (global id), d_out_rule[2r+1] = antecedent mask (bit t =
+ * t-th member; the consequent is the rest), d_out_confidence[r], d_out_lift[r].
+ * *d_mismatch (NOT zeroed here) is incremented for every itemset for which this pass keeps a
+ * different number of rules than pass 1 sized: must stay 0, anything else is an error. */
 int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
                      int32_t k, int64_t lvl_begin, int64_t lvl_count, int64_t n_playlists_total,
                      double min_confidence, const void* d_part, const int64_t* d_rule_off,
                      int32_t* d_out_rule, double* d_out_confidence, double* d_out_lift,
-                     kmls_stream_t stream);
+                     int32_t* d_mismatch, kmls_stream_t stream);
 /* The support column of the rule table, on demand: d_out[r] = count of rule r's itemset / N
  * (d_counts = the arena's counts). Not written by pass 2: it would be a quarter of its bytes
  * and is one gather away. */

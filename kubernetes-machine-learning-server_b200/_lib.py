@@ -54,7 +54,7 @@ SIGNATURES = {
     "kmls_words_to_host": (ctypes.c_int, [_P, _I32, _P, _P]),
     "kmls_rules_subsets": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P, _P, _P]),
     "kmls_rules_count_gather": (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _I64, _F64, _P, _P, _P, _P]),
-    "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P]),
+    "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P, _P]),
     "kmls_rule_supports": (ctypes.c_int, [_P, _I64, _P, _I64, _P, _P]),
     "kmls_rule_checksum": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P]),
     "kmls_rule_division_selftest": (ctypes.c_int, [_I64, _I64, ctypes.c_uint64, _P, _P]),

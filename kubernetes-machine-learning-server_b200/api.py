@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import os
 import pickle
+import warnings
 from typing import Dict, Iterable, List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -130,12 +131,15 @@ class HostTables:
 
 def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: float,
              min_confidence: Optional[float] = None, max_len: Optional[int] = None,
-             host_tables: Optional[HostTables] = None, split_rules: bool = False, **mine_kwargs):
+             host_tables: Optional[HostTables] = None, split_rules: bool = False,
+             rules_required: bool = True, **mine_kwargs):
     """Host CSR of track ids in, device tables out: (MineResult, RuleTable or None).
     Under torchrun each rank keeps a contiguous range of the playlists. With ``host_tables``
     the level tables are also streamed to pinned host memory during the mining (see
     HostTables); ``offsets``/``ids`` may be pinned torch tensors to make the upload async.
-    ``split_rules``: under torchrun, each rank generates only its share of the rule table."""
+    ``split_rules``: under torchrun, each rank generates only its share of the rule table.
+    ``rules_required=False`` turns a rule table that cannot be built into a warning and
+    ``rules = None`` instead of an error (the reference-facing entry points use this)."""
     device = _device()
     group, rank, world = _dist_group()
     n_total = len(offsets) - 1
@@ -155,7 +159,18 @@ def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: fl
                          group=group, max_len=max_len, **mine_kwargs)
     rules = None
     if min_confidence is not None:
-        rules = miner.generate_rules(res, min_confidence, part=(rank, world) if split_rules else (0, 1))
+        try:
+            rules = miner.generate_rules(res, min_confidence,
+                                         part=(rank, world) if split_rules else (0, 1))
+        except _lib.KmlsError as e:
+            if rules_required:
+                raise
+            # The rule table is an ADDITION to the reference's result: when it
+            # cannot be built (an itemset of more than 15 members, a table larger than the free
+            # device memory or max_rules) the itemsets - all the reference itself computes -
+            # must still come back.
+            warnings.warn(f"rule table skipped: {e}", RuntimeWarning, stacklevel=2)
+            rules = None
     if host_tables is not None:
         host_tables.finish(res)
     return res, rules
@@ -224,7 +239,7 @@ def calculate_and_save_fp_growth_fast(playlist_dict: dict, min_support=0.07, tot
     transactions = list(playlist_dict.values())
     columns, offsets, ids = encode_transactions(transactions)
     conf = MIN_CONFIDENCE if min_confidence is None else min_confidence
-    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf, max_len)
+    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf, max_len, rules_required=False)
     songs_to_song_sets = recommendations_from_result(res, columns)
 
     ts = total_songs if total_songs is not None else globals()["total_songs"]
@@ -270,7 +285,7 @@ def recommendations_from_frame(pid, track_name, min_support=0.07, total_songs=No
         miner.thresholds(min_support, 1)
     columns, offsets, ids = encode_frame(pid, track_name)
     conf = MIN_CONFIDENCE if min_confidence is None else min_confidence
-    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf)
+    res, rules = mine_ids(offsets, ids, len(columns), min_support, conf, rules_required=False)
     out = recommendations_from_result(res, columns)
     ts = total_songs if total_songs is not None else (globals()["total_songs"] or len(columns))
     missing = ts - len(out)

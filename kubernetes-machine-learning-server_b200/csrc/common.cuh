@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cstdarg>
 #include <cstdint>
 #include <cstdio>
@@ -67,13 +68,18 @@ __host__ __device__ __forceinline__ uint64_t finish_key(uint64_t sum, int k) {
   return mix64(sum ^ ((uint64_t)k << 56)) | 1ull;  // never 0 (0 marks an empty slot)
 }
 
+// SM count of the CURRENT device, cached per device ordinal (a process may use several GPUs).
 inline int num_sms() {
-  static int n = 0;
+  constexpr int kMaxDevices = 64;
+  static std::atomic<int> cache[kMaxDevices];
+  int dev = 0;
+  cudaGetDevice(&dev);
+  const bool cacheable = dev >= 0 && dev < kMaxDevices;
+  int n = cacheable ? cache[dev].load(std::memory_order_relaxed) : 0;
   if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
     if (n <= 0) n = 148;
+    if (cacheable) cache[dev].store(n, std::memory_order_relaxed);
   }
   return n;
 }

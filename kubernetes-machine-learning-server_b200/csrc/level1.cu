@@ -179,12 +179,9 @@ extern "C" int kmls_encode_bitmap(const int64_t* d_offsets, const int32_t* d_ite
   int rows_per_tile = (n_rows + row_tiles - 1) / row_tiles;
   KMLS_REQUIRE(row_tiles <= 65535, "kmls_encode_bitmap: too many rows");
   size_t smem = (size_t)rows_per_tile * kEncodeWordsPerRow * sizeof(uint32_t);
-  static bool attr_set = false;
-  if (!attr_set) {
-    KMLS_CUDA(cudaFuncSetAttribute(k_encode_bitmap, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   kEncodeMaxRows * kEncodeWordsPerRow * (int)sizeof(uint32_t)));
-    attr_set = true;
-  }
+  // the opt-in is a per-device attribute: set it on every call (a process may mine on several GPUs)
+  KMLS_CUDA(cudaFuncSetAttribute(k_encode_bitmap, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 kEncodeMaxRows * kEncodeWordsPerRow * (int)sizeof(uint32_t)));
   dim3 grid((unsigned)col_tiles, (unsigned)row_tiles);
   k_encode_bitmap<<<grid, kEncodeThreads, smem, s>>>(d_offsets, d_items, n_playlists,
                                                      d_row_of_item, n_items, n_rows,

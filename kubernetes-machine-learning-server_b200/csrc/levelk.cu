@@ -256,6 +256,7 @@ extern "C" int kmls_exclusive_scan_i32(const int32_t* d_in, int64_t n, int64_t* 
                                        void* d_scratch, size_t scratch_bytes,
                                        kmls_stream_t stream) {
   KMLS_REQUIRE(n >= 0 && d_out, "kmls_exclusive_scan_i32: bad arguments");
+  KMLS_REQUIRE(n == 0 || d_in, "kmls_exclusive_scan_i32: d_in is null");
   return scan_i32(d_in, n, d_out, d_scratch, scratch_bytes, ToI64(), (cudaStream_t)stream);
 }
 
@@ -431,7 +432,9 @@ extern "C" int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t*
 // process exits, whether or not this entry point is ever called. The first call on a
 // device looks up the array's device address (cudaGetSymbolAddress - the array's name in
 // host code is not a device pointer) and caches it for that device; make that first call
-// outside any stream capture. Nothing is allocated or freed, here or in CUB.
+// outside any stream capture. The cached address does not survive cudaDeviceReset(): a
+// process that resets a device must not call this entry point on it afterwards. Nothing is
+// allocated or freed, here or in CUB.
 //
 // Limits and sharing: n <= KMLS_NOALLOC_SCAN_MAX_N (4,194,304) - larger inputs are refused
 // with an error, never truncated. All calls on a device use the same array. It keeps
@@ -456,15 +459,17 @@ extern "C" int kmls_exclusive_scan_i32_noalloc(const int32_t* d_in, int64_t n, i
   KMLS_REQUIRE(n == 0 || d_in, "kmls_exclusive_scan_i32_noalloc: d_in is null");
   // device address of the array, looked up once per device with that device current
   constexpr int kMaxDevices = 64;
-  static void* scratch_of_device[kMaxDevices] = {nullptr};
+  // (relaxed atomics: two host threads making the first call together both look the address
+  // up and store the same value)
+  static std::atomic<void*> scratch_of_device[kMaxDevices];
   int dev = -1;
   KMLS_CUDA(cudaGetDevice(&dev));
   KMLS_REQUIRE(dev >= 0 && dev < kMaxDevices, "kmls_exclusive_scan_i32_noalloc: device index out of range");
-  void* scratch = scratch_of_device[dev];
+  void* scratch = scratch_of_device[dev].load(std::memory_order_relaxed);
   if (scratch == nullptr) {
     KMLS_CUDA(cudaGetSymbolAddress(&scratch, g_noalloc_scan_scratch));
     KMLS_REQUIRE(scratch != nullptr, "kmls_exclusive_scan_i32_noalloc: no device address for the scratch array");
-    scratch_of_device[dev] = scratch;
+    scratch_of_device[dev].store(scratch, std::memory_order_relaxed);
   }
   return scan_i32(d_in, n, d_out, scratch, kNoAllocScratchBytes, ToI64(), (cudaStream_t)stream);
 }

@@ -522,7 +522,11 @@ __global__ void __launch_bounds__(256)
 k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
               const int32_t* __restrict__ part, const int64_t* __restrict__ rule_off,
               int2* __restrict__ out_rule, double* __restrict__ out_confidence,
-              double* __restrict__ out_lift) {
+              double* __restrict__ out_lift, int32_t* __restrict__ bad) {
+  // `bad` counts the itemsets whose kept rules here differ in number from what pass 1 sized
+  // for them (rule_off[j + 1] - rule_off[j]): the two passes decide "confidence >= c" with
+  // different instruction sequences, and a disagreement would otherwise write outside the
+  // itemset's range unnoticed. The caller treats a non-zero count as an error.
   const int lane = threadIdx.x & 31;
   const int n_sub = 1 << (k - 1);
   const uint32_t full = (1u << k) - 1u;
@@ -551,6 +555,9 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
         if (ca >= 0 && cc >= 0) r = rule_values(s_x, ca, cc, n_total, rcp_n, min_conf);
       }
       const uint32_t m1 = __ballot_sync(0xffffffffu, r.k1), m2 = __ballot_sync(0xffffffffu, r.k2);
+      if (j < lvl_count && s == 0 &&
+          rule_off[j + 1] - rule_off[j] != (int64_t)(__popc(m1 & gmask) + __popc(m2 & gmask)))
+        atomicAdd(bad, 1);
       if (r.k1 || r.k2) {
         const int64_t base = rule_off[j];
         if (r.k1) {
@@ -629,6 +636,7 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
         cc[u] = nc[u];
       }
     }
+    if (lane == 0 && pos != rule_off[j + 1]) atomicAdd(bad, 1);
   }
 }
 
@@ -820,7 +828,8 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
                                 int32_t k, int64_t lvl_begin, int64_t lvl_count,
                                 int64_t n_playlists_total, double min_confidence,
                                 const void* d_part, const int64_t* d_rule_off, int32_t* d_out_rule,
-                                double* d_out_confidence, double* d_out_lift, kmls_stream_t stream) {
+                                double* d_out_confidence, double* d_out_lift, int32_t* d_mismatch,
+                                kmls_stream_t stream) {
   Arena a;
   int rc = make_arena(a, nullptr, d_counts, nullptr, level_sizes, max_k);
   if (rc) return rc;
@@ -828,12 +837,12 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
   KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
                "kmls_rules_write: itemset range out of bounds");
   if (lvl_count == 0) return 0;
-  KMLS_REQUIRE(d_part && d_rule_off && d_out_rule && d_out_confidence && d_out_lift &&
+  KMLS_REQUIRE(d_part && d_rule_off && d_out_rule && d_out_confidence && d_out_lift && d_mismatch &&
                    ((uintptr_t)d_out_rule & 7) == 0, "kmls_rules_write: null or misaligned pointer");
   int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int32_t*)d_part,
-      d_rule_off, (int2*)d_out_rule, d_out_confidence, d_out_lift);
+      d_rule_off, (int2*)d_out_rule, d_out_confidence, d_out_lift, d_mismatch);
   KMLS_LAUNCHED("k_rules_write");
   return 0;
 }

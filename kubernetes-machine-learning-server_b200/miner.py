@@ -631,7 +631,10 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
         for k, lvl_begin, cnt, out0, part_buf in plan:
             _lib.call("kmls_rules_write", arena_counts, sizes_ptr, max_k, k, lvl_begin, cnt,
                       res.n_playlists, float(min_confidence), part_buf, rule_off[out0:], o_rule,
-                      o_conf, o_lift, s)
+                      o_conf, o_lift, missing, s)
+        if dev.scalar(missing) != 0:
+            raise _lib.KmlsError("rule generation: pass 2 kept a different number of rules than pass 1 "
+                                 "sized for some itemset (the rule table would be corrupt)")
     return RuleTable(o_rule.view(n_rules, 2), o_conf, o_lift, arena_items, sizes.tolist(), arena_counts,
                      res.n_playlists)
 
