@@ -34,6 +34,10 @@ WORKLOADS = {
     # name: (n_playlists per GPU, n_tracks, mean_draws, alpha, min_support, min_confidence)
     "zipf_1Mx100k_s0.001": (1_000_000, 100_000, 72.0, 1.0, 0.001, 0.04),
     "zipf_200kx20k_s0.004": (200_000, 20_000, 50.0, 1.0, 0.004, 0.04),      # quick check
+    # a DENSE one-hot matrix (about 5 % ones, the regime of the reference's own ds2 scaled up):
+    # here the level-2 contraction is cheaper on the tensor cores than per playlist, so
+    # pair_impl="auto" picks the tcgen05 int8 GEMM
+    "dense_200kx4k_s0.02": (200_000, 4_000, 215.0, 0.2, 0.02, 0.3),
     # stand-ins for the reference's own (absent) CSVs, shaped after its report's ds2 log:
     # (n_playlists, n_names, -, -, MIN_SUPPORT, MIN_CONFIDENCE); generator synth.mpd_standin(seed)
     # BASELINE.json config 5: 10M playlists x 2M tracks in total, row-sharded over the ranks
@@ -42,7 +46,39 @@ WORKLOADS = {
     "mpd_standin_seed1_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
     "mpd_standin_seed2_s0.05": (2246, 2123, 0.0, 0.0, 0.05, 0.04),
 }
-TOTAL_IS_FIXED = {"zipf_10Mx2M_s0.001"}   # workloads whose playlist count is the job's, not per GPU
+TOTAL_IS_FIXED = {"zipf_10Mx2M_s0.001"}   # workloads generated shard by shard (a rank never holds the whole set)
+GOLDEN = os.path.join(ROOT, "tests", "golden", "full_size.json")
+
+
+def golden_for(name, min_support, n_total):
+    """The CPU oracle's result for this whole job (tests/golden/full_size.json, made by
+    tests/golden/make_full_size_golden.py), or None."""
+    try:
+        cases = json.load(open(GOLDEN))["cases"]
+    except (OSError, ValueError, KeyError):
+        return None
+    return cases.get(f"{name}|s={min_support:g}|n={n_total}")
+
+
+def whole_job_data(workload, shards=range(8)):
+    """Playlists of a workload that is generated shard by shard (config 5): the concatenation
+    of the given generator shards (all 8 = the whole job)."""
+    n_total = WORKLOADS[workload][0]
+    offs, its = [np.zeros(1, np.int64)], []
+    for r in shards:
+        o, i, t, s, conf = make_data(workload, shard=r, n_override=n_total // 8)
+        offs.append(o[1:] + offs[-1][-1])
+        its.append(i)
+    return np.concatenate(offs), np.concatenate(its), t, s, conf
+
+
+def rank_slice(off, items, rank, world):
+    """Playlists [rank*N/world, (rank+1)*N/world) of a CSR set (strong scaling: the job's
+    playlists are the same at every number of GPUs)."""
+    n = len(off) - 1
+    lo, hi = (n * rank) // world, (n * (rank + 1)) // world
+    o = off[lo:hi + 1]
+    return np.ascontiguousarray(o - o[0]), np.ascontiguousarray(items[o[0]:o[-1]])
 MIN_SUPPORT_OVERRIDE = None
 CPU_SAMPLE_PLAYLISTS = 100_000   # playlists of the CPU baseline's bounded sample
 CPU_RULE_STRIDE = 8              # rules are generated for 1/8 of the itemset table and scaled
@@ -87,8 +123,10 @@ def make_data(name, shard, n_override=None):
     off, items = synth.zipf_playlists(n, t, draws, alpha, seed=0, shard=shard,
                                       workers=min(16, os.cpu_count() or 1))
     log(f"[bench] generated {n} playlists ({len(items)} rows) in {time.time() - t0:.1f}s")
-    try:
-        np.savez(fn, offsets=off, items=items)
+    try:   # atomic: several ranks of one box may generate the same file at the same time
+        tmp = f"{fn}.{os.getpid()}.tmp.npz"
+        np.savez(tmp, offsets=off, items=items)
+        os.replace(tmp, fn)
     except OSError:
         pass
     return off, items, t, s, conf
@@ -229,42 +267,104 @@ def cpu_sample_run(name, threads):
                        f"(itemset, antecedent) splits evaluated (x{rule_scale:.2f})")}
 
 
+def try_mlxtend():
+    """The reference's own third-party miner (mlxtend 0.23.3, machine-learning/uv.lock:302), if
+    this box has it: run it on the hand vectors and diff with the oracle. It is absent from
+    every image seen so far; the outcome is reported either way."""
+    try:
+        import mlxtend  # noqa: F401
+        from mlxtend.frequent_patterns import fpgrowth
+        from mlxtend.preprocessing import TransactionEncoder
+    except Exception as e:      # noqa: BLE001
+        return {"available": False, "note": f"mlxtend: unavailable on this box ({type(e).__name__})"}
+    import pandas as pd
+    vec = json.load(open(os.path.join(ROOT, "tests", "golden", "hand_vectors.json")))
+    bad = checked = 0
+    for case in vec["cases"]:
+        tx, s_ = case.get("transactions"), case.get("min_support")
+        if not tx or s_ is None or "itemsets" not in case:
+            continue
+        te = TransactionEncoder()
+        df = pd.DataFrame(te.fit(tx).transform(tx), columns=te.columns_)
+        got = {frozenset(r.itemsets): int(round(r.support * len(tx)))
+               for r in fpgrowth(df, min_support=s_, use_colnames=True).itertuples()}
+        want = {frozenset(k.split("|")): int(v) for k, v in case["itemsets"].items()}
+        checked += 1
+        bad += got != want
+    return {"available": True, "version": getattr(mlxtend, "__version__", "?"),
+            "hand_vectors_checked": checked, "hand_vector_mismatches": int(bad)}
+
+
 def run_reference(args):
+    """The reference's algorithm on the host cores: ONE measured pass over the whole job
+    (mining + rules), whatever --steps/--warmup say - a pass takes about a minute, and an
+    extrapolated figure is not a measurement. The line reports the steps it really ran."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
     name = args.workload
-    vals = []
-    for i in range(args.warmup + args.steps):
-        if name.startswith("mpd_standin"):
-            sec, n_keys, n_sets = python_reference_run(name)
-            threads = 1
-            r = {"measured_s": sec, "estimate_full_s": sec,
-                 "sample": "the whole workload, Python restatement of mlxtend in the reference's glue, 1 thread"}
-        else:
-            r = cpu_sample_run(name, threads)
-        log(f"[bench/reference] step {i}: measured {r['measured_s']:.1f}s -> estimate {r['estimate_full_s']:.1f}s")
-        if i >= args.warmup:
-            vals.append(r)
-        if i == 0 and r["measured_s"] > 60:
-            # keep the whole run within minutes: one measured step stands for all of them
-            vals = [r] * args.steps
-            break
-    v = float(np.mean([r["estimate_full_s"] for r in vals]))
     n, t, draws, alpha, s, conf = WORKLOADS[name]
+    if MIN_SUPPORT_OVERRIDE is not None:
+        s = MIN_SUPPORT_OVERRIDE
+    extra = {}
+    if name.startswith("mpd_standin"):
+        secs = []
+        for i in range(args.warmup + args.steps):
+            sec, n_keys, n_sets = python_reference_run(name)
+            log(f"[bench/reference] step {i}: {sec:.2f}s")
+            if i >= args.warmup:
+                secs.append(sec)
+        v, threads, steps, warmup = float(np.mean(secs)), 1, args.steps, args.warmup
+        n_total = n
+        sample = ("the whole workload, every step: Python restatement of mlxtend inside the reference's own glue "
+                  "(main.py:262-313), 1 thread as the reference runs it; no rule table (the reference computes none)")
+    else:
+        from oracle import fpgrowth_c, mlxtend_restated as M
+        if name in TOTAL_IS_FIXED:
+            off, items, t, s, conf = whole_job_data(name)
+        else:
+            off, items, t, s, conf = make_data(name, shard=0)
+            if args.scaling == "weak" and args.gpus > 1:
+                extra["not_comparable"] = ("weak scaling: the GPU arm mines --gpus x this many playlists; "
+                                           "this arm mines one rank's set")
+        n_total = len(off) - 1
+        t1, tk = M.thresholds(s, n_total)
+        t0 = time.time()
+        r = fpgrowth_c.fpgrowth(off, items, t, t1, tk, store=not args.no_rules, n_threads=threads,
+                                rules_min_confidence=None if args.no_rules else conf)
+        v = time.time() - t0
+        steps, warmup = 1, 0
+        lv = r.level_counts
+        got = {"level_sizes": lv[1:int(np.max(np.nonzero(lv)[0], initial=0)) + 1].tolist(),
+               "itemset_checksum": str(r.checksum), "n_rules": r.n_rules,
+               "rule_checksum": None if r.rule_checksum is None else str(r.rule_checksum)}
+        want = golden_for(name, s, n_total)
+        extra["result"] = got
+        if want is not None:
+            keys = ["level_sizes", "itemset_checksum"] + ([] if args.no_rules else ["n_rules", "rule_checksum"])
+            extra["parity"] = {"ok": all(got[k] == want[k] for k in keys), "compared": keys,
+                               "source": "tests/golden/full_size.json"}
+        log(f"[bench/reference] one full pass: {v:.1f}s on {threads} threads: {got}")
+        sample = (f"the WHOLE job measured once ({n_total} playlists, every level, the full rule table): C++ "
+                  f"restatement of the reference's algorithm (oracle/fpgrowth_ref.cpp), {threads} threads; "
+                  f"--steps {args.steps} --warmup {args.warmup} were requested, 1 pass was run")
     line = {
         "impl": "reference", "metric": "mine+rules wall time", "value": v, "unit": "s",
-        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": v * 1e3,
-        "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "int64+f64",
-        "data": "synthetic",
-        "config": {"workload": name, "n_playlists_per_gpu": n, "n_tracks": t, "min_support": s,
-                   "min_confidence": conf, "note": "CPU oracle port of the reference algorithm (mlxtend "
-                   "FP-Growth + association_rules semantics, C++, all host threads); the reference itself "
-                   "(pure-Python mlxtend) is not installable here and cannot hold this workload in memory"},
-        "cpu_baseline": {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": vals[0]["sample"]},
+        "n_gpus": args.gpus, "steps": steps, "warmup": warmup, "steps_requested": args.steps,
+        "warmup_requested": args.warmup, "ms_per_step": v * 1e3,
+        "higher_is_better": False, "scaling": "strong" if (args.scaling == "strong" or name in TOTAL_IS_FIXED) else "weak",
+        "vs_baseline": None, "dtype": "int64+f64", "data": "synthetic",
+        "config": {"workload": name, "n_playlists": n_total, "n_tracks": t, "mean_draws": draws, "zipf_alpha": alpha,
+                   "min_support": s, "min_confidence": None if args.no_rules else conf,
+                   "note": "CPU oracle port of the reference algorithm (mlxtend FP-Growth + association_rules "
+                           "semantics, C++, all host threads); the reference itself (pure-Python mlxtend) is not "
+                           "installable here and cannot hold this workload in memory"},
+        "cpu_baseline": {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "mlxtend": try_mlxtend(),
     }
+    line.update(extra)
     emit(line)
 
 
@@ -286,10 +386,23 @@ def run_gpu(args):
         group = dist.group.WORLD
     name = args.workload
     fixed = name in TOTAL_IS_FIXED
-    off, items, n_tracks, s, conf = make_data(name, shard=rank,
-                                              n_override=WORKLOADS[name][0] // world if fixed else None)
+    strong = fixed or args.scaling == "strong"
+    if fixed:
+        # the job's set is the concatenation of 8 generator shards; rank r of R holds shards
+        # r*8/R .. (r+1)*8/R - 1, so the job is the same at every R that divides 8
+        n_all = WORKLOADS[name][0]
+        if 8 % world:
+            raise SystemExit(f"{name} is generated in 8 shards: --gpus must divide 8")
+        off, items, n_tracks, s, conf = whole_job_data(name, range(rank * 8 // world, (rank + 1) * 8 // world))
+        n_total = n_all
+    elif strong:
+        off, items, n_tracks, s, conf = make_data(name, shard=0)
+        n_total = len(off) - 1
+        off, items = rank_slice(off, items, rank, world)
+    else:
+        off, items, n_tracks, s, conf = make_data(name, shard=rank)
+        n_total = (len(off) - 1) * world
     n_local = len(off) - 1
-    n_total = n_local * world
     h_off = torch.from_numpy(off).pin_memory()
     h_items = torch.from_numpy(items).pin_memory()
     d_off, d_items = h_off.to(device), h_items.to(device)
@@ -484,6 +597,48 @@ def run_gpu(args):
         e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
         h2d = h_off.numel() * 8 + h_items.numel() * 4
 
+    # ---- parity: one more (untimed) pass, compared on the device with the CPU oracle's
+    # committed result for this whole job (tests/golden/full_size.json) - at every N
+    parity = None
+    if not args.no_parity:
+        res, rules = step(d_off, d_items)
+        cs_items = miner.itemset_checksum(res)
+        n_rules_all, cs_rules = rules.n_rules, 0
+        if not args.no_rules:
+            cs_rules = miner.rule_checksum(res, rules)
+        if world > 1:
+            # every rank holds the whole itemset table; the rule table is split by rank
+            t = torch.tensor([n_rules_all, cs_rules - (1 << 64) if cs_rules >= (1 << 63) else cs_rules],
+                             dtype=torch.int64, device=device)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)      # int64 wraps: sums modulo 2^64
+            n_rules_all, cs_rules = int(t[0].item()), int(t[1].item()) & ((1 << 64) - 1)
+            t = torch.tensor([cs_items - (1 << 64) if cs_items >= (1 << 63) else cs_items, res.n_itemsets],
+                             dtype=torch.int64, device=device)
+            tmax, tmin = t.clone(), t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+            ranks_agree = bool(torch.equal(tmax, tmin))
+        else:
+            ranks_agree = True
+        got = {"level_sizes": [int(c.numel()) for _, c in res.levels], "itemset_checksum": str(cs_items),
+               "n_rules": None if args.no_rules else n_rules_all,
+               "rule_checksum": None if args.no_rules else str(cs_rules)}
+        del res, rules
+        want = golden_for(name, s, n_total)
+        if want is None:
+            parity = {"ok": None, "note": "no committed oracle result for this job (tests/golden/full_size.json)",
+                      "ranks_agree": ranks_agree, "gpu": got}
+        else:
+            keys = ["level_sizes", "itemset_checksum"]
+            if not args.no_rules and want.get("n_rules") is not None and want.get("min_confidence") == conf:
+                keys += ["n_rules", "rule_checksum"]
+            ok = ranks_agree and all(got[k_] == want[k_] for k_ in keys)
+            parity = {"ok": ok, "compared": keys, "ranks_agree": ranks_agree, "gpu": got,
+                      "oracle": {k_: want[k_] for k_ in keys},
+                      "source": "tests/golden/full_size.json (CPU oracle oracle/fpgrowth_ref.cpp, "
+                                f"{want.get('oracle_seconds')} s on {want.get('oracle_threads')} threads)"}
+        log(f"[bench] parity: {parity}")
+
     verify = None
     if args.verify and world == 1:
         from oracle import fpgrowth_c, mlxtend_restated as M
@@ -526,10 +681,10 @@ def run_gpu(args):
         line = {
             "metric": "mine+rules wall time", "value": step_s, "unit": "s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3,
-            "higher_is_better": False, "scaling": "strong" if fixed else "weak", "vs_baseline": None,
+            "higher_is_better": False, "scaling": "strong" if strong else "weak", "vs_baseline": None,
             "dtype": "u32+f64",
             "data": "synthetic",
-            "config": {"workload": name, "n_playlists_per_gpu": n_local, "n_tracks": n_tracks, "mean_draws": draws,
+            "config": {"workload": name, "n_playlists": n_total, "n_playlists_per_gpu": n_local, "n_tracks": n_tracks, "mean_draws": draws,
                        "zipf_alpha": alpha, "min_support": s, "min_confidence": None if args.no_rules else conf,
                        "parallelism": f"playlist-sharded x{world}, rules split by itemset range",
                        "l2": ("inputs larger than L2 (CSR 0.5 GB, bitmap 0.75 GB per GPU)" if n_local >= 500_000
@@ -548,11 +703,15 @@ def run_gpu(args):
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
             "top_kernel": top,
+            "parity": parity,
             "verify_full_size": verify,
         }
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and parity["ok"] is False:
+        log("[bench] PARITY MISMATCH against the committed oracle result")
+        sys.exit(3)
 
 
 def main():
@@ -578,6 +737,10 @@ def main():
     ap.add_argument("--verify", action="store_true",
                     help="after the run, mine the FULL workload with the CPU oracle (minutes) and compare level "
                          "sizes, the itemset checksum and the number of rules")
+    ap.add_argument("--no-parity", action="store_true", help="skip the comparison with the committed oracle result")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
+                    help="strong (default): the job's playlists are the same at every --gpus N, sliced over the "
+                         "ranks; weak: every rank generates its own set of the workload's size")
     ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
     ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc", "csr"])
     ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])

@@ -280,6 +280,14 @@ int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_
                      double min_confidence, const void* d_part, const int64_t* d_rule_off,
                      int32_t* d_out_rule, double* d_out_confidence, double* d_out_lift,
                      int32_t* d_mismatch, kmls_stream_t stream);
+/* No counterpart in the reference (parity plumbing). Adds to *d_out (NOT zeroed here) the
+ * order-independent checksum of one level table d_items[n][k] (bitmap rows) / d_counts[n]:
+ * sum over itemsets of mix(sum_i mix(track id_i + 1) ^ mix(count * 0x100000001B3 + k)) mod
+ * 2^64, track ids through d_row_items. Same arithmetic as the CPU oracle's, so a full-size
+ * result can be compared with a committed golden value without leaving the device. */
+int kmls_itemset_checksum(const int32_t* d_items, const int32_t* d_counts, int64_t n, int32_t k,
+                          const int32_t* d_row_items, uint64_t* d_out, kmls_stream_t stream);
+
 /* The support column of the rule table, on demand: d_out[r] = count of rule r's itemset / N
  * (d_counts = the arena's counts). Not written by pass 2: it would be a quarter of its bytes
  * and is one gather away. */
@@ -304,6 +312,111 @@ int kmls_rule_checksum(const int32_t* d_items, const int32_t* d_counts, const in
  * 0. */
 int kmls_rule_division_selftest(int64_t n_playlists_total, int64_t n_samples, uint64_t seed,
                                 uint64_t* d_mismatches, kmls_stream_t stream);
+
+/* ---- the whole path in one call (what stands behind
+ *      TransactionEncoder().fit().transform() + fpgrowth(df, min_support, use_colnames=True),
+ *      machine-learning/main.py:267-272, and behind association_rules for the rule table) ---
+ *
+ * kmls_mine runs every level on the device and returns when the tables are complete; the
+ * level loop, its sizing decisions and its buffers live inside the library. Device memory
+ * comes from ONE caller-supplied workspace (no cudaMalloc here): tables that make up the
+ * result are placed at its low end and stay valid until the caller reuses the workspace,
+ * per-level buffers come and go above them. When the workspace is too small the call fails
+ * with a capacity error whose text says how much was missing; nothing is ever truncated -
+ * call again with a larger workspace. The host reads a few sizes per level from a pinned
+ * mailbox (a small cudaHostAlloc per host thread, made on the thread's first call; host
+ * memory, but make that first call outside stream capture). */
+#define KMLS_MAX_LEVELS 32
+
+typedef struct kmls_mine_options {
+  int32_t max_len;        /* longest itemset to mine; 0 = no limit (fpgrowth's max_len=None) */
+  int32_t pair_impl;      /* level 2: 0 = choose by cost, 1 = per playlist (sparse), 2 = CUDA-core
+                             AND+popc, 3 = tcgen05 int8 GEMM */
+  int32_t keep_words;     /* conditional rows at most this wide keep their column space (AND
+                             instead of bit extract); 0 = default (256), at most 256 */
+  int32_t n_parts;        /* class partition for multi-GPU jobs: this call mines only the      */
+  int32_t part;           /* subtrees of the frequent pairs in blocks part, part + n_parts, ... */
+  int32_t part_block;     /* of part_block consecutive pairs; n_parts <= 1 = everything        */
+  int64_t max_itemsets;   /* guard: fail (never truncate) beyond this many itemsets; 0 = 2e8   */
+  void* h_tables;         /* optional PINNED host buffer: every level table is copied there on */
+  size_t h_tables_bytes;  /* a side stream as soon as it is final, while mining continues      */
+} kmls_mine_options;
+
+typedef struct kmls_mine_result {
+  int64_t n_playlists_total;
+  int32_t t1, tk, thr_k;  /* thresholds used: level 1, levels >= 2, and the one applied */
+  int32_t n_rows;         /* frequent tracks = rows of the bitmap, in ascending-support order */
+  int32_t max_k;          /* longest frequent itemset */
+  int32_t pair_impl_used;
+  int64_t n_itemsets;
+  int64_t kernel_launches;
+  size_t workspace_peak_bytes;
+  /* index k = itemset size (0 unused). Tables of level k, as BYTE OFFSETS into the workspace
+   * (-1 = none): items int32[n][k] (bitmap rows, ascending inside an itemset, table sorted),
+   * counts int32[n], parent int32[n] (index in level k-1 of the itemset minus its last member,
+   * k >= 2; for k == 2 the first member's row). */
+  int64_t level_size[KMLS_MAX_LEVELS + 2];
+  int64_t level_candidates[KMLS_MAX_LEVELS + 2];
+  int64_t level_row_words[KMLS_MAX_LEVELS + 2];  /* words of conditional rows built for the level */
+  int64_t items_off[KMLS_MAX_LEVELS + 2];
+  int64_t counts_off[KMLS_MAX_LEVELS + 2];
+  int64_t parent_off[KMLS_MAX_LEVELS + 2];
+  int64_t row_items_off;    /* int32[n_rows]: row -> track id */
+  int64_t occurrences_off;  /* int32[n_items]: rows of the input per track (with repeats) */
+  int64_t pair_off;         /* int32[n_rows][n_rows] pair counts (upper triangle valid), or -1 */
+  /* with options.h_tables: byte offsets into that host buffer, same indexing */
+  int64_t h_items_off[KMLS_MAX_LEVELS + 2];
+  int64_t h_counts_off[KMLS_MAX_LEVELS + 2];
+  int64_t h_row_items_off;
+  int64_t h_bytes;
+} kmls_mine_result;
+
+/* The two integer thresholds mlxtend's float tests amount to, computed with
+ * the same IEEE double operations as Python: *t1 = min{c : c / (double)n >= min_support}
+ * (fpcommon.setup_fptree), *tk = ceil(min_support * n) (fpgrowth.fpgrowth). Returns an
+ * argument error for min_support <= 0 (mlxtend raises ValueError there). */
+int kmls_thresholds(double min_support, int64_t n_playlists_total, int64_t* t1, int64_t* tk);
+
+/* Playlists in CSR (this process's: d_offsets[n_playlists + 1], d_items[nnz], track ids
+ * 0 .. n_items-1) -> all frequent itemsets. n_playlists_total is N of the whole job (it may
+ * exceed n_playlists only when the caller merges counts itself; single process: equal).
+ * d_workspace: 256-byte aligned device memory. All work is enqueued on `stream`; the call
+ * synchronises that stream several times per level and returns with the tables complete. */
+int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64_t n_playlists, int32_t n_items,
+              int64_t n_playlists_total, int32_t t1, int32_t tk, const kmls_mine_options* options,
+              void* d_workspace, size_t workspace_bytes, kmls_mine_result* result,
+              kmls_stream_t stream);
+
+typedef struct kmls_rules_result {
+  int64_t n_rules;          /* rules this call wrote (its part of the table) */
+  int64_t n_itemsets;       /* itemsets of all levels (= length of the arena's counts) */
+  int64_t n_splits;         /* pass-1 slots of this part: sum of 2^(k-1) over its itemsets */
+  /* byte offsets into the workspace (-1 = none): rule int32[n_rules][2] = (itemset global id =
+   * position in the level tables concatenated in level order, antecedent bit mask over its
+   * members), confidence double[n_rules], lift double[n_rules]; and the concatenated level
+   * tables the ids refer to: arena_items (members, level after level), arena_counts int32 */
+  int64_t rule_off, confidence_off, lift_off, arena_items_off, arena_counts_off;
+  size_t workspace_needed_bytes;  /* set as soon as it is known, also when the call fails for lack of room */
+  size_t workspace_peak_bytes;
+  int64_t kernel_launches;
+  int32_t pass1_used;       /* 1 = gather route, 2 = search route */
+  int32_t reserved;
+} kmls_rules_result;
+
+/* association_rules(metric="confidence", min_threshold=min_confidence) over the tables of a
+ * kmls_mine result (mined->*_off are byte offsets from d_tables_base, normally the mining
+ * workspace; a caller that assembled the tables itself may pass absolute addresses and a NULL
+ * base): confidence = (cX/N)/(cA/N), lift = confidence/(cC/N) in mlxtend's operation order,
+ * kept iff confidence >= min_confidence; support is the itemset's own count / N
+ * (kmls_rule_supports). part / n_parts: write only the part-th of n_parts contiguous slices of
+ * the table, cut by work (how the ranks of a multi-GPU job divide it; every rank needs the
+ * whole itemset table). pass1: 0 = choose, 1 = gather (whole table only), 2 = search.
+ * d_workspace must not overlap the tables. Capacity errors name the bytes needed
+ * (result->workspace_needed_bytes); max_rules <= 0 = 4e9. Itemsets of more than 15 members
+ * are refused. */
+int kmls_rules(const kmls_mine_result* mined, const void* d_tables_base, double min_confidence,
+               int32_t part, int32_t n_parts, int32_t pass1, int64_t max_rules, void* d_workspace,
+               size_t workspace_bytes, kmls_rules_result* result, kmls_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -55,10 +55,37 @@ SIGNATURES = {
     "kmls_rules_subsets": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P, _P, _P]),
     "kmls_rules_count_gather": (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _I64, _F64, _P, _P, _P, _P]),
     "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P, _P]),
+    "kmls_itemset_checksum": (ctypes.c_int, [_P, _P, _I64, _I32, _P, _P, _P]),
     "kmls_rule_supports": (ctypes.c_int, [_P, _I64, _P, _I64, _P, _P]),
     "kmls_rule_checksum": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P]),
+    "kmls_thresholds": (ctypes.c_int, [_F64, _I64, _P, _P]),
+    "kmls_mine": (ctypes.c_int, [_P, _P, _I64, _I32, _I64, _I32, _I32, _P, _P, _SZ, _P, _P]),
     "kmls_rule_division_selftest": (ctypes.c_int, [_I64, _I64, ctypes.c_uint64, _P, _P]),
 }
+
+KMLS_MAX_LEVELS = 32
+_LV = KMLS_MAX_LEVELS + 2
+
+
+class MineOptions(ctypes.Structure):
+    """struct kmls_mine_options (include/kmls_b200.h)."""
+    _fields_ = [("max_len", c_int32), ("pair_impl", c_int32), ("keep_words", c_int32),
+                ("n_parts", c_int32), ("part", c_int32), ("part_block", c_int32),
+                ("max_itemsets", c_int64), ("h_tables", c_void_p), ("h_tables_bytes", c_size_t)]
+
+
+class MineResultC(ctypes.Structure):
+    """struct kmls_mine_result (include/kmls_b200.h)."""
+    _fields_ = [("n_playlists_total", c_int64), ("t1", c_int32), ("tk", c_int32), ("thr_k", c_int32),
+                ("n_rows", c_int32), ("max_k", c_int32), ("pair_impl_used", c_int32),
+                ("n_itemsets", c_int64), ("kernel_launches", c_int64), ("workspace_peak_bytes", c_size_t),
+                ("level_size", c_int64 * _LV), ("level_candidates", c_int64 * _LV),
+                ("level_row_words", c_int64 * _LV), ("items_off", c_int64 * _LV),
+                ("counts_off", c_int64 * _LV), ("parent_off", c_int64 * _LV),
+                ("row_items_off", c_int64), ("occurrences_off", c_int64), ("pair_off", c_int64),
+                ("h_items_off", c_int64 * _LV), ("h_counts_off", c_int64 * _LV),
+                ("h_row_items_off", c_int64), ("h_bytes", c_int64)]
+
 
 _lib = None
 
@@ -106,7 +133,20 @@ def _arg(a):
     # torch tensors are passed as their device (or host) address
     if hasattr(a, "data_ptr"):
         return a.data_ptr()
+    if isinstance(a, ctypes.Structure):
+        return ctypes.addressof(a)
     return a
+
+
+EXTRA_LAUNCHES = 0   # kernels launched inside the one-call entry points (they report their own count)
+
+
+def call_rc(name: str, *args):
+    """Call an int-returning entry point and hand back (return code, error text) instead of
+    raising: for callers that react to a capacity error by retrying with a larger buffer."""
+    lib = load()
+    rc = getattr(lib, name)(*[_arg(a) for a in args])
+    return rc, (lib.kmls_last_error().decode("utf-8", "replace") if rc != 0 else "")
 
 
 def call(name: str, *args, algo_bytes=None):
@@ -128,7 +168,7 @@ def call(name: str, *args, algo_bytes=None):
 
 
 def kernel_launches() -> int:
-    return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in CALLS.items())
+    return sum(KERNELS_PER_CALL.get(k, 1) * v for k, v in CALLS.items()) + EXTRA_LAUNCHES
 
 
 def value(name: str, *args):

@@ -416,6 +416,41 @@ extern "C" int kmls_emit_level(const int32_t* d_items, int32_t k, const int32_t*
 }
 
 // ---------------------------------------------------------------------------------------
+// Order-independent checksum of a level table, for comparing a whole result with another
+// implementation's without moving it (same arithmetic as the CPU oracle's Sink::emit and
+// oracle/fpgrowth_c.itemset_checksum): sum over itemsets of
+//   mix( sum_i mix(track id_i + 1)  ^  mix(count * 0x100000001B3 + k) )   (mod 2^64).
+// ---------------------------------------------------------------------------------------
+namespace kmls {
+__global__ void __launch_bounds__(256)
+k_itemset_checksum(const int32_t* __restrict__ items, const int32_t* __restrict__ counts, int64_t n,
+                   int k, const int32_t* __restrict__ row_items, unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    uint64_t h = 0;
+    for (int t = 0; t < k; ++t) h += mix64((uint64_t)__ldg(row_items + __ldg(items + i * k + t)) + 1);
+    acc += mix64(h ^ mix64((uint64_t)__ldg(counts + i) * 0x100000001B3ull + (uint64_t)k));
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+}  // namespace kmls
+
+extern "C" int kmls_itemset_checksum(const int32_t* d_items, const int32_t* d_counts, int64_t n,
+                                     int32_t k, const int32_t* d_row_items, uint64_t* d_out,
+                                     kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && k >= 1 && d_out, "kmls_itemset_checksum: bad arguments");
+  if (n == 0) return 0;
+  KMLS_REQUIRE(d_items && d_counts && d_row_items, "kmls_itemset_checksum: null pointer");
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
+  k_itemset_checksum<<<grid, 256, 0, (cudaStream_t)stream>>>(d_items, d_counts, n, k, d_row_items,
+                                                            (unsigned long long*)d_out);
+  KMLS_LAUNCHED("k_itemset_checksum");
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
 // kmls_exclusive_scan_i32_noalloc: the 64-bit exclusive scan above for callers that have no
 // way to hand over a scratch buffer.
 //

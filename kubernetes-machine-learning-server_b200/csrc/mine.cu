@@ -1,0 +1,950 @@
+// kmls_mine: the whole mining path behind one C call.
+//
+// Stands where the reference calls mlxtend (machine-learning/main.py:267-272:
+// TransactionEncoder().fit().transform() + fpgrowth(df, min_support, use_colnames=True)) and
+// produces the result set of SURVEY.md section 8c item 5, level by level:
+//
+//   level 1   item histogram -> select + order the frequent tracks -> bit-packed vertical
+//             bitmap (k_encode_bitmap) -> exact supports (k_row_popcount)
+//   level 2   pair counts (per playlist, CUDA-core or tcgen05 int8 GEMM) -> frequent pairs
+//             -> conditional rows of the pairs (k_row_tidlists + k_project_gather)
+//   level k   k_join_size -> k_count_project -> k_emit_rows          (until a level is empty)
+//
+// Levels >= 3 are where this file differs from the kernel-by-kernel entry points the Python
+// loop of round 1 drove: the support of a candidate (P, x_i, x_j) is the popcount of
+// row(P,x_i) AND row(P,x_j), and the conditional row of a SURVIVING candidate is that same
+// AND (or its bit-extract). k_count_project forms it once: a warp owns a parent p = (P,x_i),
+// keeps row(p) in registers, streams the rows of its later siblings through, and stores the
+// AND of every candidate that reaches the threshold straight into the slot reserved for it
+// in the next level's arena. Slots are sized before counting (all candidates of a parent have
+// the same row width), so there is no second pass over the rows and no compaction of them:
+// the new level table simply points at the slots of the survivors.
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
+#include <cub/iterator/counting_input_iterator.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
+#include <cmath>
+#include <cstring>
+
+#include "common.cuh"
+#include "kmls_b200.h"
+#include "workspace.cuh"
+
+namespace kmls {
+
+volatile int64_t* mailbox() {
+  static thread_local int64_t* box = nullptr;
+  if (box == nullptr) {
+    void* p = nullptr;
+    if (cudaHostAlloc(&p, 64 * sizeof(int64_t), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) {
+      cudaGetLastError();
+      return nullptr;
+    }
+    box = (int64_t*)p;
+  }
+  return box;
+}
+
+// up to four device words -> mailbox (null sources are skipped)
+__global__ void k_post(const int64_t* a, const int64_t* b, const int32_t* c, const int32_t* d,
+                       volatile int64_t* dst) {
+  if (a) dst[0] = *a;
+  if (b) dst[1] = *b;
+  if (c) dst[2] = *c;
+  if (d) dst[3] = *d;
+  __threadfence_system();
+}
+
+struct I2 {
+  long long a, b;
+};
+struct I2Sum {
+  __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.a + y.a, x.b + y.b}; }
+};
+
+// ---- level 1 helpers --------------------------------------------------------------------
+struct OccAtLeast {
+  const int32_t* occ;
+  int32_t thr;
+  __host__ __device__ bool operator()(int32_t i) const { return occ[i] >= thr; }
+};
+
+__global__ void __launch_bounds__(256)
+k_gather_i32(const int32_t* __restrict__ src, const int32_t* __restrict__ idx, int64_t n,
+             int32_t* __restrict__ dst) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = src[idx[i]];
+}
+
+__global__ void __launch_bounds__(256) k_fill_i32(int32_t* __restrict__ dst, int64_t n, int32_t v) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = v;
+}
+
+// row_of_item[cand[r]] = r; level-1 table: items1[r] = r
+__global__ void __launch_bounds__(256)
+k_number_rows(const int32_t* __restrict__ cand, int32_t n_rows, int32_t* __restrict__ row_of_item,
+              int32_t* __restrict__ items1) {
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+    row_of_item[cand[r]] = r;
+    if (items1) items1[r] = r;
+  }
+}
+
+// flags[0] += 1 for every row whose exact support differs from the occurrence count it was
+// ordered by; flags[1] (64-bit, at flags + 2) += the supports (mean kept tracks per playlist)
+__global__ void __launch_bounds__(256)
+k_check_counts(const int32_t* __restrict__ counts, const int32_t* __restrict__ keys, int32_t n_rows,
+               int32_t* __restrict__ flags) {
+  long long sum = 0;
+  int bad = 0;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
+    bad += counts[r] != keys[r];
+    sum += counts[r];
+  }
+  if (bad) atomicAdd(flags, bad);
+  if (sum) atomicAdd((unsigned long long*)(flags + 2), (unsigned long long)sum);
+}
+
+// mlxtend's root single-path shortcut: the root FP-tree is one path iff
+// the supports are nested, i.e. every pair count equals the rarer member's support (rows are
+// in ascending-support order, so the rarer member of (i, j), i < j, is i). flag += violations.
+__global__ void __launch_bounds__(256)
+k_nested_check(const int32_t* __restrict__ pair, const int32_t* __restrict__ counts1, int32_t n_rows,
+               int32_t* __restrict__ flag) {
+  int bad = 0;
+  const int64_t n2 = (int64_t)n_rows * n_rows;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n2; e += (int64_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e / n_rows), j = (int)(e - (int64_t)i * n_rows);
+    if (j > i && pair[e] != counts1[i]) ++bad;
+  }
+  if (bad) atomicAdd(flag, bad);
+}
+
+// the two members of every pair as separate columns (the first is the "parent" column of level 2)
+__global__ void __launch_bounds__(256)
+k_pair_parents(const int32_t* __restrict__ items2, int64_t n2, int32_t* __restrict__ par2,
+               int32_t* __restrict__ second2) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) {
+    par2[i] = items2[2 * i];
+    second2[i] = items2[2 * i + 1];
+  }
+}
+
+// ---- levels >= 3 --------------------------------------------------------------------------
+// Join sizing, one thread per itemset p of level k. Its candidates are its later siblings
+// (same parent; the table is sorted, so they follow it). ncand[p] = their number, wnew[p] =
+// width in words of the conditional rows of p's children: p's own width when that is at
+// most keep_words (the children stay in p's column space: AND), else ceil(count(p) / 32)
+// padded to 4 words (columns where row(p) is 0 are squeezed out: bit extract).
+// `n_parts > 1`: only itemsets of blocks part, part + n_parts, ... get candidates (level 2
+// of a class-partitioned job; deeper levels hold only owned subtrees anyway).
+__global__ void __launch_bounds__(256)
+k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
+            const int32_t* __restrict__ counts, int64_t n, int keep_words, int n_parts, int part,
+            int part_block, int32_t* __restrict__ ncand, int32_t* __restrict__ wnew) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t w_old = roww[p];
+    int32_t m = 0, w = 0;
+    const bool mine = n_parts <= 1 || (int)((p / part_block) % n_parts) == part;
+    if (w_old > 0 && mine) {
+      const int32_t cls = __ldg(par + p);
+      // end of the class: gallop forward, then bisect the last stride
+      int64_t lo = p, step = 1;              // par[lo] == cls
+      while (lo + step < n && __ldg(par + lo + step) == cls) {
+        lo += step;
+        step <<= 1;
+      }
+      int64_t hi = min(lo + step, n);        // par[hi] != cls or hi == n
+      while (hi - lo > 1) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (__ldg(par + mid) == cls) lo = mid; else hi = mid;
+      }
+      m = (int32_t)(lo - p);
+      w = w_old <= keep_words ? w_old : ((((__ldg(counts + p) + 31) >> 5) + 3) & ~3);
+    }
+    ncand[p] = m;
+    wnew[p] = w;
+  }
+}
+
+struct CandSlots {
+  const int32_t* ncand;
+  const int32_t* wnew;
+  __host__ __device__ I2 operator()(int64_t p) const {
+    const long long m = ncand[p];
+    return I2{m, m * (long long)wnew[p]};
+  }
+};
+
+__global__ void k_i2_total(const int32_t* ncand, const int32_t* wnew, int64_t n, I2* off2,
+                           volatile int64_t* box) {
+  I2 t{0, 0};
+  if (n > 0) {
+    const long long m = ncand[n - 1];
+    t = I2{off2[n - 1].a + m, off2[n - 1].b + m * (long long)wnew[n - 1]};
+  }
+  off2[n] = t;
+  box[0] = t.a;
+  box[1] = t.b;
+  __threadfence_system();
+}
+
+__device__ __forceinline__ uint4 or4z() { return make_uint4(0u, 0u, 0u, 0u); }
+
+constexpr int kAndIlp = 4;   // candidates of a parent in flight per warp (AND route)
+constexpr int kChunk = 8;    // candidates of a parent handled together (bit-extract route)
+constexpr int kKeepWordsMax = 256;
+
+// Count + project, one warp per parent p (see the file header). Candidate i of p is its i-th
+// later sibling q = p + 1 + i; its number in the level's candidate list is off2[p].a + i and
+// its slot in the new arena starts at word off2[p].b + i * wnew[p].
+//
+// AND route (row(p) at most keep_words <= 256 words): row(p) sits in two uint4 registers per
+// lane; per candidate two 128-bit loads, AND, popcount, warp reduction; a surviving AND is
+// stored from the registers it is already in. A parent's FIRST survivor is held back until a
+// second one appears: an only child is never joined again, so its row is never written.
+//
+// Bit-extract route (wider rows): per chunk of up to 8 candidates, first the popcounts of
+// row(p) AND row(q) (128-bit loads, all rows of the chunk per mask block), then, for the
+// survivors only, new_row = row(q) with the columns where row(p) is 0 squeezed out: 32 mask
+// words per step, the compress network's move masks (Hacker's Delight 7-4) derived ONCE per
+// mask word for all survivors of the chunk, output words assembled in shared memory.
+__global__ void __launch_bounds__(256)
+k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
+                const int32_t* __restrict__ roww_old, const int32_t* __restrict__ ncand,
+                const int32_t* __restrict__ wnew, const I2* __restrict__ off2, int64_t n, int32_t thr,
+                int keep_words, uint32_t* __restrict__ arena_new, int32_t* __restrict__ cand_cnt,
+                int32_t* __restrict__ cand_p) {
+  __shared__ uint32_t sbuf[8][kChunk][36];
+  __shared__ int64_t s_src[8][kChunk], s_dst[8][kChunk];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int64_t p = (int64_t)blockIdx.x * 8 + warp; p < n; p += (int64_t)gridDim.x * 8) {
+    const int m = __ldg(ncand + p);
+    if (m == 0) continue;                        // warp-uniform
+    const int w_old = __ldg(roww_old + p), w_new = __ldg(wnew + p);
+    const I2 o = off2[p];
+    const uint32_t* rowp = arena_old + __ldg(rowptr_old + p);
+    if (w_old <= keep_words) {
+      const int nv = w_old >> 2;
+      const uint4* p4 = reinterpret_cast<const uint4*>(rowp);
+      const bool h0 = lane < nv, h1 = lane + 32 < nv;
+      const uint4 m0 = h0 ? ldg4(p4 + lane) : or4z();
+      const uint4 m1 = h1 ? ldg4(p4 + lane + 32) : or4z();
+      int n_surv = 0, pend_i = 0;
+      uint4 pend0 = or4z(), pend1 = or4z();
+      for (int i0 = 0; i0 < m; i0 += kAndIlp) {
+        uint4 a0[kAndIlp], a1[kAndIlp];
+#pragma unroll
+        for (int u = 0; u < kAndIlp; ++u) {
+          a0[u] = a1[u] = or4z();
+          if (i0 + u < m) {
+            const uint4* q4 = reinterpret_cast<const uint4*>(arena_old + __ldg(rowptr_old + p + 1 + i0 + u));
+            if (h0) a0[u] = ldg4(q4 + lane);
+            if (h1) a1[u] = ldg4(q4 + lane + 32);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kAndIlp; ++u) {
+          if (i0 + u < m) {                      // warp-uniform
+            const uint4 r0 = and4(a0[u], m0), r1 = and4(a1[u], m1);
+            const int cnt = warp_sum(popc4(r0) + popc4(r1));
+            const int i = i0 + u;
+            if (lane == 0) {
+              cand_cnt[o.a + i] = cnt;
+              cand_p[o.a + i] = (int32_t)p;
+            }
+            if (cnt >= thr) {
+              if (n_surv == 0) {
+                pend0 = r0;
+                pend1 = r1;
+                pend_i = i;
+              } else {
+                if (n_surv == 1) {
+                  uint4* d = reinterpret_cast<uint4*>(arena_new + o.b + (int64_t)pend_i * w_new);
+                  if (h0) d[lane] = pend0;
+                  if (h1) d[lane + 32] = pend1;
+                }
+                uint4* d = reinterpret_cast<uint4*>(arena_new + o.b + (int64_t)i * w_new);
+                if (h0) d[lane] = r0;
+                if (h1) d[lane + 32] = r1;
+              }
+              ++n_surv;
+            }
+          }
+        }
+      }
+      continue;
+    }
+    // ---- bit-extract route ----
+    const int nv = w_old >> 2;
+    const uint4* msk4 = reinterpret_cast<const uint4*>(rowp);
+    for (int i0 = 0; i0 < m; i0 += kChunk) {
+      const int mc = min(kChunk, m - i0);
+      const int64_t my_src = lane < mc ? __ldg(rowptr_old + p + 1 + i0 + lane) : 0;
+      int acc[kChunk];
+      const uint4* rows[kChunk];
+#pragma unroll
+      for (int t = 0; t < kChunk; ++t) {
+        acc[t] = 0;
+        rows[t] = reinterpret_cast<const uint4*>(arena_old + __shfl_sync(0xffffffffu, my_src, t));
+      }
+      for (int v = lane; v < nv; v += 32) {
+        const uint4 mw = ldg4(msk4 + v);
+#pragma unroll
+        for (int t = 0; t < kChunk; ++t)
+          if (t < mc) acc[t] += popc4(and4(ldg4(rows[t] + v), mw));
+      }
+      uint32_t surv = 0;
+#pragma unroll
+      for (int t = 0; t < kChunk; ++t) {
+        if (t < mc) {
+          const int cnt = warp_sum(acc[t]);
+          if (lane == 0) {
+            cand_cnt[o.a + i0 + t] = cnt;
+            cand_p[o.a + i0 + t] = (int32_t)p;
+          }
+          if (cnt >= thr) surv |= 1u << t;
+        }
+      }
+      if (surv == 0) continue;
+      const int ns = __popc(surv);
+      __syncwarp();
+      if (lane < mc && ((surv >> lane) & 1u)) {
+        const int slot = __popc(surv & ((1u << lane) - 1u));
+        s_src[warp][slot] = my_src;
+        s_dst[warp][slot] = o.b + (int64_t)(i0 + lane) * w_new;
+      }
+      for (int i = lane; i < ns * 36; i += 32) sbuf[warp][i / 36][i % 36] = 0;
+      __syncwarp();
+      int base = 0;                            // bits emitted so far (the same for every row)
+      for (int blk = 0; blk < w_old; blk += 32) {
+        const int w = blk + lane;
+        const uint32_t mw = w < w_old ? __ldg(rowp + w) : 0u;
+        uint32_t xs[kChunk];
+#pragma unroll
+        for (int t = 0; t < kChunk; ++t)
+          xs[t] = (t < ns && w < w_old) ? __ldg(arena_old + s_src[warp][t] + w) : 0u;
+        const int nb = __popc(mw);
+        int incl = nb;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int u = __shfl_up_sync(0xffffffffu, incl, d);
+          if (lane >= d) incl += u;
+        }
+        const int tot = __shfl_sync(0xffffffffu, incl, 31);
+        if (nb) {
+          uint32_t mv[5];
+          uint32_t mm = mw, mk = ~mw << 1;
+#pragma unroll
+          for (int i = 0; i < 5; ++i) {
+            uint32_t mp = mk ^ (mk << 1);
+            mp ^= mp << 2;
+            mp ^= mp << 4;
+            mp ^= mp << 8;
+            mp ^= mp << 16;
+            mv[i] = mp & mm;
+            mm = (mm ^ mv[i]) | (mv[i] >> (1 << i));
+            mk &= ~mp;
+          }
+          const int bitpos = (base & 31) + incl - nb;
+          const int word = bitpos >> 5, sh = bitpos & 31;
+#pragma unroll
+          for (int t = 0; t < kChunk; ++t) {
+            if (t < ns) {
+              uint32_t x = xs[t] & mw;
+#pragma unroll
+              for (int i = 0; i < 5; ++i) {
+                const uint32_t tt = x & mv[i];
+                x = (x ^ tt) | (tt >> (1 << i));
+              }
+              if (x) {
+                uint32_t* buf = sbuf[warp][t];
+                atomicOr(buf + word, x << sh);
+                if (sh + nb > 32) atomicOr(buf + word + 1, x >> (32 - sh));
+              }
+            }
+          }
+        }
+        __syncwarp();
+        const int nbits = (base & 31) + tot, full = nbits >> 5, w0 = base >> 5;
+        for (int t = 0; t < ns; ++t) {
+          uint32_t* buf = sbuf[warp][t];
+          uint32_t* dst = arena_new + s_dst[warp][t];
+          const uint32_t v0 = buf[lane], v1 = lane < 4 ? buf[32 + lane] : 0u;
+          const uint32_t partial = buf[full];
+          __syncwarp();
+          if (lane < full && w0 + lane < w_new) dst[w0 + lane] = v0;
+          if (lane < 4 && 32 + lane < full && w0 + 32 + lane < w_new) dst[w0 + 32 + lane] = v1;
+          buf[lane] = lane == 0 ? partial : 0u;
+          if (lane < 4) buf[32 + lane] = 0u;
+        }
+        __syncwarp();
+        base += tot;
+      }
+      for (int t = 0; t < ns; ++t) {
+        uint32_t* dst = arena_new + s_dst[warp][t];
+        int done = base >> 5;
+        if ((base & 31) && lane == 0 && done < w_new) dst[done] = sbuf[warp][t][0];
+        if (base & 31) ++done;
+        for (int i = done + lane; i < w_new; i += 32) dst[i] = 0u;
+      }
+      __syncwarp();
+    }
+  }
+}
+
+struct GeThr {
+  int32_t thr;
+  __host__ __device__ int64_t operator()(int32_t c) const { return c >= thr ? 1 : 0; }
+};
+
+__global__ void k_scan_total_post(const int32_t* cnt, int64_t n, int32_t thr, int64_t* off,
+                                  volatile int64_t* box) {
+  const int64_t t = n > 0 ? off[n - 1] + (cnt[n - 1] >= thr ? 1 : 0) : 0;
+  off[n] = t;
+  box[0] = t;
+  __threadfence_system();
+}
+
+// New level table from the survivors (order preserved, so the table stays sorted): members,
+// count, parent, and the conditional row = the slot k_count_project filled. A survivor
+// whose parent has no other survivor gets width 0: it has no sibling to be joined with.
+__global__ void __launch_bounds__(256)
+k_emit_rows(const int32_t* __restrict__ items, int k, const int32_t* __restrict__ cand_p,
+            const int32_t* __restrict__ cand_cnt, int64_t n_cand, int32_t thr,
+            const int64_t* __restrict__ out_off, const I2* __restrict__ off2,
+            const int32_t* __restrict__ wnew, int32_t* __restrict__ out_items,
+            int32_t* __restrict__ out_counts, int32_t* __restrict__ out_par,
+            int64_t* __restrict__ out_rowptr, int32_t* __restrict__ out_roww) {
+  for (int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; c < n_cand; c += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t cnt = cand_cnt[c];
+    if (cnt < thr) continue;
+    const int64_t o = out_off[c];
+    const int32_t p = cand_p[c];
+    const I2 b = off2[p], e = off2[p + 1];
+    const int64_t i = c - b.a;
+    const int64_t q = (int64_t)p + 1 + i;
+    const int32_t* ip = items + (int64_t)p * k;
+    int32_t* op = out_items + o * (k + 1);
+    for (int t = 0; t < k; ++t) op[t] = __ldg(ip + t);
+    op[k] = __ldg(items + q * k + (k - 1));
+    out_counts[o] = cnt;
+    out_par[o] = p;
+    const int32_t w = __ldg(wnew + p);
+    const int64_t survivors = out_off[e.a] - out_off[b.a];
+    out_rowptr[o] = b.b + i * w;
+    out_roww[o] = survivors >= 2 ? w : 0;
+  }
+}
+
+// ---- host side -----------------------------------------------------------------------------
+struct Miner {
+  Workspace ws;
+  cudaStream_t s;
+  volatile int64_t* box;
+  int64_t launches = 0;
+  const char* stage = "start";
+  Miner(void* base, size_t bytes, cudaStream_t stream) : ws(base, bytes), s(stream), box(mailbox()) {}
+
+  template <class T>
+  int take(T** out, int64_t n, bool high = true) {
+    *out = (T*)ws.alloc(sizeof(T) * (size_t)std::max<int64_t>(n, 1), high);
+    if (*out == nullptr)
+      return fail(kCapacityError,
+                  "kmls_mine: workspace too small at %s: %zu more bytes needed while %zu are in use "
+                  "(call again with a larger workspace; nothing was truncated)",
+                  stage, ws.failed_bytes, ws.in_use);
+    return 0;
+  }
+  int sync() {
+    KMLS_CUDA(cudaStreamSynchronize(s));
+    return 0;
+  }
+};
+
+#define KMLS_TRY(expr)        \
+  do {                        \
+    int rc_ = (expr);         \
+    if (rc_) return rc_;      \
+  } while (0)
+
+static inline int grid_for(int64_t n, int per_block, int max_per_sm) {
+  return (int)std::max<int64_t>(1, std::min<int64_t>((n + per_block - 1) / per_block, (int64_t)num_sms() * max_per_sm));
+}
+
+// frequent tracks: ids with key[id] >= thr, ordered by (key, id). Returns their number.
+static int select_and_order(Miner& M, const int32_t* d_key, int32_t n, int32_t thr, int32_t** d_ids_out,
+                            int32_t** d_keys_out, int32_t* n_out) {
+  int32_t *sel = nullptr, *keys = nullptr, *ids2 = nullptr, *keys2 = nullptr, *d_n = nullptr;
+  KMLS_TRY(M.take(&sel, n));
+  KMLS_TRY(M.take(&d_n, 2));
+  cub::CountingInputIterator<int32_t> idx(0);
+  size_t need = 0;
+  KMLS_CUDA(cub::DeviceSelect::If(nullptr, need, idx, sel, d_n, n, OccAtLeast{d_key, thr}, M.s));
+  void* tmp = nullptr;
+  KMLS_TRY(M.take((char**)&tmp, (int64_t)need));
+  KMLS_CUDA(cub::DeviceSelect::If(tmp, need, idx, sel, d_n, n, OccAtLeast{d_key, thr}, M.s));
+  M.launches += 2;
+  k_post<<<1, 1, 0, M.s>>>(nullptr, nullptr, d_n, nullptr, M.box);
+  KMLS_LAUNCHED("k_post");
+  KMLS_TRY(M.sync());
+  M.ws.release(tmp);
+  const int32_t m = (int32_t)M.box[2];
+  *n_out = m;
+  *d_ids_out = *d_keys_out = nullptr;
+  if (m > 0) {
+    KMLS_TRY(M.take(&keys, m));
+    KMLS_TRY(M.take(&ids2, m, false));
+    KMLS_TRY(M.take(&keys2, m));
+    k_gather_i32<<<grid_for(m, 256, 8), 256, 0, M.s>>>(d_key, sel, m, keys);
+    KMLS_LAUNCHED("k_gather_i32");
+    need = 0;
+    KMLS_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, need, keys, keys2, sel, ids2, m, 0, 32, M.s));
+    KMLS_TRY(M.take((char**)&tmp, (int64_t)need));
+    KMLS_CUDA(cub::DeviceRadixSort::SortPairs(tmp, need, keys, keys2, sel, ids2, m, 0, 32, M.s));   // stable
+    M.launches += 8;
+    M.ws.release(tmp);
+    M.ws.release(keys);
+    *d_ids_out = ids2;
+    *d_keys_out = keys2;
+  }
+  M.ws.release(sel);
+  M.ws.release(d_n);
+  return 0;
+}
+
+}  // namespace kmls
+
+using namespace kmls;
+
+extern "C" int kmls_thresholds(double min_support, int64_t n, int64_t* t1, int64_t* tk) {
+  KMLS_REQUIRE(t1 && tk && n >= 0, "kmls_thresholds: bad arguments");
+  KMLS_REQUIRE(min_support > 0.0,
+               "`min_support` must be a positive number within the interval `(0, 1]`. Got %g.", min_support);
+  const double prod = min_support * (double)n;
+  const int64_t k = (int64_t)std::ceil(prod);
+  *tk = k;
+  if (n == 0) {
+    *t1 = 0;
+    return 0;
+  }
+  int64_t c = std::max<int64_t>(0, std::min<int64_t>(n + 1, k));
+  while (c > 0 && (double)(c - 1) / (double)n >= min_support) --c;
+  while (c <= n && !((double)c / (double)n >= min_support)) ++c;
+  *t1 = c;
+  return 0;
+}
+
+extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64_t n_playlists,
+                         int32_t n_items, int64_t n_total, int32_t t1, int32_t tk,
+                         const kmls_mine_options* opt_in, void* d_workspace, size_t workspace_bytes,
+                         kmls_mine_result* R, kmls_stream_t stream) {
+  KMLS_REQUIRE(R != nullptr, "kmls_mine: result is null");
+  kmls_mine_options opt{};
+  if (opt_in) opt = *opt_in;
+  memset(R, 0, sizeof(*R));
+  for (int k = 0; k < KMLS_MAX_LEVELS + 2; ++k)
+    R->items_off[k] = R->counts_off[k] = R->parent_off[k] = R->h_items_off[k] = R->h_counts_off[k] = -1;
+  R->row_items_off = R->occurrences_off = R->pair_off = R->h_row_items_off = -1;
+  R->n_playlists_total = n_total;
+  R->t1 = t1;
+  R->tk = R->thr_k = tk;
+  KMLS_REQUIRE(n_playlists >= 0 && n_items >= 0 && n_total >= n_playlists && t1 >= 0 && tk >= 0,
+               "kmls_mine: bad sizes or thresholds");
+  const int keep_words = opt.keep_words > 0 ? opt.keep_words : kKeepWordsMax;
+  KMLS_REQUIRE(keep_words <= kKeepWordsMax && (keep_words & 3) == 0, "kmls_mine: keep_words must be a multiple of 4, at most 256");
+  KMLS_REQUIRE(opt.n_parts <= 1 || (opt.part >= 0 && opt.part < opt.n_parts && opt.part_block >= 1),
+               "kmls_mine: bad class partition");
+  const int64_t max_itemsets = opt.max_itemsets > 0 ? opt.max_itemsets : 200000000;
+  const int max_len = opt.max_len > 0 ? opt.max_len : KMLS_MAX_LEVELS;
+  if (n_total == 0 || n_items == 0 || n_playlists == 0) return 0;
+  KMLS_REQUIRE(d_offsets && d_items, "kmls_mine: null input");
+  KMLS_REQUIRE(d_workspace && ((uintptr_t)d_workspace & 255) == 0, "kmls_mine: workspace must be 256-byte aligned device memory");
+  cudaStream_t s = (cudaStream_t)stream;
+  Miner M(d_workspace, workspace_bytes, s);
+  KMLS_REQUIRE(M.box != nullptr, "kmls_mine: cannot allocate the pinned mailbox");
+  char* const ws_base = (char*)d_workspace;
+  auto off_of = [&](const void* p) { return (int64_t)((const char*)p - ws_base); };
+
+  // host-side copies of the tables (optional), on a side stream
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev = nullptr;
+  size_t h_used = 0;
+  struct SideGuard {
+    cudaStream_t& st;
+    cudaEvent_t& e;
+    ~SideGuard() {
+      if (e) cudaEventDestroy(e);
+      if (st) cudaStreamDestroy(st);
+    }
+  } side_guard{side, ev};
+  if (opt.h_tables) {
+    KMLS_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+    KMLS_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  }
+  auto to_host = [&](const void* d_src, size_t bytes, int64_t* h_off) -> int {
+    if (!opt.h_tables) return 0;
+    const size_t at = (h_used + 255) / 256 * 256;
+    if (at + bytes > opt.h_tables_bytes)
+      return fail(kCapacityError, "kmls_mine: h_tables too small (%zu bytes needed so far, %zu given)",
+                  at + bytes, opt.h_tables_bytes);
+    KMLS_CUDA(cudaEventRecord(ev, s));
+    KMLS_CUDA(cudaStreamWaitEvent(side, ev, 0));
+    // in pieces: a later small transfer is never stuck behind one long copy
+    const size_t piece = (size_t)4 << 20;
+    for (size_t a = 0; a < bytes; a += piece)
+      KMLS_CUDA(cudaMemcpyAsync((char*)opt.h_tables + at + a, (const char*)d_src + a, std::min(piece, bytes - a),
+                                cudaMemcpyDeviceToHost, side));
+    *h_off = (int64_t)at;
+    h_used = at + bytes;
+    return 0;
+  };
+
+  // ---------------------------------------------------------------- level 1
+  M.stage = "level 1";
+  int32_t* occ = nullptr;
+  KMLS_TRY(M.take(&occ, n_items, false));
+  R->occurrences_off = off_of(occ);
+  // nnz from the offsets' last entry
+  k_post<<<1, 1, 0, s>>>(d_offsets + n_playlists, nullptr, nullptr, nullptr, M.box);
+  KMLS_LAUNCHED("k_post");
+  KMLS_TRY(M.sync());
+  const int64_t nnz = M.box[0];
+  KMLS_REQUIRE(nnz >= 0, "kmls_mine: offsets are not ascending");
+  KMLS_TRY(kmls_item_histogram(d_items, nnz, n_items, occ, s));
+  ++M.launches;
+  const int32_t thr1 = std::max(t1, 1);
+  int32_t *cand = nullptr, *keys = nullptr, n_rows = 0;
+  KMLS_TRY(select_and_order(M, occ, n_items, thr1, &cand, &keys, &n_rows));
+  if (n_rows == 0) {
+    R->workspace_peak_bytes = M.ws.peak;
+    R->kernel_launches = M.launches;
+    return 0;
+  }
+  const int64_t row_words = kmls_bitmap_row_words(n_playlists);
+  int32_t* row_of_item = nullptr;
+  uint32_t* bitmap = nullptr;
+  int32_t *counts1 = nullptr, *flags = nullptr;
+  KMLS_TRY(M.take(&row_of_item, n_items));
+  KMLS_TRY(M.take(&bitmap, (int64_t)n_rows * row_words));
+  KMLS_TRY(M.take(&counts1, n_rows, false));
+  KMLS_TRY(M.take(&flags, 8));
+  KMLS_CUDA(cudaMemsetAsync(flags, 0, 8 * sizeof(int32_t), s));
+  k_fill_i32<<<grid_for(n_items, 256, 8), 256, 0, s>>>(row_of_item, n_items, -1);
+  KMLS_LAUNCHED("k_fill_i32");
+  k_number_rows<<<grid_for(n_rows, 256, 8), 256, 0, s>>>(cand, n_rows, row_of_item, nullptr);
+  KMLS_LAUNCHED("k_number_rows");
+  KMLS_TRY(kmls_encode_bitmap(d_offsets, d_items, n_playlists, row_of_item, n_items, n_rows, bitmap, row_words, s));
+  KMLS_TRY(kmls_row_popcount(bitmap, n_rows, row_words, counts1, s));
+  k_check_counts<<<grid_for(n_rows, 256, 4), 256, 0, s>>>(counts1, keys, n_rows, flags);
+  KMLS_LAUNCHED("k_check_counts");
+  k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), nullptr, flags, nullptr, M.box);
+  KMLS_LAUNCHED("k_post");
+  M.launches += 6;
+  KMLS_TRY(M.sync());
+  int64_t sum_counts = M.box[0];
+  if (M.box[2] != 0) {
+    // some playlist repeats a track: exact supports are below the occurrence
+    // counts, so drop the rows that fell under T1 and restore ascending-support order
+    int32_t *src = nullptr, *keys2 = nullptr, n_keep = 0;
+    KMLS_TRY(select_and_order(M, counts1, n_rows, thr1, &src, &keys2, &n_keep));
+    if (n_keep == 0) {
+      R->workspace_peak_bytes = M.ws.peak;
+      R->kernel_launches = M.launches;
+      return 0;
+    }
+    uint32_t* bitmap2 = nullptr;
+    int32_t* cand2 = nullptr;
+    KMLS_TRY(M.take(&bitmap2, (int64_t)n_keep * row_words));
+    KMLS_TRY(M.take(&cand2, n_keep, false));
+    KMLS_TRY(kmls_gather_rows(bitmap, src, n_keep, row_words, bitmap2, s));
+    k_gather_i32<<<grid_for(n_keep, 256, 8), 256, 0, s>>>(cand, src, n_keep, cand2);
+    KMLS_LAUNCHED("k_gather_i32");
+    KMLS_CUDA(cudaMemcpyAsync(counts1, keys2, sizeof(int32_t) * (size_t)n_keep, cudaMemcpyDeviceToDevice, s));
+    KMLS_CUDA(cudaMemsetAsync(flags, 0, 8 * sizeof(int32_t), s));
+    k_check_counts<<<grid_for(n_keep, 256, 4), 256, 0, s>>>(counts1, keys2, n_keep, flags);
+    KMLS_LAUNCHED("k_check_counts");
+    k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), nullptr, nullptr, nullptr, M.box);
+    KMLS_LAUNCHED("k_post");
+    KMLS_TRY(M.sync());
+    sum_counts = M.box[0];
+    M.launches += 5;
+    M.ws.release(bitmap);
+    M.ws.release(cand);
+    M.ws.release(src);
+    M.ws.release(keys2);
+    bitmap = bitmap2;
+    cand = cand2;
+    n_rows = n_keep;
+    k_fill_i32<<<grid_for(n_items, 256, 8), 256, 0, s>>>(row_of_item, n_items, -1);
+    KMLS_LAUNCHED("k_fill_i32");
+    k_number_rows<<<grid_for(n_rows, 256, 8), 256, 0, s>>>(cand, n_rows, row_of_item, nullptr);
+    KMLS_LAUNCHED("k_number_rows");
+    M.launches += 2;
+  }
+  M.ws.release(keys);
+  int32_t* items1 = nullptr;
+  KMLS_TRY(M.take(&items1, n_rows, false));
+  k_number_rows<<<grid_for(n_rows, 256, 8), 256, 0, s>>>(cand, n_rows, row_of_item, items1);
+  KMLS_LAUNCHED("k_number_rows");
+  ++M.launches;
+  R->n_rows = n_rows;
+  R->row_items_off = off_of(cand);
+  R->max_k = 1;
+  R->level_size[1] = n_rows;
+  R->level_candidates[1] = n_items;
+  R->items_off[1] = off_of(items1);
+  R->counts_off[1] = off_of(counts1);
+  R->n_itemsets = n_rows;
+  KMLS_TRY(to_host(cand, sizeof(int32_t) * (size_t)n_rows, &R->h_row_items_off));
+  KMLS_TRY(to_host(items1, sizeof(int32_t) * (size_t)n_rows, &R->h_items_off[1]));
+  KMLS_TRY(to_host(counts1, sizeof(int32_t) * (size_t)n_rows, &R->h_counts_off[1]));
+
+  auto finish = [&]() -> int {
+    if (opt.h_tables) {
+      KMLS_CUDA(cudaStreamSynchronize(side));
+      R->h_bytes = (int64_t)h_used;
+    }
+    KMLS_CUDA(cudaStreamSynchronize(s));
+    R->workspace_peak_bytes = M.ws.peak;
+    R->kernel_launches = M.launches;
+    return 0;
+  };
+  if (n_rows < 2 || max_len <= 1) return finish();
+
+  // ---------------------------------------------------------------- level 2
+  M.stage = "level 2";
+  int32_t* pair = nullptr;
+  KMLS_TRY(M.take(&pair, (int64_t)n_rows * n_rows, false));
+  R->pair_off = off_of(pair);
+  int impl = opt.pair_impl;
+  const bool big = n_rows >= 256 && row_words >= 512;
+  if (impl == 0) {
+    // tensor cores once there are enough tiles and playlists to feed them, unless the
+    // one-hot matrix is so sparse that counting each playlist's pairs is cheaper: about
+    // 0.65 m^2 counter updates per playlist (m = mean kept tracks) at ~2e11 updates/s,
+    // against F(F+1)N int8 operations at ~2.2e15/s
+    impl = big ? 3 : 2;
+    if (big && n_rows <= 16384) {
+      const double m_mean = (double)sum_counts / (double)n_playlists;
+      if (0.65 * m_mean * m_mean * (double)n_playlists / 2.0e11 <
+          (double)n_rows * (n_rows + 1.0) * (double)n_playlists / 2.2e15)
+        impl = 1;
+    }
+  }
+  if (impl == 1) {
+    KMLS_TRY(kmls_pair_counts_csr(d_offsets, d_items, n_playlists, row_of_item, n_rows, pair, flags + 4, s));
+    k_post<<<1, 1, 0, s>>>(nullptr, nullptr, flags + 4, nullptr, M.box);
+    KMLS_LAUNCHED("k_post");
+    M.launches += 2;
+    KMLS_TRY(M.sync());
+    if (M.box[2] != 0) impl = big ? 3 : 2;   // a playlist with more than 1024 kept tracks
+  }
+  if (impl == 2) {
+    KMLS_TRY(kmls_pair_counts(bitmap, n_rows, row_words, pair, s));
+    ++M.launches;
+  } else if (impl == 3) {
+    const size_t gbytes = kmls_pair_gemm_scratch_bytes(n_rows, row_words);
+    char* gscratch = nullptr;
+    KMLS_TRY(M.take(&gscratch, (int64_t)gbytes));
+    KMLS_TRY(kmls_pair_counts_i8(bitmap, n_rows, row_words, pair, gscratch, gbytes, s));
+    M.launches += 2;
+    M.ws.release(gscratch);
+  } else if (impl != 1) {
+    return fail(kArgError, "kmls_mine: unknown pair_impl %d", impl);
+  }
+  R->pair_impl_used = impl;
+  M.ws.release(row_of_item);
+  int32_t thr = tk;
+  if (t1 < tk) {
+    KMLS_CUDA(cudaMemsetAsync(flags, 0, sizeof(int32_t), s));
+    k_nested_check<<<grid_for((int64_t)n_rows * n_rows, 256, 8), 256, 0, s>>>(pair, counts1, n_rows, flags);
+    KMLS_LAUNCHED("k_nested_check");
+    k_post<<<1, 1, 0, s>>>(nullptr, nullptr, flags, nullptr, M.box);
+    KMLS_LAUNCHED("k_post");
+    M.launches += 2;
+    KMLS_TRY(M.sync());
+    if (M.box[2] == 0) thr = t1;
+  }
+  R->thr_k = thr;
+  int64_t* row_off = nullptr;
+  KMLS_TRY(M.take(&row_off, n_rows + 1));
+  KMLS_TRY(kmls_pair_select(pair, n_rows, thr, 0, row_off, nullptr, nullptr, s));
+  k_post<<<1, 1, 0, s>>>(row_off + n_rows, nullptr, nullptr, nullptr, M.box);
+  KMLS_LAUNCHED("k_post");
+  M.launches += 3;
+  KMLS_TRY(M.sync());
+  const int64_t n2 = M.box[0];
+  R->level_candidates[2] = (int64_t)n_rows * (n_rows - 1) / 2;
+  if (n2 == 0) return finish();
+  KMLS_REQUIRE(n2 <= 0x7fffffff, "kmls_mine: more than 2^31-1 frequent pairs");
+  int32_t *items_k = nullptr, *counts_k = nullptr, *par_k = nullptr, *second2 = nullptr;
+  KMLS_TRY(M.take(&items_k, n2 * 2, false));
+  KMLS_TRY(M.take(&counts_k, n2, false));
+  KMLS_TRY(M.take(&par_k, n2, false));
+  KMLS_TRY(M.take(&second2, n2));
+  KMLS_TRY(kmls_pair_select(pair, n_rows, thr, n2, row_off, items_k, counts_k, s));
+  k_pair_parents<<<grid_for(n2, 256, 8), 256, 0, s>>>(items_k, n2, par_k, second2);
+  KMLS_LAUNCHED("k_pair_parents");
+  M.launches += 4;
+  M.ws.release(row_off);
+  R->max_k = 2;
+  R->level_size[2] = n2;
+  R->items_off[2] = off_of(items_k);
+  R->counts_off[2] = off_of(counts_k);
+  R->parent_off[2] = off_of(par_k);
+  R->n_itemsets += n2;
+  KMLS_TRY(to_host(items_k, sizeof(int32_t) * 2 * (size_t)n2, &R->h_items_off[2]));
+  KMLS_TRY(to_host(counts_k, sizeof(int32_t) * (size_t)n2, &R->h_counts_off[2]));
+  if (n2 < 2 || max_len <= 2) return finish();
+
+  // conditional rows of the pairs: row(a, b) = row_b sampled at the playlists of a
+  int64_t n_k = n2;
+  uint32_t* arena_k = nullptr;
+  int64_t* rowptr_k = nullptr;
+  int32_t* roww_k = nullptr;
+  {
+    size_t sbytes = kmls_scan_scratch_bytes(std::max<int64_t>(n2, n_rows));
+    char* scratch = nullptr;
+    int64_t* tid_off = nullptr;
+    int32_t* tids = nullptr;
+    KMLS_TRY(M.take(&roww_k, n2));
+    KMLS_TRY(M.take(&rowptr_k, n2 + 1));
+    KMLS_TRY(M.take(&scratch, (int64_t)sbytes));
+    KMLS_TRY(M.take(&tid_off, n_rows + 1));
+    KMLS_TRY(kmls_row_alloc(par_k, n2, counts1, nullptr, keep_words, roww_k, s));
+    KMLS_TRY(kmls_exclusive_scan_i32(roww_k, n2, rowptr_k, scratch, sbytes, s));
+    KMLS_TRY(kmls_exclusive_scan_i32(counts1, n_rows, tid_off, scratch, sbytes, s));
+    k_post<<<1, 1, 0, s>>>(rowptr_k + n2, tid_off + n_rows, nullptr, nullptr, M.box);
+    KMLS_LAUNCHED("k_post");
+    M.launches += 8;
+    KMLS_TRY(M.sync());
+    const int64_t words = M.box[0], n_tids = M.box[1];
+    R->level_row_words[2] = words;
+    KMLS_TRY(M.take(&arena_k, words));
+    KMLS_TRY(M.take(&tids, n_tids));
+    KMLS_TRY(kmls_row_tidlists(bitmap, n_rows, row_words, tid_off, tids, s));
+    KMLS_TRY(kmls_project_rows_gather(bitmap, row_words, par_k, second2, n2, tids, tid_off, arena_k, rowptr_k,
+                                      words, s));
+    M.launches += 2;
+    M.ws.release(tids);
+    M.ws.release(tid_off);
+    M.ws.release(scratch);
+  }
+  M.ws.release(second2);
+  M.ws.release(bitmap);
+  bitmap = nullptr;
+
+  // ---------------------------------------------------------------- levels k >= 3
+  int k = 2;
+  int64_t total = R->n_itemsets;
+  while (k < max_len && n_k >= 2) {
+    M.stage = "levels >= 3";
+    KMLS_REQUIRE(k + 1 <= KMLS_MAX_LEVELS, "kmls_mine: itemsets longer than %d members", KMLS_MAX_LEVELS);
+    KMLS_REQUIRE(n_k <= 0x7fffffff, "kmls_mine: more than 2^31-1 itemsets at level %d", k);
+    int32_t *ncand = nullptr, *wnew = nullptr;
+    I2* off2 = nullptr;
+    KMLS_TRY(M.take(&ncand, n_k));
+    KMLS_TRY(M.take(&wnew, n_k));
+    KMLS_TRY(M.take(&off2, n_k + 1));
+    const bool parted = k == 2 && opt.n_parts > 1;
+    k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words,
+                                                       parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
+                                                       ncand, wnew);
+    KMLS_LAUNCHED("k_join_size");
+    {
+      cub::CountingInputIterator<int64_t> idx(0);
+      cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(idx, CandSlots{ncand, wnew});
+      size_t need = 0;
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
+      char* tmp = nullptr;
+      KMLS_TRY(M.take(&tmp, (int64_t)need));
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
+      M.ws.release(tmp);
+    }
+    k_i2_total<<<1, 1, 0, s>>>(ncand, wnew, n_k, off2, M.box);
+    KMLS_LAUNCHED("k_i2_total");
+    M.launches += 4;
+    KMLS_TRY(M.sync());
+    const int64_t n_cand = M.box[0], slot_words = M.box[1];
+    R->level_candidates[k + 1] = n_cand;
+    if (n_cand == 0) break;
+    if (total + n_cand > max_itemsets * 4)
+      return fail(kCapacityError, "kmls_mine: level %d: %lld candidates exceed the max_itemsets guard", k + 1,
+                  (long long)n_cand);
+    KMLS_REQUIRE(n_cand <= 0x7fffffff, "kmls_mine: more than 2^31-1 candidates at level %d", k + 1);
+    uint32_t* arena_n = nullptr;
+    int32_t *cand_cnt = nullptr, *cand_p = nullptr;
+    int64_t* out_off = nullptr;
+    KMLS_TRY(M.take(&arena_n, slot_words));
+    KMLS_TRY(M.take(&cand_cnt, n_cand));
+    KMLS_TRY(M.take(&cand_p, n_cand));
+    KMLS_TRY(M.take(&out_off, n_cand + 1));
+    k_count_project<<<grid_for(n_k, 8, 64), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, n_k, thr,
+                                                         keep_words, arena_n, cand_cnt, cand_p);
+    KMLS_LAUNCHED("k_count_project");
+    {
+      cub::TransformInputIterator<int64_t, GeThr, const int32_t*> it(cand_cnt, GeThr{thr});
+      size_t need = 0;
+      KMLS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, it, out_off, (int)n_cand, s));
+      char* tmp = nullptr;
+      KMLS_TRY(M.take(&tmp, (int64_t)need));
+      KMLS_CUDA(cub::DeviceScan::ExclusiveSum(tmp, need, it, out_off, (int)n_cand, s));
+      M.ws.release(tmp);
+    }
+    k_scan_total_post<<<1, 1, 0, s>>>(cand_cnt, n_cand, thr, out_off, M.box);
+    KMLS_LAUNCHED("k_scan_total_post");
+    M.launches += 4;
+    KMLS_TRY(M.sync());
+    const int64_t n_next = M.box[0];
+    if (n_next == 0) break;
+    total += n_next;
+    if (total > max_itemsets)
+      return fail(kCapacityError,
+                  "kmls_mine: more than max_itemsets=%lld frequent itemsets at level %d; raise the guard or "
+                  "min_support (results are never truncated)", (long long)max_itemsets, k + 1);
+    int32_t *items_n = nullptr, *counts_n = nullptr, *par_n = nullptr, *roww_n = nullptr;
+    int64_t* rowptr_n = nullptr;
+    KMLS_TRY(M.take(&items_n, n_next * (k + 1), false));
+    KMLS_TRY(M.take(&counts_n, n_next, false));
+    KMLS_TRY(M.take(&par_n, n_next, false));
+    KMLS_TRY(M.take(&rowptr_n, n_next));
+    KMLS_TRY(M.take(&roww_n, n_next));
+    k_emit_rows<<<grid_for(n_cand, 256, 16), 256, 0, s>>>(items_k, k, cand_p, cand_cnt, n_cand, thr, out_off, off2,
+                                                          wnew, items_n, counts_n, par_n, rowptr_n, roww_n);
+    KMLS_LAUNCHED("k_emit_rows");
+    ++M.launches;
+    // this level's scratch and the previous level's rows are done with (stream order)
+    M.ws.release(ncand);
+    M.ws.release(wnew);
+    M.ws.release(off2);
+    M.ws.release(cand_cnt);
+    M.ws.release(cand_p);
+    M.ws.release(out_off);
+    M.ws.release(arena_k);
+    M.ws.release(rowptr_k);
+    M.ws.release(roww_k);
+    ncand = wnew = cand_cnt = cand_p = nullptr;
+    arena_k = arena_n;
+    rowptr_k = rowptr_n;
+    roww_k = roww_n;
+    items_k = items_n;
+    counts_k = counts_n;
+    par_k = par_n;
+    n_k = n_next;
+    ++k;
+    R->max_k = k;
+    R->level_size[k] = n_k;
+    R->level_row_words[k] = slot_words;
+    R->items_off[k] = off_of(items_k);
+    R->counts_off[k] = off_of(counts_k);
+    R->parent_off[k] = off_of(par_k);
+    R->n_itemsets = total;
+    KMLS_TRY(to_host(items_k, sizeof(int32_t) * (size_t)k * (size_t)n_k, &R->h_items_off[k]));
+    KMLS_TRY(to_host(counts_k, sizeof(int32_t) * (size_t)n_k, &R->h_counts_off[k]));
+  }
+  return finish();
+}

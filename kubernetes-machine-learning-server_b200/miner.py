@@ -63,6 +63,9 @@ class MineResult:
     stats: Optional[dict] = None
     # parents[k-2][i] = index, in level k-1, of level-k itemset i without its last member
     parents: Optional[List[torch.Tensor]] = None
+    workspace: Optional[object] = None      # keeps the native path's device memory alive
+    occurrences: Optional[torch.Tensor] = None
+    host_layout: Optional[dict] = None
 
     @property
     def n_itemsets(self) -> int:
@@ -252,13 +255,131 @@ def prepare(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppor
                     pair, pair_local)
 
 
+class Workspace:
+    """Device memory handed to the one-call entry points (kmls_mine, kmls_rules): one torch
+    uint8 tensor that grows on demand. The tables a call returns are VIEWS of this memory:
+    they stay valid until the same Workspace is passed to another call."""
+
+    def __init__(self, device, nbytes: int = 0):
+        self.device = device
+        self.buf = None
+        if nbytes:
+            self.ensure(nbytes)
+
+    @property
+    def nbytes(self) -> int:
+        return 0 if self.buf is None else int(self.buf.numel())
+
+    def ensure(self, nbytes: int):
+        if self.nbytes < nbytes:
+            self.buf = None                       # release first: the two need not coexist
+            self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+        return self.buf
+
+    def grow(self):
+        """Double (bounded by what the device can still give); False when that is no growth."""
+        free = torch.cuda.mem_get_info(self.device)[0] + torch.cuda.memory_reserved(self.device) \
+            - torch.cuda.memory_allocated(self.device)
+        have = self.nbytes
+        want = min(max(2 * have, 1 << 30), int(0.92 * (free + have)))
+        if want <= have:
+            return False
+        self.ensure(want)
+        return True
+
+    def view(self, byte_off: int, n: int, dtype) -> torch.Tensor:
+        size = torch.empty(0, dtype=dtype).element_size()
+        return self.buf[byte_off:byte_off + n * size].view(dtype)
+
+
+_PAIR_IMPL = {"auto": 0, "csr": 1, "popc": 2, "i8": 3}
+
+
+def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
+                n_playlists_total: Optional[int] = None, max_len: Optional[int] = None,
+                max_itemsets: int = 200_000_000, keep_pair_counts: bool = False, pair_impl: str = "auto",
+                keep_words: Optional[int] = None, workspace: Optional[Workspace] = None,
+                part: Tuple[int, int] = (0, 1), part_block: int = 64,
+                host_tables: Optional[torch.Tensor] = None) -> MineResult:
+    """All levels through ONE call into the library (``kmls_mine``): the level loop, its
+    sizing and its buffers live in C++; this function only marshals. ``workspace``: device
+    memory for the call (a fresh one by default; the returned tables are views of it, so a
+    workspace that is reused invalidates earlier results). A workspace that turns out too small
+    is grown and the call repeated - the library never truncates. ``part = (i, n)``: mine only
+    the subtrees of the i-th of n interleaved blocks of ``part_block`` frequent pairs (levels 1
+    and 2 are always complete): the class partition of a multi-GPU job. ``host_tables``: a
+    pinned uint8 tensor the level tables are also streamed into while mining continues."""
+    if min_support <= 0.0:
+        thresholds(min_support, 1)  # raises the reference's ValueError
+    if not (offsets.is_cuda and items.is_cuda):
+        raise _lib.KmlsError("mine_native needs CUDA tensors: this path has no CPU fallback")
+    assert offsets.dtype == torch.int64 and items.dtype == torch.int32
+    device = offsets.device
+    n_local = int(offsets.numel()) - 1
+    n_total = n_local if n_playlists_total is None else int(n_playlists_total)
+    t1, tk = thresholds(min_support, n_total)
+    opt = _lib.MineOptions()
+    opt.max_len = int(max_len or 0)
+    opt.pair_impl = _PAIR_IMPL[pair_impl]
+    opt.keep_words = int(keep_words or 0)
+    opt.n_parts, opt.part, opt.part_block = int(part[1]), int(part[0]), int(part_block)
+    opt.max_itemsets = int(max_itemsets)
+    if host_tables is not None:
+        opt.h_tables, opt.h_tables_bytes = host_tables.data_ptr(), int(host_tables.numel())
+    ws = workspace if workspace is not None else Workspace(device)
+    if ws.nbytes == 0:
+        ws.ensure(max(1 << 30, 48 * int(items.numel())))
+    out = _lib.MineResultC()
+    while True:
+        rc, msg = _lib.call_rc("kmls_mine", offsets, items, n_local, int(n_items), n_total, t1, tk, opt,
+                               ws.buf, ws.nbytes, out, _stream())
+        _lib.CALLS["kmls_mine"] = _lib.CALLS.get("kmls_mine", 0) + 1
+        if rc == 0:
+            break
+        if rc == -2 and "workspace too small" in msg and ws.grow():
+            continue
+        raise _lib.KmlsError(f"kmls_mine failed with code {rc}: {msg}")
+    _lib.EXTRA_LAUNCHES += int(out.kernel_launches) - 1
+    stats = {"levels": [], "t1": t1, "tk": tk, "thr_k": int(out.thr_k), "n_playlists": n_total,
+             "nnz_local": int(items.numel()), "workspace_peak_bytes": int(out.workspace_peak_bytes),
+             "pair_impl": {v: k for k, v in _PAIR_IMPL.items()}.get(int(out.pair_impl_used)),
+             "h_bytes": int(out.h_bytes)}
+    e32 = torch.empty(0, dtype=torch.int32, device=device)
+    n_rows, max_k = int(out.n_rows), int(out.max_k)
+    levels, parents = [], []
+    for k in range(1, max_k + 1):
+        n = int(out.level_size[k])
+        levels.append((ws.view(int(out.items_off[k]), n * k, torch.int32).view(n, k),
+                       ws.view(int(out.counts_off[k]), n, torch.int32)))
+        if k >= 2:
+            parents.append(ws.view(int(out.parent_off[k]), n, torch.int32))
+        stats["levels"].append({"k": k, "candidates": int(out.level_candidates[k]), "frequent": n,
+                                "row_words_total": int(out.level_row_words[k])})
+    if max_k + 1 < _lib.KMLS_MAX_LEVELS and int(out.level_candidates[max_k + 1]):
+        stats["levels"].append({"k": max_k + 1, "candidates": int(out.level_candidates[max_k + 1]), "frequent": 0})
+    row_items = ws.view(int(out.row_items_off), n_rows, torch.int32) if n_rows else e32
+    pair = None
+    if keep_pair_counts and int(out.pair_off) >= 0:
+        pair = ws.view(int(out.pair_off), n_rows * n_rows, torch.int32).view(n_rows, n_rows)
+    res = MineResult(n_total, t1, tk, row_items, levels, pair, stats, parents)
+    res.workspace = ws
+    res.occurrences = ws.view(int(out.occurrences_off), int(n_items), torch.int32) \
+        if int(out.occurrences_off) >= 0 else None
+    res.host_layout = None
+    if host_tables is not None and n_rows:
+        res.host_layout = {"row_items": (int(out.h_row_items_off), n_rows),
+                           "levels": [(int(out.h_items_off[k]), int(out.h_counts_off[k]), int(out.level_size[k]))
+                                      for k in range(1, max_k + 1)]}
+    return res
+
+
 def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
              n_playlists_total: Optional[int] = None, group=None, max_len: Optional[int] = None,
              max_itemsets: int = 200_000_000, keep_pair_counts: bool = False,
              pair_impl: str = "auto", count_impl: str = "projected",
              prune: Optional[bool] = None, first_projection: str = "gather",
              keep_words: Optional[int] = None, prepared: Optional["Prepared"] = None,
-             on_level=None) -> MineResult:
+             on_level=None, impl: str = "auto", workspace: Optional["Workspace"] = None) -> MineResult:
     """Mine the playlists ``offsets[int64, n+1] / items[int32, nnz]`` (CUDA tensors, CSR by
     playlist, this rank's shard) for itemsets with the reference's thresholds.
 
@@ -270,6 +391,18 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     fingerprint set costs more than counting the few extra candidates - with members in
     ascending-support order the subsets a probe checks drop a RARER member and are almost
     always frequent). ``first_projection``: "gather" or "pext" for the level 1 -> 2 rows."""
+    native_ok = (group is None and prepared is None and on_level is None and count_impl == "projected"
+                 and not prune and first_projection == "gather"
+                 and (keep_words is None or (0 < keep_words <= 256 and keep_words % 4 == 0)))
+    if impl == "native" and not native_ok:
+        raise ValueError("impl='native' does not take group / prepared / on_level / fullwidth / prune")
+    if impl in ("auto", "native") and native_ok:
+        # the default: the whole level loop inside the library (kmls_mine)
+        import os
+        kw = keep_words if keep_words is not None else int(os.environ.get("KMLS_KEEP_WORDS", 0)) or None
+        return mine_native(offsets, items, n_items, min_support, n_playlists_total=n_playlists_total,
+                           max_len=max_len, max_itemsets=max_itemsets, keep_pair_counts=keep_pair_counts,
+                           pair_impl=pair_impl, keep_words=kw, workspace=workspace)
     if prune is None:
         prune = count_impl != "projected"
     if keep_words is None:
@@ -637,6 +770,16 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
                                  "sized for some itemset (the rule table would be corrupt)")
     return RuleTable(o_rule.view(n_rules, 2), o_conf, o_lift, arena_items, sizes.tolist(), arena_counts,
                      res.n_playlists)
+
+
+def itemset_checksum(res: MineResult) -> int:
+    """Order-independent checksum of the whole itemset table, computed on the device (same
+    arithmetic as ``oracle.fpgrowth_c.itemset_checksum``)."""
+    out = torch.zeros(1, dtype=torch.int64, device=res.row_items.device)
+    for k, (it, ct) in enumerate(res.levels, start=1):
+        if int(ct.numel()):
+            _lib.call("kmls_itemset_checksum", it, ct, int(ct.numel()), k, res.row_items, out, _stream())
+    return int(out.item()) & ((1 << 64) - 1)
 
 
 def rule_checksum(res: MineResult, rules: RuleTable) -> int:
