@@ -369,11 +369,49 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------ GPU arm
+def load_job_data(args, rank, world, barrier):
+    """(offsets, items, n_tracks, min_support, min_confidence, n_total, strong) of this rank.
+    partition "classes": every rank holds the job's WHOLE playlist set (the candidate space is
+    what is split); "playlists": a contiguous slice of it."""
+    name = args.workload
+    fixed = name in TOTAL_IS_FIXED
+    strong = fixed or args.scaling == "strong"
+    whole = args.partition == "classes" or world == 1
+    if fixed:
+        # generated in 8 shards; every rank first makes "its" shards (they land in the cache)
+        if 8 % world:
+            raise SystemExit(f"{name} is generated in 8 shards: --gpus must divide 8")
+        mine = range(rank * 8 // world, (rank + 1) * 8 // world)
+        off, items, n_tracks, s, conf = whole_job_data(name, mine)
+        if whole and world > 1:
+            barrier()
+            off, items, n_tracks, s, conf = whole_job_data(name)
+        return off, items, n_tracks, s, conf, WORKLOADS[name][0], True
+    if strong:
+        off, items, n_tracks, s, conf = make_data(name, shard=0)
+        n_total = len(off) - 1
+        if not whole:
+            off, items = rank_slice(off, items, rank, world)
+        return off, items, n_tracks, s, conf, n_total, True
+    # weak: the job is `world` generator shards
+    off, items, n_tracks, s, conf = make_data(name, shard=rank)
+    n_total = (len(off) - 1) * world
+    if whole and world > 1:
+        barrier()
+        offs, its = [np.zeros(1, np.int64)], []
+        for r in range(world):
+            o, i, _, _, _ = make_data(name, shard=r)
+            offs.append(o[1:] + offs[-1][-1])
+            its.append(i)
+        off, items = np.concatenate(offs), np.concatenate(its)
+    return off, items, n_tracks, s, conf, n_total, False
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
     import kmls_b200
-    from kmls_b200 import _lib, miner
+    from kmls_b200 import _lib, miner, multi
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -384,42 +422,39 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=device)
         group = dist.group.WORLD
-    name = args.workload
-    fixed = name in TOTAL_IS_FIXED
-    strong = fixed or args.scaling == "strong"
-    if fixed:
-        # the job's set is the concatenation of 8 generator shards; rank r of R holds shards
-        # r*8/R .. (r+1)*8/R - 1, so the job is the same at every R that divides 8
-        n_all = WORKLOADS[name][0]
-        if 8 % world:
-            raise SystemExit(f"{name} is generated in 8 shards: --gpus must divide 8")
-        off, items, n_tracks, s, conf = whole_job_data(name, range(rank * 8 // world, (rank + 1) * 8 // world))
-        n_total = n_all
-    elif strong:
-        off, items, n_tracks, s, conf = make_data(name, shard=0)
-        n_total = len(off) - 1
-        off, items = rank_slice(off, items, rank, world)
-    else:
-        off, items, n_tracks, s, conf = make_data(name, shard=rank)
-        n_total = (len(off) - 1) * world
-    n_local = len(off) - 1
-    h_off = torch.from_numpy(off).pin_memory()
-    h_items = torch.from_numpy(items).pin_memory()
-    d_off, d_items = h_off.to(device), h_items.to(device)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    name = args.workload
+    off, items, n_tracks, s, conf, n_total, strong = load_job_data(args, rank, world, barrier)
+    n_local = len(off) - 1
+    h_off = torch.from_numpy(off).pin_memory()
+    h_items = torch.from_numpy(items).pin_memory()
+    d_off, d_items = h_off.to(device), h_items.to(device)
+    by_playlists = world > 1 and args.partition == "playlists"
+    # device memory of the one-call entry points, kept across steps (the tables a step returns
+    # are views of it and are dropped before the next step)
+    spaces = {"mine": miner.Workspace(device), "rules": miner.Workspace(device)}
+
+    def mine(o, i):
+        if by_playlists or args.count_impl != "projected":
+            return miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group if by_playlists else None,
+                                  pair_impl=args.pair_impl, count_impl=args.count_impl, impl="python")
+        if world > 1:
+            return multi.mine_partitioned(o, i, n_tracks, s, group, block=args.part_block, workspace=spaces["mine"],
+                                          pair_impl=args.pair_impl)
+        return miner.mine_native(o, i, n_tracks, s, n_playlists_total=n_total, pair_impl=args.pair_impl,
+                                 workspace=spaces["mine"])
+
     def step(o, i):
-        res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group,
-                             prune=False if args.no_prune else None, pair_impl=args.pair_impl,
-                             count_impl=args.count_impl)
+        res = mine(o, i)
         if args.no_rules:
             e = torch.empty(0, device=device)
             return res, miner.RuleTable(e.view(0, 2), e, e, e, [])
-        rules = miner.generate_rules(res, conf, part=(rank, world))
+        rules = miner.generate_rules(res, conf, part=(rank, world), workspace=spaces["rules"])
         return res, rules
 
     def max_over_ranks(x):
@@ -438,20 +473,19 @@ def run_gpu(args):
             f"rules={rules.n_rules} levels={[int(c.numel()) for _, c in res.levels]}")
         info = {"itemsets": res.n_itemsets, "rules_this_rank": rules.n_rules,
                 "levels": [int(c.numel()) for _, c in res.levels], "stats": res.stats,
-                # classes per level (distinct parents), for the rule kernel's probe count
-                "classes": [0, 0] + [int((p[1:] != p[:-1]).sum().item()) + 1 if p.numel() else 0
-                                     for p in (res.parents or [])]}
+                "rule_stats": getattr(rules, "stats", None)}
         del res, rules
 
     # ---- timed region: K steps, inputs resident in HBM ------------------------------------
     # Rank 0 samples its GPU (the line below is rank 0's). Every NVML / nvidia-smi query takes
-    # driver-wide locks; with one sampler per rank their stalls add up through the per-level
-    # allreduce (4 ranks: 84 ms per step with four samplers, 75 ms without).
+    # driver-wide locks; with one sampler per rank their stalls add up across the ranks.
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     _lib.CALLS.clear()
+    _lib.EXTRA_LAUNCHES = 0
     _lib.TRACE = []
+    _lib.profile_begin()          # per-kernel CUDA events inside kmls_mine / kmls_rules
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -462,20 +496,37 @@ def run_gpu(args):
     barrier()
     clocks = sampler.summary()
     trace, _lib.TRACE = _lib.TRACE, None
+    prof = _lib.profile_report()
     launches = _lib.kernel_launches()
     step_s = max_over_ranks(e0.elapsed_time(e1) / 1e3 / args.steps)
 
+    # ---- per-kernel times and roofline objects ---------------------------------------------
+    # `prof`: one record per kernel launch inside the one-call entry points, with the launch's
+    # algorithmic work as DESIGN.md section 3 defines it; `trace`: library calls made from Python
+    # (the whole kmls_mine / kmls_rules calls, and every kernel of the Python-driven paths).
     per = {}
+    for nm, lv, ms, work in prof:
+        d = per.setdefault(nm, {"ms": 0.0, "calls": 0, "work": 0.0, "levels": {}})
+        d["ms"] += ms
+        d["calls"] += 1
+        d["work"] += work
+        lvd = d["levels"].setdefault(lv, [0.0, 0.0])
+        lvd[0] += ms
+        lvd[1] += work
+    calls = {}
     for nm, a, b, nbytes in trace:
-        d = per.setdefault(nm, {"ms": 0.0, "calls": 0, "bytes": 0})
+        d = calls.setdefault(nm, {"ms": 0.0, "calls": 0, "work": 0.0})
         d["ms"] += a.elapsed_time(b)
         d["calls"] += 1
-        d["bytes"] += nbytes or 0
-    top = max(per, key=lambda k: per[k]["ms"]) if per else None
+        d["work"] += nbytes or 0
+        if nm not in ("kmls_mine", "kmls_rules") and not prof:
+            per.setdefault(nm, {"ms": 0.0, "calls": 0, "work": 0.0, "levels": {}})
+            per[nm]["ms"] += a.elapsed_time(b)
+            per[nm]["calls"] += 1
+            per[nm]["work"] += nbytes or 0
     if args.trace and rank == 0:
-        per_step = len(trace) // args.steps
-        for nm, a, b, nbytes in trace[-per_step:]:
-            log(f"[trace] {nm:28s} {a.elapsed_time(b):9.3f} ms  bytes={nbytes}")
+        for nm, lv, ms, work in prof[-(len(prof) // max(args.steps, 1)):]:
+            log(f"[trace] {nm:22s} level {lv:2d} {ms:9.3f} ms  {work / max(ms, 1e-9) / 1e6:9.1f} GB/s")
         log("[trace] level stats: " + json.dumps(info.get("stats", {}).get("levels", [])))
     peaks = {}
     try:
@@ -484,91 +535,59 @@ def run_gpu(args):
         pass
     peak, peak_src = (peaks["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs") if "hbm_gbs" in peaks else \
         (6650.0, "fallback of B200_PROFILING.md")
-    # Roofline objects. Algorithmic work per launch:
-    #   k_rules_count  32 B per index lookup (parent node + child entry) + 8 B per (itemset, antecedent) split written
-    #   k_rules_write  8 B per split read + 24 B per rule written
-    #   k_pair_gemm_i8 2 * N * F(F+1)/2 int8 ops (upper triangle incl. diagonal)
-    #   others         the bytes the caller annotates (miner.py, algo_bytes=...)
     int8_peak = 2.0 * peaks.get("bf16_tflops", 1590.0)   # TOP/s: int8 dense = 2x the measured bf16 GEMM peak
-    lv_sizes = info.get("levels", [])
-    classes = info.get("classes", [])
-    splits = sum(n * ((1 << (k - 1)) - 1) for k, n in enumerate(lv_sizes, start=1) if k >= 2)
-    probes = sum(classes[k] * max((1 << (k - 1)) - k, 0) + n * max((1 << (k - 1)) - 2, 0)
-                 for k, n in enumerate(lv_sizes, start=1) if k >= 2 and k < len(classes) + 0)
-    algo = {
-        "kmls_rules_count": (32 * probes + 8 * splits) / max(world, 1),
-        "kmls_rules_write": (8 * splits) / max(world, 1) + 24 * (info.get("rules_this_rank") or 0),
-        # gather route of pass 1 (one GPU): two 4-byte counts read + 8 bytes written per split;
-        # one index lookup (32 B) + 4 bytes written per (itemset, dropped member)
-        "kmls_rules_count_gather": 16 * splits,
-        "kmls_rules_subsets": 36 * sum(n * (k - 1) for k, n in enumerate(lv_sizes, start=1) if k >= 2),
-    }
-
-    def roof_of(nm, kernel, bound):
-        if nm not in per or per[nm]["ms"] <= 0:
-            return None
-        sec = per[nm]["ms"] / 1e3 / args.steps           # all launches of one step
-        work = algo.get(nm, per[nm]["bytes"] / args.steps)
-        if bound == "tensor":
-            ach, pk, unit, src = work / sec / 1e12, int8_peak, "TOP/s", "2 x bf16_tflops of MEASURED_PEAKS.json"
-        else:
-            ach, pk, unit, src = work / sec / 1e9, peak, "GB/s", peak_src
-        return {"kernel": kernel, "bound": bound, "achieved": ach, "peak": pk, "unit": unit,
-                "frac": ach / pk, "traffic": None, "peak_source": src,
-                "launches_per_step": per[nm]["calls"] / args.steps, "ms_per_step": sec * 1e3,
-                "algorithmic_work_per_step": work}
-
-    kernel_of = {"kmls_rules_count": ("k_rules_count", "hbm"), "kmls_rules_write": ("k_rules_write", "hbm"),
-                 "kmls_rules_count_gather": ("k_rules_gather", "hbm"), "kmls_rules_subsets": ("k_rules_subsets", "hbm"),
-                 "kmls_pair_counts_i8": ("k_pair_gemm_i8", "tensor"), "kmls_project_rows": ("k_project_rows", "hbm"),
-                 "kmls_count_candidates": ("k_count_candidates", "hbm"), "kmls_encode_bitmap": ("k_encode_bitmap", "hbm"),
-                 "kmls_row_popcount": ("k_row_popcount", "hbm"), "kmls_item_histogram": ("k_item_histogram", "hbm")}
-    rooflines = {k: roof_of(k, *v) for k, v in kernel_of.items() if k in per}
     try:   # DRAM traffic of one ncu-captured launch per kernel (workload zipf_1Mx100k_s0.001, 1 GPU)
         ncu_traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        for k_, r_ in rooflines.items():
-            if r_ and k_ in ncu_traffic and name == "zipf_1Mx100k_s0.001" and world == 1:
-                r_["traffic"] = ncu_traffic[k_]["traffic_bytes"]
-                r_["traffic_launch"] = ncu_traffic[k_]["launch"]
     except (OSError, ValueError):
-        pass
-    roof = rooflines.get(top) or next((r for r in rooflines.values() if r), None)
+        ncu_traffic = {}
 
-    # ---- e2e: pinned host CSR in, tables back on the host ---------------------------------
-    pinned = {}
+    def roof_of(nm):
+        d = per[nm]
+        if d["ms"] <= 0 or d["work"] <= 0:
+            return None
+        sec = d["ms"] / 1e3 / args.steps
+        work = d["work"] / args.steps
+        if nm == "k_pair_gemm_i8":
+            ach, pk, unit, src, bound = work / sec / 1e12, int8_peak, "TOP/s", "2 x bf16_tflops of MEASURED_PEAKS.json", "tensor"
+        else:
+            ach, pk, unit, src, bound = work / sec / 1e9, peak, "GB/s", peak_src, "hbm"
+        r = {"kernel": nm, "bound": bound, "achieved": ach, "peak": pk, "unit": unit, "frac": ach / pk,
+             "traffic": None, "peak_source": src, "launches_per_step": d["calls"] / args.steps,
+             "ms_per_step": sec * 1e3, "algorithmic_work_per_step": work,
+             "algorithmic_work_per_launch": work / max(d["calls"] / args.steps, 1e-9)}
+        if d["levels"]:
+            # the launch that takes longest, on its own: comparable with a one-launch ncu capture
+            lv, (ms_l, w_l) = max(d["levels"].items(), key=lambda kv: kv[1][0])
+            r["largest_launch"] = {"level": lv, "ms": ms_l / args.steps, "algorithmic_work": w_l / args.steps,
+                                   "achieved": w_l / max(ms_l, 1e-9) / (1e9 if bound == "tensor" else 1e6)}
+        t = ncu_traffic.get(nm)
+        if t and name == t.get("workload", "zipf_1Mx100k_s0.001") and world == 1:
+            r["traffic"] = t["traffic_bytes"]
+            r["traffic_launch"] = t["launch"]
+        return r
 
-    def to_host(i, t):
-        key = (i, t.dtype)
-        if key not in pinned or pinned[key].numel() < t.numel():
-            pinned[key] = torch.empty(max(t.numel(), 1), dtype=t.dtype).pin_memory()
-        dst = pinned[key][:t.numel()]
-        dst.copy_(t.reshape(-1), non_blocking=True)
-        return dst
+    rooflines = {nm: roof_of(nm) for nm in per}
+    rooflines = {k_: v for k_, v in rooflines.items() if v}
+    top = max(per, key=lambda k_: per[k_]["ms"]) if per else None
+    roof = rooflines.get(top) or next(iter(rooflines.values()), None)
 
+    # ---- e2e: the public call, pinned host CSR in, tables back on the host ------------------
     host_tables = kmls_b200.api.HostTables(device)
 
     def e2e_step():
-        # pinned host CSR up, mine + rules, every level table streamed back to pinned host
-        # memory on a side stream while the next levels are mined (kmls_b200.api.HostTables)
-        o = h_off.to(device, non_blocking=True)
-        i = h_items.to(device, non_blocking=True)
-        # (the level tables are identical on every rank: rank 0 alone brings them to the host,
-        # as the job does when "rank 0 writes the pickle")
-        host_tables.begin()
-        res = miner.mine_csr(o, i, n_tracks, s, n_playlists_total=n_total, group=group,
-                             prune=False if args.no_prune else None, pair_impl=args.pair_impl,
-                             count_impl=args.count_impl, on_level=host_tables.on_level if rank == 0 else None)
-        n_rules = 0
-        if not args.no_rules:
-            n_rules = miner.generate_rules(res, conf, part=(rank, world)).n_rules
-        host_tables.finish(res)
+        res, rules = kmls_b200.mine_ids(h_off, h_items, n_tracks, s, None if args.no_rules else conf,
+                                        host_tables=host_tables if rank == 0 else None, split_rules=True,
+                                        partition=args.partition, workspaces=spaces, pair_impl=args.pair_impl)
+        n_rules = rules.n_rules if rules is not None else 0
         torch.cuda.synchronize()
-        return host_tables.nbytes, n_rules
+        del res, rules
+        return (host_tables.nbytes if rank == 0 else 0), n_rules
 
-    e2e_note = ("pinned host CSR -> device -> mine + rules; every level table is streamed back to pinned host "
-                "memory while mining continues (kmls_b200.api.HostTables; by rank 0 when there are several ranks, the tables "
-                "being identical on all of them); the rule table stays on the device "
-                "(sharded by rank)")
+    e2e_note = ("kmls_b200.mine_ids(offsets, ids, ...) - the call behind calculate_and_save_fp_growth_fast - with the "
+                "playlists in pinned HOST memory: upload, mine + rules, every level table copied back to pinned host "
+                "memory on a side stream while the rules are generated (by rank 0 when there are several ranks, the "
+                "tables being identical on all of them); the rule table stays on the device (sharded by rank; "
+                "e2e_with_rules below moves it too)")
     if name.startswith("mpd_standin") and world == 1:
         # the reference-facing plugin call itself: dict of lists of names in, dict of dicts out
         from kmls_b200 import synth
@@ -639,6 +658,32 @@ def run_gpu(args):
                                 f"{want.get('oracle_seconds')} s on {want.get('oracle_threads')} threads)"}
         log(f"[bench] parity: {parity}")
 
+    # ---- e2e with the RULE TABLE brought to the host as well (on request: at config 3 it is
+    # 52 GB over PCIe, about a second)
+    e2e_rules = None
+    if args.rules_to_host and not args.no_rules:
+        def rules_step():
+            res, rules = kmls_b200.mine_ids(h_off, h_items, n_tracks, s, conf, host_tables=host_tables if rank == 0 else None,
+                                            split_rules=True, partition=args.partition, workspaces=spaces,
+                                            pair_impl=args.pair_impl)
+            hr = kmls_b200.api.rules_to_pinned(rules, rules_pinned)
+            torch.cuda.synchronize()
+            n = rules.n_rules
+            del res, rules, hr
+            return 24 * n
+        rules_pinned = {}
+        rules_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(max(1, min(args.steps, 2))):
+            rb = rules_step()
+        barrier()
+        e2e_rules = {"value": max_over_ranks((time.perf_counter() - t0) / max(1, min(args.steps, 2))), "unit": "s",
+                     "d2h_rule_bytes_per_step_this_rank": rb,
+                     "note": "as e2e, plus this rank's rule table (rule ids, confidence, lift: 24 B per rule) copied "
+                             "to pinned host memory in 64 MB pieces"}
+        del rules_pinned
+
     verify = None
     if args.verify and world == 1:
         from oracle import fpgrowth_c, mlxtend_restated as M
@@ -686,12 +731,22 @@ def run_gpu(args):
             "data": "synthetic",
             "config": {"workload": name, "n_playlists": n_total, "n_playlists_per_gpu": n_local, "n_tracks": n_tracks, "mean_draws": draws,
                        "zipf_alpha": alpha, "min_support": s, "min_confidence": None if args.no_rules else conf,
-                       "parallelism": f"playlist-sharded x{world}, rules split by itemset range",
-                       "l2": ("inputs larger than L2 (CSR 0.5 GB, bitmap 0.75 GB per GPU)" if n_local >= 500_000
-                              else "small workload: inputs fit in L2, launch/latency-bound")},
+                       "parallelism": ("1 GPU" if world == 1 else
+                                       (f"candidate space split by frequent pair over {world} ranks (every rank holds all "
+                                        f"playlists; blocks of {args.part_block} pairs dealt round-robin), tables merged by "
+                                        "one sum-allreduce, rule table split by itemset range"
+                                        if not by_playlists else
+                                        f"playlists sharded over {world} ranks, one count allreduce per level, rule table "
+                                        "split by itemset range")),
+                       "l2": ("inputs larger than L2 (CSR 0.5 GB, bitmap 0.75 GB); every step also writes several GB of "
+                              "tables and rules, far more than the 126 MB L2, so each step starts cold"
+                              if n_local >= 500_000 else
+                              "small workload: inputs fit in L2, launch/latency-bound")},
             "clocks": clocks,
             "e2e": {"value": e2e_s, "unit": "s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "note": e2e_note},
+            "e2e_with_rules": e2e_rules,
+            "phases_ms_per_step": {k_: v_["ms"] / args.steps for k_, v_ in calls.items() if k_ in ("kmls_mine", "kmls_rules")},
             "gpu_launches": launches,
             "roofline": roof,
             "rooflines": {k: v for k, v in rooflines.items() if v},
@@ -702,6 +757,7 @@ def run_gpu(args):
             "level_sizes": info.get("levels"),
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
+            "partition": info.get("stats", {}).get("partition"),
             "top_kernel": top,
             "parity": parity,
             "verify_full_size": verify,
@@ -741,6 +797,12 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong (default): the job's playlists are the same at every --gpus N, sliced over the "
                          "ranks; weak: every rank generates its own set of the workload's size")
+    ap.add_argument("--partition", default="classes", choices=["classes", "playlists"],
+                    help="multi-GPU: classes (default) = every rank holds all playlists and mines its share of the "
+                         "candidate space, no per-level exchange; playlists = row-sharded playlists with one count "
+                         "allreduce per level")
+    ap.add_argument("--part-block", type=int, default=64, help="frequent pairs per block of the class partition")
+    ap.add_argument("--rules-to-host", action="store_true", help="also measure e2e with the rule table copied to the host")
     ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
     ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc", "csr"])
     ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])

@@ -418,6 +418,38 @@ int kmls_rules(const kmls_mine_result* mined, const void* d_tables_base, double 
                int32_t part, int32_t n_parts, int32_t pass1, int64_t max_rules, void* d_workspace,
                size_t workspace_bytes, kmls_rules_result* result, kmls_stream_t stream);
 
+/* ---- multi-GPU: merging class-partitioned results (no counterpart in the reference, which
+ *      has no parallelism). Each rank mined the subtrees of its own frequent pairs (kmls_mine
+ *      with n_parts > 1); the job's table of level k >= 3 is the ranks' itemsets merged in the
+ *      order of their root pair, which is the sorted order a single GPU produces. ----------- */
+
+/* d_root[o] = the frequent pair (index into level 2) under which local itemset o of level k
+ * lives: its parent for k == 3 (d_root_prev NULL), else d_root_prev[parent] (roots of the local
+ * level k-1). d_per_root[r] (zeroed by the caller, one int per frequent pair) += itemsets. */
+int kmls_subtree_roots(const int32_t* d_par, int64_t n, const int32_t* d_root_prev, int32_t* d_root,
+                       int32_t* d_per_root, kmls_stream_t stream);
+/* Writes the n local itemsets of level k at their job-wide positions g = d_global_start[root] +
+ * (local index - d_local_start[root]) (exclusive scans over the pairs of the job-wide and of
+ * this rank's per-root counts) into job-wide tables that the caller zero-initialised and
+ * afterwards completes with a sum-allreduce; the parent column is translated to job-wide
+ * positions through d_gprev (= d_g_out of level k-1; NULL for k == 3, whose parents are pair
+ * indices already). d_g_out[o] = g. */
+int kmls_place_level(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par, int64_t n,
+                     int32_t k, const int32_t* d_root, const int64_t* d_global_start,
+                     const int64_t* d_local_start, const int32_t* d_gprev, int32_t* d_items_out,
+                     int32_t* d_counts_out, int32_t* d_par_out, int32_t* d_g_out, kmls_stream_t stream);
+
+/* ---- measurement plumbing (no counterpart in the reference) --------------------------------
+ * kmls_profile_begin switches per-kernel timing on for the calling host thread: from then on
+ * kmls_mine and kmls_rules bracket every kernel they launch with two CUDA events on the
+ * launching stream. kmls_profile_report switches it off again, waits for the events and writes
+ * one text line per launch, "kernel,level,milliseconds,algorithmic_work", into buf (at most
+ * capacity bytes, NUL-terminated); returns the bytes the full report needs. The work figure is
+ * the algorithmic bytes of the launch as DESIGN.md section 3 defines them (operations for the
+ * tensor-core GEMM). */
+int kmls_profile_begin(void);
+int64_t kmls_profile_report(char* buf, size_t capacity);
+
 #ifdef __cplusplus
 }
 #endif

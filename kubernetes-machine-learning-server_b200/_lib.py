@@ -60,6 +60,11 @@ SIGNATURES = {
     "kmls_rule_checksum": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P]),
     "kmls_thresholds": (ctypes.c_int, [_F64, _I64, _P, _P]),
     "kmls_mine": (ctypes.c_int, [_P, _P, _I64, _I32, _I64, _I32, _I32, _P, _P, _SZ, _P, _P]),
+    "kmls_rules": (ctypes.c_int, [_P, _P, _F64, _I32, _I32, _I32, _I64, _P, _SZ, _P, _P]),
+    "kmls_subtree_roots": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
+    "kmls_place_level": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "kmls_profile_begin": (ctypes.c_int, []),
+    "kmls_profile_report": (_I64, [_P, _SZ]),
     "kmls_rule_division_selftest": (ctypes.c_int, [_I64, _I64, ctypes.c_uint64, _P, _P]),
 }
 
@@ -85,6 +90,15 @@ class MineResultC(ctypes.Structure):
                 ("row_items_off", c_int64), ("occurrences_off", c_int64), ("pair_off", c_int64),
                 ("h_items_off", c_int64 * _LV), ("h_counts_off", c_int64 * _LV),
                 ("h_row_items_off", c_int64), ("h_bytes", c_int64)]
+
+
+class RulesResultC(ctypes.Structure):
+    """struct kmls_rules_result (include/kmls_b200.h)."""
+    _fields_ = [("n_rules", c_int64), ("n_itemsets", c_int64), ("n_splits", c_int64),
+                ("rule_off", c_int64), ("confidence_off", c_int64), ("lift_off", c_int64),
+                ("arena_items_off", c_int64), ("arena_counts_off", c_int64),
+                ("workspace_needed_bytes", c_size_t), ("workspace_peak_bytes", c_size_t),
+                ("kernel_launches", c_int64), ("pass1_used", c_int32), ("reserved", c_int32)]
 
 
 _lib = None
@@ -145,7 +159,15 @@ def call_rc(name: str, *args):
     """Call an int-returning entry point and hand back (return code, error text) instead of
     raising: for callers that react to a capacity error by retrying with a larger buffer."""
     lib = load()
-    rc = getattr(lib, name)(*[_arg(a) for a in args])
+    if TRACE is not None:
+        import torch
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        rc = getattr(lib, name)(*[_arg(a) for a in args])
+        e1.record()
+        TRACE.append((name, e0, e1, None))
+    else:
+        rc = getattr(lib, name)(*[_arg(a) for a in args])
     return rc, (lib.kmls_last_error().decode("utf-8", "replace") if rc != 0 else "")
 
 
@@ -174,3 +196,21 @@ def kernel_launches() -> int:
 def value(name: str, *args):
     """Call a value-returning helper (sizes)."""
     return getattr(load(), name)(*[_arg(a) for a in args])
+
+
+def profile_begin():
+    load().kmls_profile_begin()
+
+
+def profile_report():
+    """[(kernel, level, ms, algorithmic work)] of every launch kmls_mine / kmls_rules made on
+    this thread since profile_begin()."""
+    lib = load()
+    need = int(lib.kmls_profile_report(None, 0))
+    buf = ctypes.create_string_buffer(need + 16)
+    lib.kmls_profile_report(buf, need + 16)     # the first call switched recording off; events are kept
+    out = []
+    for ln in buf.value.decode().splitlines():
+        nm, lv, ms, work = ln.rsplit(",", 3)
+        out.append((nm, int(lv), float(ms), float(work)))
+    return out

@@ -117,6 +117,12 @@ class HostTables:
         counts.record_stream(self.stream)
         self._pending.append((k, hi, hc))
 
+    def copy_result(self, res):
+        """All level tables of a finished result, queued on the side stream."""
+        for k, (items, counts) in enumerate(res.levels, start=1):
+            if k not in [p[0] for p in self._pending]:
+                self.on_level(k, items, counts)
+
     def finish(self, res):
         with torch.cuda.stream(self.stream):
             self.stream.wait_stream(torch.cuda.current_stream(self.device))
@@ -132,18 +138,32 @@ class HostTables:
 def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: float,
              min_confidence: Optional[float] = None, max_len: Optional[int] = None,
              host_tables: Optional[HostTables] = None, split_rules: bool = False,
-             rules_required: bool = True, **mine_kwargs):
+             rules_required: bool = True, partition: str = "classes",
+             workspaces: Optional[dict] = None, **mine_kwargs):
     """Host CSR of track ids in, device tables out: (MineResult, RuleTable or None).
-    Under torchrun each rank keeps a contiguous range of the playlists. With ``host_tables``
-    the level tables are also streamed to pinned host memory during the mining (see
-    HostTables); ``offsets``/``ids`` may be pinned torch tensors to make the upload async.
-    ``split_rules``: under torchrun, each rank generates only its share of the rule table.
-    ``rules_required=False`` turns a rule table that cannot be built into a warning and
-    ``rules = None`` instead of an error (the reference-facing entry points use this)."""
+
+    One process: the whole path runs through ``kmls_mine`` / ``kmls_rules``. Under torchrun
+    (an initialised process group) every rank passes the same playlists and
+    ``partition="classes"`` (default) splits the candidate space over the ranks
+    (``multi.mine_partitioned``: every rank uploads the whole set, mines its share of the
+    subtrees, and ends up with the complete table); ``partition="playlists"`` gives each rank a
+    contiguous range of the playlists and sums every level's counts with an allreduce
+    (``miner.mine_csr(group=...)``). With ``host_tables`` the level tables are also copied to
+    pinned host memory on a side stream while the rules are generated (see HostTables);
+    ``offsets``/``ids`` may be pinned torch tensors to make the upload async. ``split_rules``:
+    each rank generates only its share of the rule table. ``rules_required=False`` turns a rule
+    table that cannot be built into a warning and ``rules = None`` (the reference-facing entry
+    points use this). ``workspaces``: a dict the call keeps its device workspaces in
+    (``"mine"``, ``"rules"``) so that repeated calls reuse them; the returned tables are views of
+    those workspaces and are overwritten by the next call that is given the same dict."""
     device = _device()
     group, rank, world = _dist_group()
     n_total = len(offsets) - 1
-    if world > 1:
+    python_loop = (mine_kwargs.get("impl") == "python" or mine_kwargs.get("count_impl", "projected") != "projected"
+                   or bool(mine_kwargs.get("prune")) or mine_kwargs.get("first_projection", "gather") != "gather"
+                   or mine_kwargs.get("prepared") is not None or mine_kwargs.get("on_level") is not None)
+    by_playlists = world > 1 and (partition == "playlists" or python_loop)
+    if by_playlists:
         if torch.is_tensor(offsets):
             offsets, ids = offsets.numpy(), ids.numpy()
         offsets, ids = _shard(offsets, ids, rank, world)
@@ -152,16 +172,38 @@ def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: fl
     else:
         d_off = torch.from_numpy(np.ascontiguousarray(offsets)).to(device, non_blocking=True)
         d_ids = torch.from_numpy(np.ascontiguousarray(ids)).to(device, non_blocking=True)
+    ws = workspaces if workspaces is not None else {}
     if host_tables is not None:
         host_tables.begin()
-        mine_kwargs["on_level"] = host_tables.on_level
-    res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
-                         group=group, max_len=max_len, **mine_kwargs)
+    if world > 1 and not by_playlists:
+        from . import multi
+        for k_ in ("count_impl", "prune", "first_projection", "prepared", "on_level", "impl"):
+            mine_kwargs.pop(k_, None)
+        if "mine" not in ws and workspaces is not None:
+            ws["mine"] = miner.Workspace(device)
+        res = multi.mine_partitioned(d_off, d_ids, n_items, min_support, group, max_len=max_len,
+                                     workspace=ws.get("mine"), **mine_kwargs)
+    elif by_playlists:
+        if host_tables is not None:
+            mine_kwargs["on_level"] = host_tables.on_level
+        mine_kwargs.pop("impl", None)
+        res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
+                             group=group, max_len=max_len, impl="python", **mine_kwargs)
+    else:
+        if "mine" not in ws and workspaces is not None:
+            ws["mine"] = miner.Workspace(device)
+        res = miner.mine_csr(d_off, d_ids, n_items, min_support, n_playlists_total=n_total,
+                             max_len=max_len, workspace=ws.get("mine"), **mine_kwargs)
+    if host_tables is not None and not by_playlists:
+        host_tables.copy_result(res)        # async, on the side stream: overlaps the rule generation
     rules = None
     if min_confidence is not None:
         try:
+            if "rules" not in ws and workspaces is not None:
+                ws["rules"] = miner.Workspace(device)
             rules = miner.generate_rules(res, min_confidence,
-                                         part=(rank, world) if split_rules else (0, 1))
+                                         part=(rank, world) if split_rules else (0, 1),
+                                         workspace=ws.get("rules"))
         except _lib.KmlsError as e:
             if rules_required:
                 raise
@@ -174,6 +216,36 @@ def mine_ids(offsets: np.ndarray, ids: np.ndarray, n_items: int, min_support: fl
     if host_tables is not None:
         host_tables.finish(res)
     return res, rules
+
+
+RULES_HOST_LIMIT = int(float(os.getenv("KMLS_RULES_HOST_GB", 96)) * (1 << 30))
+
+
+def rules_to_pinned(rules: miner.RuleTable, cache: Optional[dict] = None, piece: int = 64 << 20):
+    """The rule table's columns copied to pinned host memory: ``(rule int32[R, 2], confidence
+    float64[R], lift float64[R])`` as numpy views of the pinned buffers (kept in ``cache`` for
+    reuse by the next call). 24 bytes per rule, moved in pieces so that other transfers can
+    interleave. Refuses, with the size it would need, a table beyond ``KMLS_RULES_HOST_GB``
+    (default 96 GB of pinned host memory) instead of exhausting the host."""
+    n = rules.n_rules
+    need = 24 * n
+    if need > RULES_HOST_LIMIT:
+        raise _lib.KmlsError(f"the rule table ({n} rules, {need / 1e9:.1f} GB) exceeds the host-memory bound "
+                             f"KMLS_RULES_HOST_GB={RULES_HOST_LIMIT / (1 << 30):.0f}: raise the bound, raise "
+                             "min_confidence, or keep the table on the device (nothing is truncated)")
+    cache = cache if cache is not None else {}
+    out = []
+    for key, t in (("rule", rules.rule.reshape(-1)), ("confidence", rules.confidence), ("lift", rules.lift)):
+        b = cache.get(key)
+        if b is None or b.numel() < t.numel() or b.dtype != t.dtype:
+            b = cache[key] = torch.empty(max(int(t.numel()), 1), dtype=t.dtype).pin_memory()
+        dst = b[:t.numel()]
+        step = max(1, piece // t.element_size())
+        for a in range(0, int(t.numel()), step):
+            dst[a:a + step].copy_(t[a:a + step], non_blocking=True)
+        out.append(dst)
+    torch.cuda.current_stream().synchronize()
+    return out[0].numpy().reshape(-1, 2), out[1].numpy(), out[2].numpy()
 
 
 def recommendations_from_result(res: miner.MineResult, columns: Sequence[str]

@@ -30,6 +30,7 @@
 
 #include "common.cuh"
 #include "kmls_b200.h"
+#include "profile.cuh"
 #include "workspace.cuh"
 
 namespace kmls {
@@ -396,6 +397,39 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
   }
 }
 
+// work figures for the profiler (launched only while it is on)
+__global__ void __launch_bounds__(256)
+k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww, int64_t n,
+             unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
+    const long long m = ncand[p];
+    if (m) acc += (unsigned long long)((m + 1) * (long long)roww[p]);   // row(p) once + one row per candidate
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+__global__ void __launch_bounds__(256)
+k_sum_i32(const int32_t* __restrict__ v, int64_t n, unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    acc += (unsigned long long)v[i];
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+// sum of the upper triangle (diagonal included) of the pair matrix = counter updates made
+__global__ void __launch_bounds__(256)
+k_sum_upper(const int32_t* __restrict__ pair, int32_t n_rows, unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0;
+  const int64_t n2 = (int64_t)n_rows * n_rows;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n2; e += (int64_t)gridDim.x * blockDim.x) {
+    const int i = (int)(e / n_rows), j = (int)(e - (int64_t)i * n_rows);
+    if (j >= i) acc += (unsigned long long)pair[e];
+  }
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+}
+
 struct GeThr {
   int32_t thr;
   __host__ __device__ int64_t operator()(int32_t c) const { return c >= thr ? 1 : 0; }
@@ -614,7 +648,10 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   KMLS_TRY(M.sync());
   const int64_t nnz = M.box[0];
   KMLS_REQUIRE(nnz >= 0, "kmls_mine: offsets are not ascending");
-  KMLS_TRY(kmls_item_histogram(d_items, nnz, n_items, occ, s));
+  {
+    ProfScope ps("k_item_histogram", s, 4.0 * (double)nnz, 1);
+    KMLS_TRY(kmls_item_histogram(d_items, nnz, n_items, occ, s));
+  }
   ++M.launches;
   const int32_t thr1 = std::max(t1, 1);
   int32_t *cand = nullptr, *keys = nullptr, n_rows = 0;
@@ -637,8 +674,14 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   KMLS_LAUNCHED("k_fill_i32");
   k_number_rows<<<grid_for(n_rows, 256, 8), 256, 0, s>>>(cand, n_rows, row_of_item, nullptr);
   KMLS_LAUNCHED("k_number_rows");
-  KMLS_TRY(kmls_encode_bitmap(d_offsets, d_items, n_playlists, row_of_item, n_items, n_rows, bitmap, row_words, s));
-  KMLS_TRY(kmls_row_popcount(bitmap, n_rows, row_words, counts1, s));
+  {
+    ProfScope ps("k_encode_bitmap", s, 4.0 * (double)nnz + 8.0 * (double)n_playlists + 4.0 * (double)n_rows * (double)row_words, 1);
+    KMLS_TRY(kmls_encode_bitmap(d_offsets, d_items, n_playlists, row_of_item, n_items, n_rows, bitmap, row_words, s));
+  }
+  {
+    ProfScope ps("k_row_popcount", s, 4.0 * (double)n_rows * (double)row_words, 1);
+    KMLS_TRY(kmls_row_popcount(bitmap, n_rows, row_words, counts1, s));
+  }
   k_check_counts<<<grid_for(n_rows, 256, 4), 256, 0, s>>>(counts1, keys, n_rows, flags);
   KMLS_LAUNCHED("k_check_counts");
   k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), nullptr, flags, nullptr, M.box);
@@ -736,21 +779,36 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     }
   }
   if (impl == 1) {
-    KMLS_TRY(kmls_pair_counts_csr(d_offsets, d_items, n_playlists, row_of_item, n_rows, pair, flags + 4, s));
-    k_post<<<1, 1, 0, s>>>(nullptr, nullptr, flags + 4, nullptr, M.box);
+    int rec = -1;
+    {
+      ProfScope ps("k_pair_counts_csr", s, 0.0, 2);
+      rec = ps.idx;
+      KMLS_TRY(kmls_pair_counts_csr(d_offsets, d_items, n_playlists, row_of_item, n_rows, pair, flags + 4, s));
+    }
+    if (rec >= 0) {   // work = counter updates made = sum of the upper triangle, 4 bytes each
+      KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
+      k_sum_upper<<<grid_for((int64_t)n_rows * n_rows, 256, 8), 256, 0, s>>>(pair, n_rows, (unsigned long long*)(flags + 6));
+      KMLS_LAUNCHED("k_sum_upper");
+    }
+    k_post<<<1, 1, 0, s>>>(rec >= 0 ? (const int64_t*)(flags + 6) : nullptr, nullptr, flags + 4, nullptr, M.box);
     KMLS_LAUNCHED("k_post");
     M.launches += 2;
     KMLS_TRY(M.sync());
+    if (rec >= 0) profiler().records[rec].work = 4.0 * (double)M.box[0];
     if (M.box[2] != 0) impl = big ? 3 : 2;   // a playlist with more than 1024 kept tracks
   }
   if (impl == 2) {
+    ProfScope ps("k_pair_counts", s, 4.0 * (double)n_rows * (double)row_words, 2);
     KMLS_TRY(kmls_pair_counts(bitmap, n_rows, row_words, pair, s));
     ++M.launches;
   } else if (impl == 3) {
     const size_t gbytes = kmls_pair_gemm_scratch_bytes(n_rows, row_words);
     char* gscratch = nullptr;
     KMLS_TRY(M.take(&gscratch, (int64_t)gbytes));
-    KMLS_TRY(kmls_pair_counts_i8(bitmap, n_rows, row_words, pair, gscratch, gbytes, s));
+    {
+      ProfScope ps("k_pair_gemm_i8", s, (double)n_rows * (n_rows + 1.0) * (double)n_playlists, 2);
+      KMLS_TRY(kmls_pair_counts_i8(bitmap, n_rows, row_words, pair, gscratch, gbytes, s));
+    }
     M.launches += 2;
     M.ws.release(gscratch);
   } else if (impl != 1) {
@@ -772,7 +830,10 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   R->thr_k = thr;
   int64_t* row_off = nullptr;
   KMLS_TRY(M.take(&row_off, n_rows + 1));
-  KMLS_TRY(kmls_pair_select(pair, n_rows, thr, 0, row_off, nullptr, nullptr, s));
+  {
+    ProfScope ps("k_pair_select", s, 4.0 * (double)n_rows * (double)n_rows, 2);
+    KMLS_TRY(kmls_pair_select(pair, n_rows, thr, 0, row_off, nullptr, nullptr, s));
+  }
   k_post<<<1, 1, 0, s>>>(row_off + n_rows, nullptr, nullptr, nullptr, M.box);
   KMLS_LAUNCHED("k_post");
   M.launches += 3;
@@ -786,7 +847,10 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   KMLS_TRY(M.take(&counts_k, n2, false));
   KMLS_TRY(M.take(&par_k, n2, false));
   KMLS_TRY(M.take(&second2, n2));
-  KMLS_TRY(kmls_pair_select(pair, n_rows, thr, n2, row_off, items_k, counts_k, s));
+  {
+    ProfScope ps("k_pair_select", s, 4.0 * (double)n_rows * (double)n_rows + 12.0 * (double)n2, 2);
+    KMLS_TRY(kmls_pair_select(pair, n_rows, thr, n2, row_off, items_k, counts_k, s));
+  }
   k_pair_parents<<<grid_for(n2, 256, 8), 256, 0, s>>>(items_k, n2, par_k, second2);
   KMLS_LAUNCHED("k_pair_parents");
   M.launches += 4;
@@ -826,7 +890,11 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     R->level_row_words[2] = words;
     KMLS_TRY(M.take(&arena_k, words));
     KMLS_TRY(M.take(&tids, n_tids));
-    KMLS_TRY(kmls_row_tidlists(bitmap, n_rows, row_words, tid_off, tids, s));
+    {
+      ProfScope ps("k_row_tidlists", s, 4.0 * (double)n_rows * (double)row_words + 4.0 * (double)n_tids, 2);
+      KMLS_TRY(kmls_row_tidlists(bitmap, n_rows, row_words, tid_off, tids, s));
+    }
+    ProfScope ps("k_project_gather", s, 4.0 * (double)words, 2);
     KMLS_TRY(kmls_project_rows_gather(bitmap, row_words, par_k, second2, n2, tids, tid_off, arena_k, rowptr_k,
                                       words, s));
     M.launches += 2;
@@ -851,10 +919,19 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&wnew, n_k));
     KMLS_TRY(M.take(&off2, n_k + 1));
     const bool parted = k == 2 && opt.n_parts > 1;
-    k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words,
-                                                       parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
-                                                       ncand, wnew);
-    KMLS_LAUNCHED("k_join_size");
+    const bool prof = profiler().on;
+    {
+      ProfScope ps("k_join_size", s, 20.0 * (double)n_k, k + 1);
+      k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words,
+                                                         parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
+                                                         ncand, wnew);
+      KMLS_LAUNCHED("k_join_size");
+    }
+    if (prof) {
+      KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
+      k_level_work<<<grid_for(n_k, 256, 8), 256, 0, s>>>(ncand, roww_k, n_k, (unsigned long long*)(flags + 6));
+      KMLS_LAUNCHED("k_level_work");
+    }
     {
       cub::CountingInputIterator<int64_t> idx(0);
       cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(idx, CandSlots{ncand, wnew});
@@ -862,6 +939,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
       char* tmp = nullptr;
       KMLS_TRY(M.take(&tmp, (int64_t)need));
+      ProfScope ps("scan_slots", s, 24.0 * (double)n_k, k + 1);
       KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
       M.ws.release(tmp);
     }
@@ -870,6 +948,13 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     M.launches += 4;
     KMLS_TRY(M.sync());
     const int64_t n_cand = M.box[0], slot_words = M.box[1];
+    double read_words = 0.0;
+    if (prof) {
+      unsigned long long h = 0;
+      KMLS_CUDA(cudaMemcpyAsync(&h, flags + 6, 8, cudaMemcpyDeviceToHost, s));
+      KMLS_TRY(M.sync());
+      read_words = (double)h;
+    }
     R->level_candidates[k + 1] = n_cand;
     if (n_cand == 0) break;
     if (total + n_cand > max_itemsets * 4)
@@ -883,15 +968,23 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&cand_cnt, n_cand));
     KMLS_TRY(M.take(&cand_p, n_cand));
     KMLS_TRY(M.take(&out_off, n_cand + 1));
-    k_count_project<<<grid_for(n_k, 8, 64), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, n_k, thr,
-                                                         keep_words, arena_n, cand_cnt, cand_p);
-    KMLS_LAUNCHED("k_count_project");
+    int rec_cp = -1;
+    {
+      // algorithmic bytes: row(p) once per parent + one row per candidate read, 8 bytes per
+      // candidate written (count, parent), + the rows of the survivors (added below)
+      ProfScope ps("k_count_project", s, 4.0 * read_words + 8.0 * (double)n_cand, k + 1);
+      rec_cp = ps.idx;
+      k_count_project<<<grid_for(n_k, 8, 64), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, n_k, thr,
+                                                           keep_words, arena_n, cand_cnt, cand_p);
+      KMLS_LAUNCHED("k_count_project");
+    }
     {
       cub::TransformInputIterator<int64_t, GeThr, const int32_t*> it(cand_cnt, GeThr{thr});
       size_t need = 0;
       KMLS_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, need, it, out_off, (int)n_cand, s));
       char* tmp = nullptr;
       KMLS_TRY(M.take(&tmp, (int64_t)need));
+      ProfScope ps("scan_survivors", s, 12.0 * (double)n_cand, k + 1);
       KMLS_CUDA(cub::DeviceScan::ExclusiveSum(tmp, need, it, out_off, (int)n_cand, s));
       M.ws.release(tmp);
     }
@@ -913,10 +1006,22 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&par_n, n_next, false));
     KMLS_TRY(M.take(&rowptr_n, n_next));
     KMLS_TRY(M.take(&roww_n, n_next));
-    k_emit_rows<<<grid_for(n_cand, 256, 16), 256, 0, s>>>(items_k, k, cand_p, cand_cnt, n_cand, thr, out_off, off2,
-                                                          wnew, items_n, counts_n, par_n, rowptr_n, roww_n);
-    KMLS_LAUNCHED("k_emit_rows");
+    {
+      ProfScope ps("k_emit_rows", s, 16.0 * (double)n_cand + (double)n_next * (4.0 * (2 * k + 1) + 20.0), k + 1);
+      k_emit_rows<<<grid_for(n_cand, 256, 16), 256, 0, s>>>(items_k, k, cand_p, cand_cnt, n_cand, thr, out_off, off2,
+                                                            wnew, items_n, counts_n, par_n, rowptr_n, roww_n);
+      KMLS_LAUNCHED("k_emit_rows");
+    }
     ++M.launches;
+    if (rec_cp >= 0) {   // rows written by k_count_project = widths of the new itemsets that own a row
+      unsigned long long h = 0;
+      KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
+      k_sum_i32<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, n_next, (unsigned long long*)(flags + 6));
+      KMLS_LAUNCHED("k_sum_i32");
+      KMLS_CUDA(cudaMemcpyAsync(&h, flags + 6, 8, cudaMemcpyDeviceToHost, s));
+      KMLS_TRY(M.sync());
+      profiler().records[rec_cp].work += 4.0 * (double)h;
+    }
     // this level's scratch and the previous level's rows are done with (stream order)
     M.ws.release(ncand);
     M.ws.release(wnew);

@@ -14,6 +14,7 @@
 
 #include "common.cuh"
 #include "kmls_b200.h"
+#include "profile.cuh"
 #include "workspace.cuh"
 
 namespace kmls {
@@ -116,7 +117,10 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
   // ---- subset index
   void* nodes = nullptr;
   KMLS_TRY(H.take((char**)&nodes, n_all * 16, true, "the subset index"));
-  KMLS_TRY(kmls_trie_index_build(a_items, a_counts, a_par, sizes, max_k, nodes, s));
+  {
+    ProfScope ps("k_trie_build", s, 28.0 * (double)n_all, 0);
+    KMLS_TRY(kmls_trie_index_build(a_items, a_counts, a_par, sizes, max_k, nodes, s));
+  }
   int64_t launches = 1;
 
   // ---- this part's slice of the table, cut by work (2^(k-1) splits per k-itemset)
@@ -187,9 +191,17 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
       const Lvl& L = plan[i];
       int32_t* sub = nullptr;
       KMLS_TRY(H.take(&sub, L.count * (L.k - 1), true, "the subset links of pass 1"));
-      KMLS_TRY(kmls_rules_subsets(a_items, a_par, sizes, max_k, L.k, nodes, sub_prev, sub, missing, s));
-      KMLS_TRY(kmls_rules_count_gather(a_items, a_counts, a_par, sizes, max_k, L.k, sub, part_prev, n_total,
-                                       min_confidence, L.part_buf, rule_cnt + L.out0, missing, s));
+      {
+        // one index lookup (32 B) + 4 B written per (itemset, dropped member)
+        ProfScope ps("k_rules_subsets", s, 36.0 * (double)L.count * (L.k - 1), L.k);
+        KMLS_TRY(kmls_rules_subsets(a_items, a_par, sizes, max_k, L.k, nodes, sub_prev, sub, missing, s));
+      }
+      {
+        // two 4-byte counts read + 8 bytes written per split
+        ProfScope ps("k_rules_gather", s, 16.0 * (double)L.count * (double)((int64_t)1 << (L.k - 1)), L.k);
+        KMLS_TRY(kmls_rules_count_gather(a_items, a_counts, a_par, sizes, max_k, L.k, sub, part_prev, n_total,
+                                         min_confidence, L.part_buf, rule_cnt + L.out0, missing, s));
+      }
       launches += 2;
       H.ws.release(sub_prev);          // stream order: the kernels that read it are already enqueued
       sub_prev = sub;
@@ -199,6 +211,8 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
   } else {
     for (int i = 0; i < n_plan; ++i) {
       const Lvl& L = plan[i];
+      // 8 bytes written per split + one 32-byte index lookup per (itemset, antecedent) probe
+      ProfScope ps("k_rules_count", s, 40.0 * (double)L.count * (double)((int64_t)1 << (L.k - 1)), L.k);
       KMLS_TRY(kmls_rules_count(a_items, a_counts, sizes, max_k, L.k, L.begin, L.count, nodes, n_total,
                                 min_confidence, L.part_buf, rule_cnt + L.out0, missing, s));
       ++launches;
@@ -234,8 +248,18 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
                 "kmls_rules: workspace too small for the rule table: %lld rules need %zu bytes in total, %zu given "
                 "(nothing was truncated)", (long long)n_rules, R->workspace_needed_bytes, workspace_bytes);
   if (n_rules) {
+    int64_t lvl_rules[KMLS_MAX_LEVELS + 3] = {0};
+    if (profiler().on) {   // rules per level, for the work figure of pass 2
+      for (int i = 0; i < n_plan; ++i)
+        KMLS_CUDA(cudaMemcpyAsync(&lvl_rules[i], rule_off + plan[i].out0, 8, cudaMemcpyDeviceToHost, s));
+      KMLS_CUDA(cudaStreamSynchronize(s));
+      lvl_rules[n_plan] = n_rules;
+    }
     for (int i = 0; i < n_plan; ++i) {
       const Lvl& L = plan[i];
+      // 8 bytes read per split + 24 bytes written per kept rule
+      ProfScope ps("k_rules_write", s, 8.0 * (double)L.count * (double)((int64_t)1 << (L.k - 1)) +
+                                           24.0 * (double)(lvl_rules[i + 1] - lvl_rules[i]), L.k);
       KMLS_TRY(kmls_rules_write(a_counts, sizes, max_k, L.k, L.begin, L.count, n_total, min_confidence, L.part_buf,
                                 rule_off + L.out0, o_rule, o_conf, o_lift, missing + 1, s));
       ++launches;

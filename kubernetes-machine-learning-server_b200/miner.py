@@ -276,12 +276,14 @@ class Workspace:
             self.buf = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
         return self.buf
 
-    def grow(self):
-        """Double (bounded by what the device can still give); False when that is no growth."""
+    def grow(self, to: Optional[int] = None):
+        """Double, or grow to ``to`` bytes (bounded by what the device can still give); False
+        when that is no growth."""
         free = torch.cuda.mem_get_info(self.device)[0] + torch.cuda.memory_reserved(self.device) \
             - torch.cuda.memory_allocated(self.device)
         have = self.nbytes
-        want = min(max(2 * have, 1 << 30), int(0.92 * (free + have)))
+        want = max(2 * have, 1 << 30) if to is None else int(to)
+        want = min(want, int(0.95 * (free + have)))
         if want <= have:
             return False
         self.ensure(want)
@@ -293,6 +295,7 @@ class Workspace:
 
 
 _PAIR_IMPL = {"auto": 0, "csr": 1, "popc": 2, "i8": 3}
+_SIZE_HINT = {}   # (device index, "mine" | "rules") -> bytes the last call needed: first guess of the next
 
 
 def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_support: float, *,
@@ -327,8 +330,9 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
     if host_tables is not None:
         opt.h_tables, opt.h_tables_bytes = host_tables.data_ptr(), int(host_tables.numel())
     ws = workspace if workspace is not None else Workspace(device)
+    hint_key = (device.index, "mine")
     if ws.nbytes == 0:
-        ws.ensure(max(1 << 30, 48 * int(items.numel())))
+        ws.ensure(max(1 << 28, 48 * int(items.numel()), _SIZE_HINT.get(hint_key, 0)))
     out = _lib.MineResultC()
     while True:
         rc, msg = _lib.call_rc("kmls_mine", offsets, items, n_local, int(n_items), n_total, t1, tk, opt,
@@ -340,6 +344,7 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
             continue
         raise _lib.KmlsError(f"kmls_mine failed with code {rc}: {msg}")
     _lib.EXTRA_LAUNCHES += int(out.kernel_launches) - 1
+    _SIZE_HINT[hint_key] = max(_SIZE_HINT.get(hint_key, 0), int(out.workspace_peak_bytes * 1.1) + (1 << 20))
     stats = {"levels": [], "t1": t1, "tk": tk, "thr_k": int(out.thr_k), "n_playlists": n_total,
              "nnz_local": int(items.numel()), "workspace_peak_bytes": int(out.workspace_peak_bytes),
              "pair_impl": {v: k for k, v in _PAIR_IMPL.items()}.get(int(out.pair_impl_used)),
@@ -629,6 +634,8 @@ class RuleTable:
     arena_counts: Optional[torch.Tensor] = None
     n_playlists: int = 0
     _support: Optional[torch.Tensor] = None
+    workspace: Optional[object] = None     # keeps the native path's device memory alive
+    stats: Optional[dict] = None
 
     @property
     def n_rules(self) -> int:
@@ -653,8 +660,98 @@ class RuleTable:
         return self._support
 
 
+def _tables_as_c(res: MineResult) -> "_lib.MineResultC":
+    """A kmls_mine_result naming the tables of ``res`` by ABSOLUTE device address (to be used
+    with a NULL base): works for tables from any source (kmls_mine, the Python loop, a merged
+    multi-GPU result)."""
+    c = _lib.MineResultC()
+    c.n_playlists_total = int(res.n_playlists)
+    c.t1, c.tk = int(res.t1), int(res.tk)
+    c.max_k = len(res.levels)
+    c.n_rows = int(res.row_items.numel())
+    for k, (it, ct) in enumerate(res.levels, start=1):
+        assert it.is_contiguous() and ct.is_contiguous() and it.dtype == torch.int32 and ct.dtype == torch.int32
+        c.level_size[k] = int(ct.numel())
+        c.items_off[k] = it.data_ptr() if ct.numel() else -1
+        c.counts_off[k] = ct.data_ptr() if ct.numel() else -1
+        if k >= 2:
+            par = res.parents[k - 2]
+            assert par.is_contiguous() and par.dtype == torch.int32
+            c.parent_off[k] = par.data_ptr() if ct.numel() else -1
+    return c
+
+
+_PASS1 = {"auto": 0, "gather": 1, "search": 2}
+
+
 def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_000_000_000,
-                   part: Tuple[int, int] = (0, 1), pass1: str = "auto") -> RuleTable:
+                   part: Tuple[int, int] = (0, 1), pass1: str = "auto",
+                   workspace: Optional[Workspace] = None, impl: str = "native") -> RuleTable:
+    """fp64 confidence/lift for every (itemset, antecedent) split, kept iff
+    confidence >= min_confidence (mlxtend ``association_rules`` semantics), through ONE call
+    into the library (``kmls_rules``; ``impl="python"`` = the kernel-by-kernel loop below it).
+    ``part = (i, n)`` generates only the rules of the i-th of n contiguous slices of the
+    itemset table (how ranks of a multi-GPU job divide the rule table among themselves).
+    ``pass1``: how the subset counts of a split are found - "gather" (from the previous level's
+    pass-1 output; needs the whole table, i.e. ``part == (0, 1)``), "search" (in the subset
+    index; works on any slice), "auto" = gather when possible. ``workspace``: device memory for
+    the call (the returned columns are views of it); grown and the call repeated when too small."""
+    if impl != "native":
+        return generate_rules_python(res, min_confidence, max_rules, part, pass1)
+    if pass1 not in _PASS1:
+        raise ValueError(f"unknown pass1 {pass1!r}")
+    if pass1 == "gather" and tuple(part) != (0, 1):
+        raise ValueError("pass1='gather' needs the whole table on this GPU (part=(0, 1))")
+    device = res.row_items.device
+    sizes = [0] + [int(ct.numel()) for _, ct in res.levels]
+    e_i32 = torch.empty(0, dtype=torch.int32, device=device)
+    e_f64 = torch.empty(0, dtype=torch.float64, device=device)
+    if len(res.levels) < 2 or sum(sizes[2:]) == 0:
+        arena = torch.cat([it.reshape(-1) for it, _ in res.levels]) if res.levels else e_i32
+        return RuleTable(e_i32.view(0, 2), e_f64, e_f64, arena, sizes + [0], None, res.n_playlists)
+    if len(res.levels) > 15:
+        raise _lib.KmlsError(f"rule generation supports itemsets of at most 15 members, got {len(res.levels)}")
+    mined = _tables_as_c(res)
+    ws = workspace if workspace is not None else Workspace(device)
+    hint_key = (device.index, "rules")
+    if ws.nbytes == 0:
+        n_all = sum(sizes)
+        splits = sum(sizes[k] << (k - 1) for k in range(2, len(sizes))) // max(part[1], 1)
+        guess = 4 * sum(sizes[k] * k for k in range(1, len(sizes))) + 28 * n_all + 32 * splits + (64 << 20)
+        free = torch.cuda.mem_get_info(device)[0] + torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
+        ws.ensure(min(max(guess, _SIZE_HINT.get(hint_key, 0)), int(0.9 * free)))
+    out = _lib.RulesResultC()
+    while True:
+        rc, msg = _lib.call_rc("kmls_rules", mined, 0, float(min_confidence), int(part[0]), int(part[1]),
+                               _PASS1[pass1], int(max_rules), ws.buf, ws.nbytes, out, _stream())
+        _lib.CALLS["kmls_rules"] = _lib.CALLS.get("kmls_rules", 0) + 1
+        if rc == 0:
+            break
+        if rc == -2 and "workspace too small" in msg and ws.grow(int(out.workspace_needed_bytes * 1.02) + (16 << 20)
+                                                                  if out.workspace_needed_bytes else None):
+            continue
+        raise _lib.KmlsError(f"kmls_rules failed with code {rc}: {msg}")
+    _lib.EXTRA_LAUNCHES += int(out.kernel_launches) - 1
+    _SIZE_HINT[hint_key] = max(_SIZE_HINT.get(hint_key, 0), int(out.workspace_peak_bytes * 1.02) + (16 << 20))
+    n_rules = int(out.n_rules)
+    if n_rules == 0 and int(out.rule_off) < 0:
+        arena = torch.cat([it.reshape(-1) for it, _ in res.levels])
+        return RuleTable(e_i32.view(0, 2), e_f64, e_f64, arena, sizes + [0], torch.cat([ct for _, ct in res.levels]),
+                         res.n_playlists)
+    n_members = sum(sizes[k] * k for k in range(1, len(sizes)))
+    table = RuleTable(ws.view(int(out.rule_off), 2 * n_rules, torch.int32).view(n_rules, 2),
+                      ws.view(int(out.confidence_off), n_rules, torch.float64),
+                      ws.view(int(out.lift_off), n_rules, torch.float64),
+                      ws.view(int(out.arena_items_off), n_members, torch.int32), sizes + [0],
+                      ws.view(int(out.arena_counts_off), sum(sizes), torch.int32), res.n_playlists)
+    table.workspace = ws
+    table.stats = {"n_splits": int(out.n_splits), "pass1": {1: "gather", 2: "search"}.get(int(out.pass1_used)),
+                   "workspace_peak_bytes": int(out.workspace_peak_bytes)}
+    return table
+
+
+def generate_rules_python(res: MineResult, min_confidence: float, max_rules: int = 4_000_000_000,
+                          part: Tuple[int, int] = (0, 1), pass1: str = "auto") -> RuleTable:
     """fp64 confidence/lift for every (itemset, antecedent) split, kept iff
     confidence >= min_confidence (mlxtend ``association_rules`` semantics).
     ``part = (i, n)`` generates only the rules of the i-th of n contiguous slices of the

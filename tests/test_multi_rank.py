@@ -75,7 +75,7 @@ def test_sharded_counts_sum_to_global_counts_gloo():
     assert out.get(timeout=5) is True
 
 
-def _gpu_worker(rank, world, port, out):
+def _gpu_worker(rank, world, port, out, partition):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     torch.cuda.set_device(rank)
@@ -84,31 +84,36 @@ def _gpu_worker(rank, world, port, out):
     from kmls_b200 import miner, synth
     n, t, s, conf = 30011, 900, 0.01, 0.5
     off, ids = synth.zipf_playlists(n, t, mean_draws=30, alpha=0.9, seed=17)
-    res, _ = kmls_b200.mine_ids(off, ids, t, s)            # shards by rank internally
-    rules = miner.generate_rules(res, conf, part=(rank, world))
+    # every rank passes the whole set: "classes" splits the candidate space, "playlists" the rows
+    res, rules = kmls_b200.mine_ids(off, ids, t, s, conf, split_rules=True, partition=partition)
     got = res.as_dict()
-    n_rules = torch.tensor([rules.n_rules], dtype=torch.int64, device="cuda")
-    dist.all_reduce(n_rules)
+    tables = [(it.cpu().numpy(), ct.cpu().numpy()) for it, ct in res.levels]
+    parents = [p.cpu().numpy() for p in res.parents]
+    cs = miner.rule_checksum(res, rules)
+    t_ = torch.tensor([rules.n_rules, cs - (1 << 64) if cs >= (1 << 63) else cs], dtype=torch.int64, device="cuda")
+    dist.all_reduce(t_)
     if rank == 0:
-        out.put((got, int(n_rules.item())))
+        out.put((got, int(t_[0].item()), int(t_[1].item()) & ((1 << 64) - 1), tables, parents,
+                 (res.stats or {}).get("partition")))
     dist.destroy_process_group()
 
 
 @pytest.mark.gpu
-def test_two_gpus_give_the_single_gpu_result():
+@pytest.mark.parametrize("partition", ["classes", "playlists"])
+def test_two_gpus_give_the_single_gpu_result(partition):
     if torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     sys.path.insert(0, ROOT)
     import kmls_b200
-    from kmls_b200 import synth
+    from kmls_b200 import miner, synth
     from oracle import fpgrowth_c, mlxtend_restated as M
     ctx = mp.get_context("spawn")
     out = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_gpu_worker, args=(r, 2, port, out)) for r in range(2)]
+    procs = [ctx.Process(target=_gpu_worker, args=(r, 2, port, out, partition)) for r in range(2)]
     for p in procs:
         p.start()
-    got, n_rules = out.get(timeout=300)
+    got, n_rules, rule_cs, tables, parents, part_info = out.get(timeout=300)
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
@@ -118,3 +123,13 @@ def test_two_gpus_give_the_single_gpu_result():
     ref = fpgrowth_c.fpgrowth(off, ids, t, t1, tk, rules_min_confidence=conf)
     assert got == ref.as_dict()
     assert n_rules == ref.n_rules
+    assert rule_cs == ref.rule_checksum
+    # the merged tables are the single-GPU tables, entry for entry (order and parent links included)
+    one, _ = kmls_b200.mine_ids(off, ids, t, s)
+    assert len(tables) == len(one.levels)
+    for (it, ct), (it1, ct1) in zip(tables, one.levels):
+        assert (it == it1.cpu().numpy()).all() and (ct == ct1.cpu().numpy()).all()
+    for p2, p1 in zip(parents, one.parents):
+        assert (p2 == p1.cpu().numpy()).all()
+    if partition == "classes":
+        assert part_info and part_info["world"] == 2

@@ -169,3 +169,57 @@ def test_golden_through_ctypes_alone(g):
                                          base + out.row_items_off, cs.data_ptr(),
                                          torch.cuda.current_stream().cuda_stream) == 0
     assert str(int(cs.item()) & ((1 << 64) - 1)) == g["itemset_checksum"]
+
+
+# ------------------------------------------------------------------ kmls_rules (one call)
+@pytest.mark.parametrize("pass1", ["gather", "search"])
+def test_rules_one_call_equals_kernel_by_kernel_loop(pass1):
+    off, items = synth.zipf_playlists(20000, 2000, mean_draws=35, alpha=1.0, seed=21)
+    d_off, d_items = to_dev(off, items)
+    res = miner.mine_native(d_off, d_items, 2000, 0.008)
+    a = miner.generate_rules(res, 0.3, pass1=pass1)
+    b = miner.generate_rules_python(res, 0.3, pass1=pass1)
+    assert a.n_rules == b.n_rules > 1000
+    assert torch.equal(a.rule, b.rule) and torch.equal(a.confidence, b.confidence) and torch.equal(a.lift, b.lift)
+    assert miner.rule_checksum(res, a) == miner.rule_checksum(res, b)
+    t1, tk = M.thresholds(0.008, 20000)
+    ref = fpgrowth_c.fpgrowth(off, items, 2000, t1, tk, rules_min_confidence=0.3)
+    assert a.n_rules == ref.n_rules and miner.rule_checksum(res, a) == ref.rule_checksum
+    assert miner.itemset_checksum(res) == ref.checksum
+
+
+def test_rules_one_call_slices_add_up_and_workspace_grows():
+    off, items = synth.zipf_playlists(20000, 2000, mean_draws=35, alpha=1.0, seed=21)
+    d_off, d_items = to_dev(off, items)
+    res = miner.mine_native(d_off, d_items, 2000, 0.008)
+    whole = miner.generate_rules(res, 0.3)
+    total, cs = 0, 0
+    for part in range(3):
+        ws = miner.Workspace(dev(), 1 << 16)                  # too small: grown to what the call says it needs
+        r = miner.generate_rules(res, 0.3, part=(part, 3), workspace=ws)
+        assert ws.nbytes > (1 << 16)
+        total += r.n_rules
+        cs = (cs + miner.rule_checksum(res, r)) & ((1 << 64) - 1)
+    assert total == whole.n_rules and cs == miner.rule_checksum(res, whole)
+    with pytest.raises(_lib.KmlsError, match="max_rules"):
+        miner.generate_rules(res, 0.3, max_rules=10)
+    # the bare C call: a capacity error that names the bytes needed
+    small = torch.empty(1 << 16, dtype=torch.uint8, device=dev())
+    out = _lib.RulesResultC()
+    rc, msg = _lib.call_rc("kmls_rules", miner._tables_as_c(res), 0, 0.3, 0, 1, 0, 0, small, small.numel(), out,
+                           torch.cuda.current_stream().cuda_stream)
+    assert rc == -2 and "workspace too small" in msg
+
+
+def test_profile_report_names_the_kernels():
+    off, items = synth.zipf_playlists(9000, 700, mean_draws=30, alpha=0.9, seed=31)
+    d_off, d_items = to_dev(off, items)
+    _lib.profile_begin()
+    res = miner.mine_native(d_off, d_items, 700, 0.012)
+    miner.generate_rules(res, 0.3)
+    rec = _lib.profile_report()
+    names = {r[0] for r in rec}
+    assert {"k_encode_bitmap", "k_count_project", "k_emit_rows", "k_rules_gather", "k_rules_write"} <= names
+    assert all(ms >= 0 for _, _, ms, _ in rec)
+    assert any(nm == "k_count_project" and work > 0 for nm, _, _, work in rec)
+    assert miner.mine_native(d_off, d_items, 700, 0.012).as_dict() == res.as_dict()   # profiling off again: same result
