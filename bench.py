@@ -560,6 +560,17 @@ def run_gpu(args):
             lv, (ms_l, w_l) = max(d["levels"].items(), key=lambda kv: kv[1][0])
             r["largest_launch"] = {"level": lv, "ms": ms_l / args.steps, "algorithmic_work": w_l / args.steps,
                                    "achieved": w_l / max(ms_l, 1e-9) / (1e9 if bound == "tensor" else 1e6)}
+        if nm == "k_pair_counts_csr":
+            # this kernel is bound by the rate at which L2 retires counter updates (RED.ADD), not by
+            # bytes: quote it against the micro-benchmark's rate as well (tools/redg_peak.py)
+            r["atomic_updates_per_s"] = work / 4.0 / sec
+            try:
+                pk_a = json.load(open(os.path.join(ROOT, "profiles", "r2_redg_peak.json")))["peak_updates_per_s"]
+                r["atomic_peak_updates_per_s"] = pk_a
+                r["atomic_frac"] = r["atomic_updates_per_s"] / pk_a
+                r["atomic_peak_source"] = "profiles/r2_redg_peak.json (tools/redg_peak.py, uniform scatter)"
+            except (OSError, ValueError, KeyError):
+                pass
         t = ncu_traffic.get(nm)
         if t and name == t.get("workload", "zipf_1Mx100k_s0.001") and world == 1:
             r["traffic"] = t["traffic_bytes"]

@@ -99,6 +99,20 @@ int kmls_pair_select(const int32_t* d_pair, int32_t n_rows, int32_t thr, int64_t
                      int64_t* d_row_off, int32_t* d_items2, int32_t* d_counts,
                      kmls_stream_t stream);
 
+/* The fold of main.py:282-296 as a CSR, from the frequent-pair table (d_items2[n_pairs][2]
+ * bitmap rows, d_counts2[n_pairs]): the entries of row r (track d_row_items[r]) are
+ * d_indptr[r] .. d_indptr[r+1]-1; entry e says "d_other[e] (a TRACK ID) occurs with this track
+ * in a frequent pair of support d_support[e] = count / N". Both directions of every pair are
+ * present (2 * n_pairs entries); inside a row entries are ordered by support descending, ties
+ * by track id ascending, so that the dict the host builds from it (and rest_api's stable
+ * top-K over it, rest_api/app/main.py:250) is deterministic. d_indptr[n_rows + 1],
+ * d_other / d_support[2 * n_pairs]; d_scratch: kmls_pair_map_scratch_bytes() bytes, 256-aligned. */
+size_t kmls_pair_map_scratch_bytes(int64_t n_pairs, int32_t n_rows);
+int kmls_pair_map(const int32_t* d_items2, const int32_t* d_counts2, int64_t n_pairs,
+                  const int32_t* d_row_items, int32_t n_rows, int64_t n_playlists_total,
+                  int64_t* d_indptr, int32_t* d_other, double* d_support, void* d_scratch,
+                  size_t scratch_bytes, kmls_stream_t stream);
+
 /* fpcommon.generate_itemsets: support = count / N (IEEE double division). */
 int kmls_supports_f64(const int32_t* d_counts, int64_t n, int64_t n_playlists_total,
                       double* d_out, kmls_stream_t stream);
@@ -447,6 +461,11 @@ int kmls_place_level(const int32_t* d_items, const int32_t* d_counts, const int3
  * capacity bytes, NUL-terminated); returns the bytes the full report needs. The work figure is
  * the algorithmic bytes of the launch as DESIGN.md section 3 defines them (operations for the
  * tensor-core GEMM). */
+/* Measurement plumbing: n_updates 32-bit RED.ADD updates scattered uniformly over
+ * d_buf[n_words] - the micro-benchmark that gives k_pair_counts_csr's roofline its peak
+ * (counter updates per second; tools/redg_peak.py times it). */
+int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_updates, uint64_t seed,
+                         kmls_stream_t stream);
 int kmls_profile_begin(void);
 int64_t kmls_profile_report(char* buf, size_t capacity);
 

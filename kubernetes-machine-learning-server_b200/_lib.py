@@ -28,6 +28,8 @@ SIGNATURES = {
     "kmls_pair_gemm_scratch_bytes": (_SZ, [_I32, _I64]),
     "kmls_pair_counts_i8": (ctypes.c_int, [_P, _I32, _I64, _P, _P, _SZ, _P]),
     "kmls_pair_select": (ctypes.c_int, [_P, _I32, _I32, _I64, _P, _P, _P, _P]),
+    "kmls_pair_map_scratch_bytes": (_SZ, [_I64, _I32]),
+    "kmls_pair_map": (ctypes.c_int, [_P, _P, _I64, _P, _I32, _I64, _P, _P, _P, _P, _SZ, _P]),
     "kmls_supports_f64": (ctypes.c_int, [_P, _I64, _I64, _P, _P]),
     "kmls_scan_scratch_bytes": (_SZ, [_I64]),
     "kmls_exclusive_scan_i32": (ctypes.c_int, [_P, _I64, _P, _P, _SZ, _P]),
@@ -63,6 +65,7 @@ SIGNATURES = {
     "kmls_rules": (ctypes.c_int, [_P, _P, _F64, _I32, _I32, _I32, _I64, _P, _SZ, _P, _P]),
     "kmls_subtree_roots": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
     "kmls_place_level": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
+    "kmls_redg_microbench": (ctypes.c_int, [_P, _I64, _I64, ctypes.c_uint64, _P]),
     "kmls_profile_begin": (ctypes.c_int, []),
     "kmls_profile_report": (_I64, [_P, _SZ]),
     "kmls_rule_division_selftest": (ctypes.c_int, [_I64, _I64, ctypes.c_uint64, _P, _P]),

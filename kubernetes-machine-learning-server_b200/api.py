@@ -248,27 +248,44 @@ def rules_to_pinned(rules: miner.RuleTable, cache: Optional[dict] = None, piece:
     return out[0].numpy().reshape(-1, 2), out[1].numpy(), out[2].numpy()
 
 
+def pair_map_csr(res: miner.MineResult):
+    """The fold's content as host arrays, built on the device (``kmls_pair_map``): ``(rows,
+    indptr, other, support)``: ``rows[r]`` = track id of bitmap row r; the entries of row r are
+    ``indptr[r]:indptr[r+1]``; ``other`` = the co-occurring TRACK id, ``support`` = count / N;
+    inside a row ordered by support descending, ties by track id."""
+    device = res.row_items.device
+    n_rows = int(res.row_items.numel())
+    rows = res.row_items.cpu().numpy()
+    n2 = int(res.levels[1][1].numel()) if len(res.levels) >= 2 else 0
+    if n_rows == 0 or n2 == 0:
+        return rows, np.zeros(n_rows + 1, np.int64), np.zeros(0, np.int32), np.zeros(0, np.float64)
+    it2, ct2 = res.levels[1]
+    indptr = torch.empty(n_rows + 1, dtype=torch.int64, device=device)
+    other = torch.empty(2 * n2, dtype=torch.int32, device=device)
+    support = torch.empty(2 * n2, dtype=torch.float64, device=device)
+    nbytes = int(_lib.value("kmls_pair_map_scratch_bytes", n2, n_rows))
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=device)
+    _lib.call("kmls_pair_map", it2, ct2, n2, res.row_items, n_rows, res.n_playlists, indptr, other, support,
+              scratch, nbytes, torch.cuda.current_stream().cuda_stream)
+    return rows, indptr.cpu().numpy(), other.cpu().numpy(), support.cpu().numpy()
+
+
 def recommendations_from_result(res: miner.MineResult, columns: Sequence[str]
                                 ) -> Dict[str, Dict[str, float]]:
     """The fold of main.py:282-296 from the level-1 and level-2 tables: every frequent single
     name is a key (possibly with an empty dict) and d[a][b] = support({a, b}),
-    which is what the reference's max over all itemsets containing both evaluates to."""
+    which is what the reference's max over all itemsets containing both evaluates to. The
+    pairs arrive as a CSR sorted on the device (``pair_map_csr``), so the dict is two array
+    walks: keys in the caller's column order, each inner dict in support-descending order
+    (ties by name) - plain ``dict/str/float`` only, as rest_api's image has no numpy."""
+    rows, indptr, other, support = pair_map_csr(res)
+    names = np.asarray(list(columns), dtype=object)
+    other_names = names[other].tolist() if len(other) else []
+    support = support.tolist()
     out: Dict[str, Dict[str, float]] = {}
-    rows = res.row_items.cpu().numpy()
-    names = [columns[i] for i in rows]
-    # iterate singles in the caller's column order for a stable key order
-    for r in np.argsort(rows, kind="stable"):
-        out[names[r]] = {}
-    if len(res.levels) >= 2:
-        it2, ct2 = res.levels[1]
-        sup = torch.empty(ct2.numel(), dtype=torch.float64, device=ct2.device)
-        _lib.call("kmls_supports_f64", ct2, int(ct2.numel()), res.n_playlists, sup,
-                  torch.cuda.current_stream().cuda_stream)
-        it2 = it2.cpu().numpy()
-        sup = sup.cpu().numpy()
-        for (a, b), s in zip(it2.tolist(), sup.tolist()):
-            out[names[a]][names[b]] = s
-            out[names[b]][names[a]] = s
+    for r in np.argsort(rows, kind="stable").tolist():
+        lo, hi = int(indptr[r]), int(indptr[r + 1])
+        out[names[rows[r]]] = dict(zip(other_names[lo:hi], support[lo:hi]))
     return out
 
 
@@ -283,14 +300,45 @@ def itemsets_frame(res: miner.MineResult, columns: Sequence[str]) -> pd.DataFram
     })
 
 
+def rule_columns(res: miner.MineResult, rules: miner.RuleTable, cache: Optional[dict] = None) -> dict:
+    """The rule table as host columns without a Python loop over rules: ``ante_items`` /
+    ``ante_off`` and ``cons_items`` / ``cons_off`` (CSR of TRACK ids per rule, members in row
+    order), ``support``, ``confidence``, ``lift`` (float64). The three device columns come over
+    in pieces through pinned memory (``rules_to_pinned``), the member lists are expanded with
+    numpy from the itemset arena."""
+    n = rules.n_rules
+    rule, conf, lift = rules_to_pinned(rules, cache)
+    sup = rules.support.cpu().numpy() if n else np.zeros(0, np.float64)
+    rows = res.row_items.cpu().numpy()
+    arena = rules.arena_items.cpu().numpy()
+    sizes = np.asarray(rules.level_sizes, dtype=np.int64)
+    id_off = np.concatenate([[0], np.cumsum(sizes)])                 # id_off[k] = first global id of level k
+    item_off = np.concatenate([[0], np.cumsum(sizes * np.arange(len(sizes)))])
+    gid = rule[:, 0].astype(np.int64)
+    mask = rule[:, 1].astype(np.int64)
+    k = np.searchsorted(id_off, gid, side="right") - 1               # itemset size of every rule
+    base = item_off[k] + (gid - id_off[k]) * k                       # first member in the arena
+    # expand to one entry per (rule, member)
+    rep = np.repeat(np.arange(n, dtype=np.int64), k)
+    first = np.concatenate([[0], np.cumsum(k)])[:-1] if n else np.zeros(0, np.int64)
+    t = np.arange(int(k.sum()), dtype=np.int64) - np.repeat(first, k)   # member position inside its itemset
+    member = rows[arena[np.repeat(base, k) + t]]
+    in_ante = ((np.repeat(mask, k) >> t) & 1).astype(bool)
+    n_ante = np.bincount(rep[in_ante], minlength=n).astype(np.int64) if n else np.zeros(0, np.int64)
+    return {"ante_items": member[in_ante].astype(np.int32), "ante_off": np.concatenate([[0], np.cumsum(n_ante)]),
+            "cons_items": member[~in_ante].astype(np.int32), "cons_off": np.concatenate([[0], np.cumsum(k - n_ante)]),
+            "support": sup, "confidence": np.array(conf, copy=True), "lift": np.array(lift, copy=True)}
+
+
 def rules_frame(res: miner.MineResult, rules: miner.RuleTable, columns: Sequence[str]) -> pd.DataFrame:
-    rows = miner.rules_to_host(res, rules)
+    c = rule_columns(res, rules)
+    names = np.asarray(list(columns), dtype=object)
+    an, cn = names[c["ante_items"]], names[c["cons_items"]]
+    ao, co = c["ante_off"], c["cons_off"]
     return pd.DataFrame({
-        "antecedents": [frozenset(columns[i] for i in a) for a, _, _, _, _ in rows],
-        "consequents": [frozenset(columns[i] for i in c) for _, c, _, _, _ in rows],
-        "support": [s for _, _, s, _, _ in rows],
-        "confidence": [c for _, _, _, c, _ in rows],
-        "lift": [l for _, _, _, _, l in rows],
+        "antecedents": [frozenset(an[ao[r]:ao[r + 1]]) for r in range(len(c["support"]))],
+        "consequents": [frozenset(cn[co[r]:co[r + 1]]) for r in range(len(c["support"]))],
+        "support": c["support"], "confidence": c["confidence"], "lift": c["lift"],
     })
 
 
@@ -408,20 +456,31 @@ def sweep_supports(playlist_dict: dict, supports: Iterable[float], total_songs=N
     return out
 
 
+def filter_best_tracks(track_infos: List[dict], percentile: Optional[float] = None) -> List[dict]:
+    """``filter_best_tracks`` (main.py:177-184): the first ``len * TOP_TRACKS_SAVE_PERCENTILE``
+    entries of the frequency-sorted list (env knob of main.py:47, default 0.03)."""
+    p = float(os.getenv("TOP_TRACKS_SAVE_PERCENTILE", 0.03)) if percentile is None else percentile
+    return track_infos[:int(len(track_infos) * p)]
+
+
 def save_rules(path: str, result: Optional[dict] = None) -> None:
     """Write the extra rule artifact: a dict of plain-Python columns ``antecedents``,
-    ``consequents`` (tuples of names), ``support``, ``confidence``, ``lift`` (floats),
-    loadable without numpy/torch. rest_api ignores it."""
+    ``consequents`` (tuples of names, sorted), ``support``, ``confidence``, ``lift`` (floats),
+    loadable without numpy/torch. rest_api ignores it. Built from ``rule_columns`` (numpy);
+    the only per-rule Python work is making the tuples the pickle consists of. Tables beyond
+    the host-memory bound of ``rules_to_pinned`` are refused, never truncated."""
     result = result or last_result
     if result is None or result.get("rules") is None:
         raise ValueError("no rule table to save: run calculate_and_save_fp_growth_fast first")
-    df = rules_frame(result["itemsets"], result["rules"], result["columns"])
+    c = rule_columns(result["itemsets"], result["rules"])
+    names = np.asarray(list(result["columns"]), dtype=object)
+    an, cn = names[c["ante_items"]].tolist(), names[c["cons_items"]].tolist()
+    ao, co = c["ante_off"].tolist(), c["cons_off"].tolist()
+    n = len(c["support"])
     data = {
-        "antecedents": [tuple(sorted(a)) for a in df["antecedents"]],
-        "consequents": [tuple(sorted(c)) for c in df["consequents"]],
-        "support": [float(x) for x in df["support"]],
-        "confidence": [float(x) for x in df["confidence"]],
-        "lift": [float(x) for x in df["lift"]],
+        "antecedents": [tuple(sorted(an[ao[r]:ao[r + 1]])) for r in range(n)],
+        "consequents": [tuple(sorted(cn[co[r]:co[r + 1]])) for r in range(n)],
+        "support": c["support"].tolist(), "confidence": c["confidence"].tolist(), "lift": c["lift"].tolist(),
     }
     with open(path, "wb") as f:
         pickle.dump(data, f)

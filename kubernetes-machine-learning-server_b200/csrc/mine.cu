@@ -58,11 +58,12 @@ __global__ void k_post(const int64_t* a, const int64_t* b, const int32_t* c, con
   __threadfence_system();
 }
 
+// per parent: a = candidates, b = slot words, c = work units of the AND kernel (prefix-summed)
 struct I2 {
-  long long a, b;
+  long long a, b, c;
 };
 struct I2Sum {
-  __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.a + y.a, x.b + y.b}; }
+  __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.a + y.a, x.b + y.b, x.c + y.c}; }
 };
 
 // ---- level 1 helpers --------------------------------------------------------------------
@@ -145,7 +146,9 @@ k_pair_parents(const int32_t* __restrict__ items2, int64_t n2, int32_t* __restri
 __global__ void __launch_bounds__(256)
 k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
             const int32_t* __restrict__ counts, int64_t n, int keep_words, int n_parts, int part,
-            int part_block, int32_t* __restrict__ ncand, int32_t* __restrict__ wnew) {
+            int part_block, int32_t* __restrict__ ncand, int32_t* __restrict__ wnew,
+            int32_t* __restrict__ n_wide) {
+  int wide = 0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
     const int32_t w_old = roww[p];
     int32_t m = 0, w = 0;
@@ -165,124 +168,201 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
       }
       m = (int32_t)(lo - p);
       w = w_old <= keep_words ? w_old : ((((__ldg(counts + p) + 31) >> 5) + 3) & ~3);
+      if (m > 0 && w_old > keep_words) wide += (m + 7) >> 3;   // chunks of kChunk = 8 candidates
     }
     ncand[p] = m;
     wnew[p] = w;
   }
+  if (wide) atomicAdd(n_wide, wide);     // work units (parent, chunk) of the bit-extract route
 }
+
+constexpr int kUnitCands = 4;   // candidates of one parent per work unit of the AND kernel
 
 struct CandSlots {
   const int32_t* ncand;
   const int32_t* wnew;
+  const int32_t* roww;
+  int keep_words;
   __host__ __device__ I2 operator()(int64_t p) const {
     const long long m = ncand[p];
-    return I2{m, m * (long long)wnew[p]};
+    const long long units = (m > 0 && roww[p] <= keep_words) ? (m + kUnitCands - 1) / kUnitCands : 0;
+    return I2{m, m * (long long)wnew[p], units};
   }
 };
 
-__global__ void k_i2_total(const int32_t* ncand, const int32_t* wnew, int64_t n, I2* off2,
-                           volatile int64_t* box) {
-  I2 t{0, 0};
-  if (n > 0) {
-    const long long m = ncand[n - 1];
-    t = I2{off2[n - 1].a + m, off2[n - 1].b + m * (long long)wnew[n - 1]};
-  }
+__global__ void k_i2_total(CandSlots f, int64_t n, I2* off2, const int32_t* n_wide, volatile int64_t* box) {
+  I2 t{0, 0, 0};
+  if (n > 0) t = I2Sum()(off2[n - 1], f(n - 1));
   off2[n] = t;
   box[0] = t.a;
   box[1] = t.b;
+  box[2] = t.c;
+  box[3] = *n_wide;
   __threadfence_system();
 }
 
 __device__ __forceinline__ uint4 or4z() { return make_uint4(0u, 0u, 0u, 0u); }
 
+// ---------------------------------------------------------------------------------------
+// AND route as a list of work units. A unit = up to kUnitCands consecutive candidates of ONE
+// parent whose row is at most keep_words wide; k_expand_units writes, per unit, everything
+// the counting kernel needs as one 64-byte record, so that its dependent-load chain is
+// record -> rows (two latencies) instead of ids -> offsets -> pointers -> rows, and every
+// unit it touches has work (parents without candidates produce no unit).
+// ---------------------------------------------------------------------------------------
+struct __align__(16) Unit {
+  const uint32_t* rowp;             // row of the parent
+  uint32_t* dst;                    // slot of the unit's first candidate in the new arena
+  const uint32_t* rowq[kUnitCands]; // rows of the candidates (siblings p + 1 + i0 ...)
+  int32_t p;                        // parent
+  int32_t cand0;                    // number of the first candidate in the level's candidate list
+  int32_t mc_nv;                    // candidates in this unit << 16 | row width in 128-bit words
+  int32_t whole;                    // 1 = the unit holds ALL candidates of its parent
+};
+static_assert(sizeof(Unit) == 64, "Unit must be 64 bytes");
+
+__global__ void __launch_bounds__(256)
+k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
+               const int32_t* __restrict__ roww_old, const int32_t* __restrict__ ncand,
+               const I2* __restrict__ off2, int64_t n, int keep_words, uint32_t* __restrict__ arena_new,
+               Unit* __restrict__ units, int2* __restrict__ wide_list, int32_t* __restrict__ wide_fill) {
+  for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
+    const int m = ncand[p];
+    const int w = roww_old[p];
+    if (m == 0) continue;
+    if (w > keep_words) {       // bit-extract route: k_count_project walks this list (order is irrelevant)
+      const int chunks = (m + 7) >> 3;
+      const int base = atomicAdd(wide_fill, chunks);
+      for (int c = 0; c < chunks; ++c) wide_list[base + c] = make_int2((int32_t)p, c << 3);
+      continue;
+    }
+    const I2 o = off2[p];
+    const uint32_t* rowp = arena_old + rowptr_old[p];
+    for (int i0 = 0, u = 0; i0 < m; i0 += kUnitCands, ++u) {
+      Unit un;
+      un.rowp = rowp;
+      un.dst = arena_new + o.b + (int64_t)i0 * w;
+      const int mc = min(kUnitCands, m - i0);
+#pragma unroll
+      for (int t = 0; t < kUnitCands; ++t)
+        un.rowq[t] = t < mc ? arena_old + __ldg(rowptr_old + p + 1 + i0 + t) : rowp;
+      un.p = (int32_t)p;
+      un.cand0 = (int32_t)(o.a + i0);
+      un.mc_nv = (mc << 16) | (w >> 2);
+      un.whole = (m <= kUnitCands) ? 1 : 0;
+      uint4* d = reinterpret_cast<uint4*>(units + o.c + u);
+      const uint4* sv = reinterpret_cast<const uint4*>(&un);
+      d[0] = sv[0];
+      d[1] = sv[1];
+      d[2] = sv[2];
+      d[3] = sv[3];
+    }
+  }
+}
+
+// One warp per unit: row(p) and the unit's candidate rows are all in flight at once; AND,
+// popcount, warp reduction; the AND of a candidate that reaches the threshold is stored from
+// the registers it is in (rows of more than 128 words: the second half is formed again from
+// the L1-resident rows). When the unit holds all candidates of its parent and exactly one
+// survives, nothing is stored: an only child is never joined again (k_emit_rows gives it
+// width 0).
+__global__ void __launch_bounds__(256)
+k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_t* __restrict__ cand_cnt,
+            int32_t* __restrict__ cand_p) {
+  const int lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * 8;
+  for (int64_t ui = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); ui < n_units; ui += stride) {
+    const uint4* u4 = reinterpret_cast<const uint4*>(units + ui);
+    const uint4 d0 = __ldg(u4), d1 = __ldg(u4 + 1), d2 = __ldg(u4 + 2), d3 = __ldg(u4 + 3);
+    const uint4* rowp = reinterpret_cast<const uint4*>(((uint64_t)d0.y << 32) | d0.x);
+    uint4* dst = reinterpret_cast<uint4*>(((uint64_t)d0.w << 32) | d0.z);
+    const uint4* rq[kUnitCands] = {reinterpret_cast<const uint4*>(((uint64_t)d1.y << 32) | d1.x),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d1.w << 32) | d1.z),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d2.y << 32) | d2.x),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d2.w << 32) | d2.z)};
+    const int mc = (int)d3.z >> 16, nv = (int)d3.z & 0xffff;
+    const bool h0 = lane < nv, h1 = lane + 32 < nv;
+    const uint4 m0 = h0 ? ldg4(rowp + lane) : or4z();
+    uint4 r0[kUnitCands];
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) r0[t] = (h0 && t < mc) ? ldg4(rq[t] + lane) : or4z();
+    int cnt[kUnitCands];
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+      r0[t] = and4(r0[t], m0);
+      cnt[t] = popc4(r0[t]);
+    }
+    uint4 m1 = or4z();
+    if (nv > 32) {                               // warp-uniform
+      if (h1) m1 = ldg4(rowp + lane + 32);
+#pragma unroll
+      for (int t = 0; t < kUnitCands; ++t)
+        if (h1 && t < mc) cnt[t] += popc4(and4(ldg4(rq[t] + lane + 32), m1));
+    }
+    uint32_t surv = 0;
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+      cnt[t] = warp_sum(cnt[t]);
+      if (t < mc && cnt[t] >= thr) surv |= 1u << t;
+    }
+    if (lane < mc) {
+      int c = cnt[0];
+#pragma unroll
+      for (int t = 1; t < kUnitCands; ++t)
+        if (lane == t) c = cnt[t];
+      cand_cnt[d3.y + lane] = c;
+      cand_p[d3.y + lane] = (int32_t)d3.x;
+    }
+    if (surv == 0 || (d3.w && (surv & (surv - 1)) == 0)) continue;   // nobody, or an only child
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+      if ((surv >> t) & 1u) {                    // warp-uniform
+        uint4* d = dst + (size_t)t * nv;
+        if (h0) d[lane] = r0[t];
+        if (h1) d[lane + 32] = and4(ldg4(rq[t] + lane + 32), m1);
+      }
+    }
+  }
+}
+
 constexpr int kAndIlp = 4;   // candidates of a parent in flight per warp (AND route)
 constexpr int kChunk = 8;    // candidates of a parent handled together (bit-extract route)
+static_assert(kChunk == 8, "k_join_size and k_expand_units count chunks of 8");
 constexpr int kKeepWordsMax = 256;
 
-// Count + project, one warp per parent p (see the file header). Candidate i of p is its i-th
-// later sibling q = p + 1 + i; its number in the level's candidate list is off2[p].a + i and
-// its slot in the new arena starts at word off2[p].b + i * wnew[p].
-//
-// AND route (row(p) at most keep_words <= 256 words): row(p) sits in two uint4 registers per
-// lane; per candidate two 128-bit loads, AND, popcount, warp reduction; a surviving AND is
-// stored from the registers it is already in. A parent's FIRST survivor is held back until a
-// second one appears: an only child is never joined again, so its row is never written.
-//
-// Bit-extract route (wider rows): per chunk of up to 8 candidates, first the popcounts of
-// row(p) AND row(q) (128-bit loads, all rows of the chunk per mask block), then, for the
-// survivors only, new_row = row(q) with the columns where row(p) is 0 squeezed out: 32 mask
-// words per step, the compress network's move masks (Hacker's Delight 7-4) derived ONCE per
-// mask word for all survivors of the chunk, output words assembled in shared memory.
+// Count + project for parents whose rows are WIDER than keep_words, one warp per parent p (see
+// the file header). Candidate i of p is its i-th later sibling q = p + 1 + i; its number in the
+// level's candidate list is off2[p].a + i and its slot in the new arena starts at word
+// off2[p].b + i * wnew[p]. Per chunk of up to 8 candidates, first the popcounts of row(p) AND
+// row(q) (128-bit loads, all rows of the chunk per mask block), then, for the survivors only,
+// new_row = row(q) with the columns where row(p) is 0 squeezed out: 32 mask words per step, the
+// compress network's move masks (Hacker's Delight 7-4) derived ONCE per mask word for all
+// survivors of the chunk, output words assembled in shared memory. (Rows of at most keep_words
+// words take k_expand_units + k_count_and.)
 __global__ void __launch_bounds__(256)
 k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
                 const int32_t* __restrict__ roww_old, const int32_t* __restrict__ ncand,
-                const int32_t* __restrict__ wnew, const I2* __restrict__ off2, int64_t n, int32_t thr,
+                const int32_t* __restrict__ wnew, const I2* __restrict__ off2,
+                const int2* __restrict__ wide_list, int64_t n_wide, int32_t thr,
                 int keep_words, uint32_t* __restrict__ arena_new, int32_t* __restrict__ cand_cnt,
                 int32_t* __restrict__ cand_p) {
   __shared__ uint32_t sbuf[8][kChunk][36];
   __shared__ int64_t s_src[8][kChunk], s_dst[8][kChunk];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int64_t p = (int64_t)blockIdx.x * 8 + warp; p < n; p += (int64_t)gridDim.x * 8) {
+  for (int64_t li = (int64_t)blockIdx.x * 8 + warp; li < n_wide; li += (int64_t)gridDim.x * 8) {
+    const int2 unit = __ldg(wide_list + li);   // (parent, first candidate of the chunk)
+    const int64_t p = unit.x;
     const int m = __ldg(ncand + p);
     if (m == 0) continue;                        // warp-uniform
     const int w_old = __ldg(roww_old + p), w_new = __ldg(wnew + p);
     const I2 o = off2[p];
     const uint32_t* rowp = arena_old + __ldg(rowptr_old + p);
-    if (w_old <= keep_words) {
-      const int nv = w_old >> 2;
-      const uint4* p4 = reinterpret_cast<const uint4*>(rowp);
-      const bool h0 = lane < nv, h1 = lane + 32 < nv;
-      const uint4 m0 = h0 ? ldg4(p4 + lane) : or4z();
-      const uint4 m1 = h1 ? ldg4(p4 + lane + 32) : or4z();
-      int n_surv = 0, pend_i = 0;
-      uint4 pend0 = or4z(), pend1 = or4z();
-      for (int i0 = 0; i0 < m; i0 += kAndIlp) {
-        uint4 a0[kAndIlp], a1[kAndIlp];
-#pragma unroll
-        for (int u = 0; u < kAndIlp; ++u) {
-          a0[u] = a1[u] = or4z();
-          if (i0 + u < m) {
-            const uint4* q4 = reinterpret_cast<const uint4*>(arena_old + __ldg(rowptr_old + p + 1 + i0 + u));
-            if (h0) a0[u] = ldg4(q4 + lane);
-            if (h1) a1[u] = ldg4(q4 + lane + 32);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < kAndIlp; ++u) {
-          if (i0 + u < m) {                      // warp-uniform
-            const uint4 r0 = and4(a0[u], m0), r1 = and4(a1[u], m1);
-            const int cnt = warp_sum(popc4(r0) + popc4(r1));
-            const int i = i0 + u;
-            if (lane == 0) {
-              cand_cnt[o.a + i] = cnt;
-              cand_p[o.a + i] = (int32_t)p;
-            }
-            if (cnt >= thr) {
-              if (n_surv == 0) {
-                pend0 = r0;
-                pend1 = r1;
-                pend_i = i;
-              } else {
-                if (n_surv == 1) {
-                  uint4* d = reinterpret_cast<uint4*>(arena_new + o.b + (int64_t)pend_i * w_new);
-                  if (h0) d[lane] = pend0;
-                  if (h1) d[lane + 32] = pend1;
-                }
-                uint4* d = reinterpret_cast<uint4*>(arena_new + o.b + (int64_t)i * w_new);
-                if (h0) d[lane] = r0;
-                if (h1) d[lane + 32] = r1;
-              }
-              ++n_surv;
-            }
-          }
-        }
-      }
-      continue;
-    }
+    if (w_old <= keep_words) continue;       // narrow rows: k_count_and
     // ---- bit-extract route ----
     const int nv = w_old >> 2;
     const uint4* msk4 = reinterpret_cast<const uint4*>(rowp);
-    for (int i0 = 0; i0 < m; i0 += kChunk) {
+    {
+      const int i0 = unit.y;
       const int mc = min(kChunk, m - i0);
       const int64_t my_src = lane < mc ? __ldg(rowptr_old + p + 1 + i0 + lane) : 0;
       int acc[kChunk];
@@ -398,16 +478,45 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
 }
 
 // work figures for the profiler (launched only while it is on)
+// out[0] / out[1]: words read on the AND / bit-extract route (row(p) once + one row per candidate)
 __global__ void __launch_bounds__(256)
-k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww, int64_t n,
+k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww, int64_t n, int keep_words,
              unsigned long long* __restrict__ out) {
-  unsigned long long acc = 0;
+  unsigned long long acc = 0, acc_w = 0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
     const long long m = ncand[p];
-    if (m) acc += (unsigned long long)((m + 1) * (long long)roww[p]);   // row(p) once + one row per candidate
+    if (m) {
+      const unsigned long long w = (unsigned long long)((m + 1) * (long long)roww[p]);
+      if (roww[p] <= keep_words) acc += w; else acc_w += w;
+    }
   }
-  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  if ((threadIdx.x & 31) == 0 && acc) atomicAdd(out, acc);
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    acc_w += __shfl_xor_sync(0xffffffffu, acc_w, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (acc) atomicAdd(out, acc);
+    if (acc_w) atomicAdd(out + 1, acc_w);
+  }
+}
+// out[0] / out[1]: row words of the new level whose parent took the AND / bit-extract route
+__global__ void __launch_bounds__(256)
+k_written_work(const int32_t* __restrict__ roww_new, const int32_t* __restrict__ par_new,
+               const int32_t* __restrict__ roww_old, int64_t n, int keep_words,
+               unsigned long long* __restrict__ out) {
+  unsigned long long acc = 0, acc_w = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned long long w = (unsigned long long)roww_new[i];
+    if (roww_old[par_new[i]] <= keep_words) acc += w; else acc_w += w;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    acc_w += __shfl_xor_sync(0xffffffffu, acc_w, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (acc) atomicAdd(out, acc);
+    if (acc_w) atomicAdd(out + 1, acc_w);
+  }
 }
 __global__ void __launch_bounds__(256)
 k_sum_i32(const int32_t* __restrict__ v, int64_t n, unsigned long long* __restrict__ out) {
@@ -668,8 +777,8 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   KMLS_TRY(M.take(&row_of_item, n_items));
   KMLS_TRY(M.take(&bitmap, (int64_t)n_rows * row_words));
   KMLS_TRY(M.take(&counts1, n_rows, false));
-  KMLS_TRY(M.take(&flags, 8));
-  KMLS_CUDA(cudaMemsetAsync(flags, 0, 8 * sizeof(int32_t), s));
+  KMLS_TRY(M.take(&flags, 16));
+  KMLS_CUDA(cudaMemsetAsync(flags, 0, 16 * sizeof(int32_t), s));
   k_fill_i32<<<grid_for(n_items, 256, 8), 256, 0, s>>>(row_of_item, n_items, -1);
   KMLS_LAUNCHED("k_fill_i32");
   k_number_rows<<<grid_for(n_rows, 256, 8), 256, 0, s>>>(cand, n_rows, row_of_item, nullptr);
@@ -920,40 +1029,43 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&off2, n_k + 1));
     const bool parted = k == 2 && opt.n_parts > 1;
     const bool prof = profiler().on;
+    KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, sizeof(int32_t), s));
     {
       ProfScope ps("k_join_size", s, 20.0 * (double)n_k, k + 1);
       k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words,
                                                          parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
-                                                         ncand, wnew);
+                                                         ncand, wnew, flags + 5);
       KMLS_LAUNCHED("k_join_size");
     }
     if (prof) {
-      KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
-      k_level_work<<<grid_for(n_k, 256, 8), 256, 0, s>>>(ncand, roww_k, n_k, (unsigned long long*)(flags + 6));
+      KMLS_CUDA(cudaMemsetAsync(flags + 8, 0, 16, s));
+      k_level_work<<<grid_for(n_k, 256, 8), 256, 0, s>>>(ncand, roww_k, n_k, keep_words, (unsigned long long*)(flags + 8));
       KMLS_LAUNCHED("k_level_work");
     }
     {
       cub::CountingInputIterator<int64_t> idx(0);
-      cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(idx, CandSlots{ncand, wnew});
+      cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(
+          idx, CandSlots{ncand, wnew, roww_k, keep_words});
       size_t need = 0;
-      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       char* tmp = nullptr;
       KMLS_TRY(M.take(&tmp, (int64_t)need));
       ProfScope ps("scan_slots", s, 24.0 * (double)n_k, k + 1);
-      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0}, (int)n_k, s));
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       M.ws.release(tmp);
     }
-    k_i2_total<<<1, 1, 0, s>>>(ncand, wnew, n_k, off2, M.box);
+    k_i2_total<<<1, 1, 0, s>>>(CandSlots{ncand, wnew, roww_k, keep_words}, n_k, off2, flags + 5, M.box);
     KMLS_LAUNCHED("k_i2_total");
     M.launches += 4;
     KMLS_TRY(M.sync());
-    const int64_t n_cand = M.box[0], slot_words = M.box[1];
-    double read_words = 0.0;
+    const int64_t n_cand = M.box[0], slot_words = M.box[1], n_units = M.box[2], n_wide = M.box[3];
+    double read_and = 0.0, read_wide = 0.0;
     if (prof) {
-      unsigned long long h = 0;
-      KMLS_CUDA(cudaMemcpyAsync(&h, flags + 6, 8, cudaMemcpyDeviceToHost, s));
+      unsigned long long h[2] = {0, 0};
+      KMLS_CUDA(cudaMemcpyAsync(h, flags + 8, 16, cudaMemcpyDeviceToHost, s));
       KMLS_TRY(M.sync());
-      read_words = (double)h;
+      read_and = (double)h[0];
+      read_wide = (double)h[1];
     }
     R->level_candidates[k + 1] = n_cand;
     if (n_cand == 0) break;
@@ -968,14 +1080,34 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&cand_cnt, n_cand));
     KMLS_TRY(M.take(&cand_p, n_cand));
     KMLS_TRY(M.take(&out_off, n_cand + 1));
-    int rec_cp = -1;
+    // algorithmic bytes of counting + projecting this level: row(p) once per parent + one row
+    // per candidate read, 8 bytes per candidate written (count, parent), + the rows of the
+    // survivors (added after the emit); split between the two kernels by their share of parents
+    int rec_cp = -1, rec_and = -1;
+    Unit* units = nullptr;
+    int2* wide_list = nullptr;
+    KMLS_TRY(M.take(&units, n_units));
+    KMLS_TRY(M.take(&wide_list, n_wide));
+    KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, sizeof(int32_t), s));
     {
-      // algorithmic bytes: row(p) once per parent + one row per candidate read, 8 bytes per
-      // candidate written (count, parent), + the rows of the survivors (added below)
-      ProfScope ps("k_count_project", s, 4.0 * read_words + 8.0 * (double)n_cand, k + 1);
+      ProfScope ps("k_expand_units", s, 64.0 * (double)n_units + 24.0 * (double)n_k, k + 1);
+      k_expand_units<<<grid_for(n_k, 256, 16), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, off2, n_k, keep_words,
+                                                            arena_n, units, wide_list, flags + 5);
+      KMLS_LAUNCHED("k_expand_units");
+      ++M.launches;
+    }
+    if (n_units > 0) {
+      ProfScope ps("k_count_and", s, 4.0 * read_and + 32.0 * (double)n_units, k + 1);
+      rec_and = ps.idx;
+      k_count_and<<<grid_for(n_units, 8, 48), 256, 0, s>>>(units, n_units, thr, cand_cnt, cand_p);
+      KMLS_LAUNCHED("k_count_and");
+      ++M.launches;
+    }
+    if (n_wide > 0) {
+      ProfScope ps("k_count_project", s, 4.0 * read_wide + 8.0 * (double)n_wide, k + 1);
       rec_cp = ps.idx;
-      k_count_project<<<grid_for(n_k, 8, 64), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, n_k, thr,
-                                                           keep_words, arena_n, cand_cnt, cand_p);
+      k_count_project<<<grid_for(n_wide, 8, 64), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, wide_list,
+                                                              n_wide, thr, keep_words, arena_n, cand_cnt, cand_p);
       KMLS_LAUNCHED("k_count_project");
     }
     {
@@ -1013,16 +1145,20 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_LAUNCHED("k_emit_rows");
     }
     ++M.launches;
-    if (rec_cp >= 0) {   // rows written by k_count_project = widths of the new itemsets that own a row
-      unsigned long long h = 0;
-      KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
-      k_sum_i32<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, n_next, (unsigned long long*)(flags + 6));
-      KMLS_LAUNCHED("k_sum_i32");
-      KMLS_CUDA(cudaMemcpyAsync(&h, flags + 6, 8, cudaMemcpyDeviceToHost, s));
+    if (rec_cp >= 0 || rec_and >= 0) {   // rows written = widths of the new itemsets that own a row
+      unsigned long long h[2] = {0, 0};
+      KMLS_CUDA(cudaMemsetAsync(flags + 8, 0, 16, s));
+      k_written_work<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, par_n, roww_k, n_next, keep_words,
+                                                             (unsigned long long*)(flags + 8));
+      KMLS_LAUNCHED("k_written_work");
+      KMLS_CUDA(cudaMemcpyAsync(h, flags + 8, 16, cudaMemcpyDeviceToHost, s));
       KMLS_TRY(M.sync());
-      profiler().records[rec_cp].work += 4.0 * (double)h;
+      if (rec_and >= 0) profiler().records[rec_and].work += 4.0 * (double)h[0];
+      if (rec_cp >= 0) profiler().records[rec_cp].work += 4.0 * (double)h[1];
     }
     // this level's scratch and the previous level's rows are done with (stream order)
+    M.ws.release(units);
+    M.ws.release(wide_list);
     M.ws.release(ncand);
     M.ws.release(wnew);
     M.ws.release(off2);

@@ -359,3 +359,135 @@ extern "C" int kmls_supports_f64(const int32_t* d_counts, int64_t n, int64_t n_p
   KMLS_LAUNCHED("k_supports");
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------
+// K6: the fold of reference machine-learning/main.py:282-296 as a CSR built on the device.
+// The reference walks every frequent itemset and keeps, for every ordered pair of its members,
+// the largest support seen; by anti-monotonicity that is the support of the pair itself
+// (SURVEY.md F4), so the map is fully described by the frequent-pair table:
+//   track a -> [(track b, support({a, b})) for every frequent pair containing a]
+// in both directions. Inner lists come out sorted by support DESCENDING, ties by track id:
+// rest_api sorts the merged candidates with a stable sort (rest_api/app/main.py:250), so a
+// deterministic inner order makes its top-K deterministic too (the reference's own order
+// depends on Python's per-process string hashing).
+// ---------------------------------------------------------------------------------------
+#include <cub/device/device_segmented_sort.cuh>
+
+#include "workspace.cuh"
+
+namespace kmls {
+
+__global__ void __launch_bounds__(256)
+k_pair_degree(const int32_t* __restrict__ items2, int64_t n2, int32_t* __restrict__ degree) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < 2 * n2; i += (int64_t)gridDim.x * blockDim.x)
+    atomicAdd(degree + items2[i], 1);
+}
+
+// key = (~count) << 32 | other track id: ascending keys = descending count, then ascending id
+__global__ void __launch_bounds__(256)
+k_pair_map_fill(const int32_t* __restrict__ items2, const int32_t* __restrict__ counts2, int64_t n2,
+                const int32_t* __restrict__ row_items, const int64_t* __restrict__ indptr,
+                int32_t* __restrict__ cursor, unsigned long long* __restrict__ keys) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t a = items2[2 * i], b = items2[2 * i + 1];
+    const unsigned long long hi = (unsigned long long)(~(uint32_t)counts2[i]) << 32;
+    keys[indptr[a] + atomicAdd(cursor + a, 1)] = hi | (uint32_t)__ldg(row_items + b);
+    keys[indptr[b] + atomicAdd(cursor + b, 1)] = hi | (uint32_t)__ldg(row_items + a);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_pair_map_decode(const unsigned long long* __restrict__ keys, int64_t n, double n_total,
+                  int32_t* __restrict__ other, double* __restrict__ support) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned long long k = keys[i];
+    other[i] = (int32_t)(uint32_t)k;
+    support[i] = __ddiv_rn((double)(~(uint32_t)(k >> 32)), n_total);   // count / N as Python divides
+  }
+}
+
+static size_t pair_map_sort_bytes(int64_t n_entries, int32_t n_rows) {
+  size_t need = 0;
+  cub::DeviceSegmentedSort::SortKeys((void*)nullptr, need, (const unsigned long long*)nullptr,
+                                     (unsigned long long*)nullptr, n_entries, (int64_t)n_rows, (const int64_t*)nullptr,
+                                     (const int64_t*)nullptr);
+  return need;
+}
+
+}  // namespace kmls
+
+extern "C" size_t kmls_pair_map_scratch_bytes(int64_t n_pairs, int32_t n_rows) {
+  if (n_pairs < 0) n_pairs = 0;
+  if (n_rows < 0) n_rows = 0;
+  return 2 * (size_t)n_rows * 4 + 2 * (size_t)(2 * n_pairs) * 8 + kmls::pair_map_sort_bytes(2 * n_pairs, n_rows) +
+         kmls_scan_scratch_bytes(n_rows) + 8 * 256;
+}
+
+extern "C" int kmls_pair_map(const int32_t* d_items2, const int32_t* d_counts2, int64_t n_pairs,
+                             const int32_t* d_row_items, int32_t n_rows, int64_t n_playlists_total,
+                             int64_t* d_indptr, int32_t* d_other, double* d_support, void* d_scratch,
+                             size_t scratch_bytes, kmls_stream_t stream) {
+  using namespace kmls;
+  KMLS_REQUIRE(n_pairs >= 0 && n_rows >= 0 && d_indptr, "kmls_pair_map: bad arguments");
+  KMLS_REQUIRE(2 * n_pairs <= 0x7fffffff, "kmls_pair_map: too many pairs");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (n_rows == 0 || n_pairs == 0) {
+    KMLS_CUDA(cudaMemsetAsync(d_indptr, 0, sizeof(int64_t) * (size_t)(n_rows + 1), s));
+    return 0;
+  }
+  KMLS_REQUIRE(d_items2 && d_counts2 && d_row_items && d_other && d_support && n_playlists_total > 0,
+               "kmls_pair_map: null pointer or bad playlist count");
+  KMLS_REQUIRE(scratch_bytes >= kmls_pair_map_scratch_bytes(n_pairs, n_rows) && d_scratch,
+               "kmls_pair_map: scratch smaller than kmls_pair_map_scratch_bytes()");
+  Workspace ws(d_scratch, scratch_bytes);
+  const int64_t n_e = 2 * n_pairs;
+  int32_t* degree = (int32_t*)ws.alloc(sizeof(int32_t) * n_rows);
+  int32_t* cursor = (int32_t*)ws.alloc(sizeof(int32_t) * n_rows);
+  unsigned long long* k_in = (unsigned long long*)ws.alloc(8 * (size_t)n_e);
+  unsigned long long* k_out = (unsigned long long*)ws.alloc(8 * (size_t)n_e);
+  const size_t scan_bytes = kmls_scan_scratch_bytes(n_rows), sort_bytes = pair_map_sort_bytes(n_e, n_rows);
+  void* scan_tmp = ws.alloc(scan_bytes);
+  void* sort_tmp = ws.alloc(sort_bytes);
+  KMLS_REQUIRE(degree && cursor && k_in && k_out && scan_tmp && sort_tmp, "kmls_pair_map: scratch too small");
+  KMLS_CUDA(cudaMemsetAsync(degree, 0, sizeof(int32_t) * (size_t)n_rows, s));
+  KMLS_CUDA(cudaMemsetAsync(cursor, 0, sizeof(int32_t) * (size_t)n_rows, s));
+  const int grid = (int)std::min<int64_t>((n_e + 255) / 256, (int64_t)num_sms() * 8);
+  k_pair_degree<<<grid, 256, 0, s>>>(d_items2, n_pairs, degree);
+  KMLS_LAUNCHED("k_pair_degree");
+  int rc = kmls_exclusive_scan_i32(degree, n_rows, d_indptr, scan_tmp, scan_bytes, s);
+  if (rc) return rc;
+  k_pair_map_fill<<<grid, 256, 0, s>>>(d_items2, d_counts2, n_pairs, d_row_items, d_indptr, cursor, k_in);
+  KMLS_LAUNCHED("k_pair_map_fill");
+  size_t need = sort_bytes;
+  KMLS_CUDA(cub::DeviceSegmentedSort::SortKeys(sort_tmp, need, (const unsigned long long*)k_in, k_out, n_e,
+                                               (int64_t)n_rows, (const int64_t*)d_indptr,
+                                               (const int64_t*)d_indptr + 1, s));
+  k_pair_map_decode<<<grid, 256, 0, s>>>(k_out, n_e, (double)n_playlists_total, d_other, d_support);
+  KMLS_LAUNCHED("k_pair_map_decode");
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Micro-benchmark behind the roofline of k_pair_counts_csr (no counterpart in the reference):
+// how many 32-bit RED.ADD updates per second this GPU retires when warps scatter them over a
+// counter matrix of the size the pair counts use. n_updates updates, addresses drawn by a
+// counter-based hash over d_buf[n_words] (uniform: the worst case; the kernel's own addresses
+// are skewed towards popular rows, which it absorbs in shared memory).
+// ---------------------------------------------------------------------------------------
+namespace kmls {
+__global__ void __launch_bounds__(256)
+k_redg_microbench(int32_t* __restrict__ buf, uint64_t n_words, int64_t n_updates, uint64_t seed) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_updates; i += (int64_t)gridDim.x * blockDim.x)
+    atomicAdd(buf + mix64(seed + (uint64_t)i) % n_words, 1);
+}
+}  // namespace kmls
+
+extern "C" int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_updates, uint64_t seed,
+                                    kmls_stream_t stream) {
+  KMLS_REQUIRE(d_buf && n_words > 0 && n_updates >= 0, "kmls_redg_microbench: bad arguments");
+  if (n_updates == 0) return 0;
+  const int grid = (int)std::min<int64_t>((n_updates + 255) / 256, (int64_t)kmls::num_sms() * 32);
+  kmls::k_redg_microbench<<<grid, 256, 0, (cudaStream_t)stream>>>(d_buf, (uint64_t)n_words, n_updates, seed);
+  KMLS_LAUNCHED("k_redg_microbench");
+  return 0;
+}

@@ -219,7 +219,8 @@ def test_profile_report_names_the_kernels():
     miner.generate_rules(res, 0.3)
     rec = _lib.profile_report()
     names = {r[0] for r in rec}
-    assert {"k_encode_bitmap", "k_count_project", "k_emit_rows", "k_rules_gather", "k_rules_write"} <= names
+    assert {"k_encode_bitmap", "k_expand_units", "k_emit_rows", "k_rules_gather", "k_rules_write"} <= names
+    assert names & {"k_count_and", "k_count_project"}
     assert all(ms >= 0 for _, _, ms, _ in rec)
-    assert any(nm == "k_count_project" and work > 0 for nm, _, _, work in rec)
+    assert any(nm in ("k_count_and", "k_count_project") and work > 0 for nm, _, _, work in rec)
     assert miner.mine_native(d_off, d_items, 700, 0.012).as_dict() == res.as_dict()   # profiling off again: same result
