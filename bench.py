@@ -437,7 +437,8 @@ def run_gpu(args):
     by_playlists = world > 1 and args.partition == "playlists"
     # device memory of the one-call entry points, kept across steps (the tables a step returns
     # are views of it and are dropped before the next step)
-    spaces = {"mine": miner.Workspace(device), "rules": miner.Workspace(device)}
+    spaces = {"mine": miner.Workspace(device, int(args.mine_ws_gb * (1 << 30))),
+              "rules": miner.Workspace(device, int(args.rules_ws_gb * (1 << 30)))}
 
     def mine(o, i):
         if by_playlists or args.count_impl != "projected":
@@ -471,7 +472,11 @@ def run_gpu(args):
         torch.cuda.synchronize()
         log(f"[bench] rank {rank} warmup {i}: {time.time() - t0:.3f}s itemsets={res.n_itemsets} "
             f"rules={rules.n_rules} levels={[int(c.numel()) for _, c in res.levels]}")
-        info = {"itemsets": res.n_itemsets, "rules_this_rank": rules.n_rules,
+        merge_ms = None
+        if getattr(res, "merge_marks", None):
+            mk = res.merge_marks
+            merge_ms = {mk[i + 1][0]: mk[i][1].elapsed_time(mk[i + 1][1]) for i in range(len(mk) - 1)}
+        info = {"merge_ms": merge_ms, "itemsets": res.n_itemsets, "rules_this_rank": rules.n_rules,
                 "levels": [int(c.numel()) for _, c in res.levels], "stats": res.stats,
                 "rule_stats": getattr(rules, "stats", None)}
         del res, rules
@@ -769,6 +774,7 @@ def run_gpu(args):
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
             "partition": info.get("stats", {}).get("partition"),
+            "merge_ms": info.get("merge_ms"),
             "top_kernel": top,
             "parity": parity,
             "verify_full_size": verify,
@@ -814,6 +820,8 @@ def main():
                          "allreduce per level")
     ap.add_argument("--part-block", type=int, default=64, help="frequent pairs per block of the class partition")
     ap.add_argument("--rules-to-host", action="store_true", help="also measure e2e with the rule table copied to the host")
+    ap.add_argument("--mine-ws-gb", type=float, default=0.0, help="initial size of the mining workspace (0 = grow on demand)")
+    ap.add_argument("--rules-ws-gb", type=float, default=0.0, help="initial size of the rules workspace (0 = grow on demand)")
     ap.add_argument("--no-prune", action="store_true", help="switch Apriori pruning of the joins off")
     ap.add_argument("--pair-impl", default="auto", choices=["auto", "i8", "popc", "csr"])
     ap.add_argument("--count-impl", default="projected", choices=["projected", "fullwidth"])

@@ -294,6 +294,17 @@ int kmls_rules_write(const int32_t* d_counts, const int64_t* level_sizes, int32_
                      double min_confidence, const void* d_part, const int64_t* d_rule_off,
                      int32_t* d_out_rule, double* d_out_confidence, double* d_out_lift,
                      int32_t* d_mismatch, kmls_stream_t stream);
+/* kmls_rules_write with the two planes of pass 1 passed separately: the rows lvl_begin ..
+ * lvl_begin + lvl_count - 1 of planes that pass 1 wrote for a LARGER range (d_plane_a /
+ * d_plane_c point at the first slot of row lvl_begin in each plane). This is how a rank of a
+ * small multi-GPU job writes its slice of the rules after a gather pass 1 over whole levels. */
+int kmls_rules_write_planes(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
+                            int32_t k, int64_t lvl_begin, int64_t lvl_count,
+                            int64_t n_playlists_total, double min_confidence,
+                            const int32_t* d_plane_a, const int32_t* d_plane_c,
+                            const int64_t* d_rule_off, int32_t* d_out_rule, double* d_out_confidence,
+                            double* d_out_lift, int32_t* d_mismatch, kmls_stream_t stream);
+
 /* No counterpart in the reference (parity plumbing). Adds to *d_out (NOT zeroed here) the
  * order-independent checksum of one level table d_items[n][k] (bitmap rows) / d_counts[n]:
  * sum over itemsets of mix(sum_i mix(track id_i + 1) ^ mix(count * 0x100000001B3 + k)) mod
@@ -347,13 +358,24 @@ typedef struct kmls_mine_options {
   int32_t pair_impl;      /* level 2: 0 = choose by cost, 1 = per playlist (sparse), 2 = CUDA-core
                              AND+popc, 3 = tcgen05 int8 GEMM */
   int32_t keep_words;     /* conditional rows at most this wide keep their column space (AND
-                             instead of bit extract); 0 = default (256), at most 256 */
+                             instead of bit extract); 0 = default (256), at most 1024 */
   int32_t n_parts;        /* class partition for multi-GPU jobs: this call mines only the      */
   int32_t part;           /* subtrees of the frequent pairs in blocks part, part + n_parts, ... */
   int32_t part_block;     /* of part_block consecutive pairs; n_parts <= 1 = everything        */
+  int32_t squeeze_pct;    /* a row wider than keep_words is squeezed (bit extract) only if that
+                             leaves at most this percentage of its width; 0 = default (50)     */
+  int32_t reserved;
   int64_t max_itemsets;   /* guard: fail (never truncate) beyond this many itemsets; 0 = 2e8   */
   void* h_tables;         /* optional PINNED host buffer: every level table is copied there on */
   size_t h_tables_bytes;  /* a side stream as soon as it is final, while mining continues      */
+  /* Optional, for the ranks of a class-partitioned job (n_parts > 1, every rank holding all
+   * playlists): sum-allreduce d_buf[n] (int32, device memory inside the workspace) over the
+   * ranks, ordered on `stream`; return 0. With it the level-2 pair counts are taken from
+   * playlists part*N/n_parts .. (part+1)*N/n_parts only and summed over the ranks, instead of
+   * every rank counting all playlists. The host side of the job supplies it (NCCL through
+   * torch.distributed in this repository); the library itself links no communication library. */
+  int (*allreduce_i32)(void* ctx, int32_t* d_buf, int64_t n, kmls_stream_t stream);
+  void* allreduce_ctx;
 } kmls_mine_options;
 
 typedef struct kmls_mine_result {

@@ -58,6 +58,7 @@ SIGNATURES = {
     "kmls_rules_count_gather": (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _I64, _F64, _P, _P, _P, _P]),
     "kmls_rules_write": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P, _P]),
     "kmls_itemset_checksum": (ctypes.c_int, [_P, _P, _I64, _I32, _P, _P, _P]),
+    "kmls_rules_write_planes": (ctypes.c_int, [_P, _P, _I32, _I32, _I64, _I64, _I64, _F64, _P, _P, _P, _P, _P, _P, _P, _P]),
     "kmls_rule_supports": (ctypes.c_int, [_P, _I64, _P, _I64, _P, _P]),
     "kmls_rule_checksum": (ctypes.c_int, [_P, _P, _P, _I32, _P, _P, _P, _I64, _P, _I64, _P, _P]),
     "kmls_thresholds": (ctypes.c_int, [_F64, _I64, _P, _P]),
@@ -79,7 +80,13 @@ class MineOptions(ctypes.Structure):
     """struct kmls_mine_options (include/kmls_b200.h)."""
     _fields_ = [("max_len", c_int32), ("pair_impl", c_int32), ("keep_words", c_int32),
                 ("n_parts", c_int32), ("part", c_int32), ("part_block", c_int32),
-                ("max_itemsets", c_int64), ("h_tables", c_void_p), ("h_tables_bytes", c_size_t)]
+                ("squeeze_pct", c_int32), ("reserved", c_int32),
+                ("max_itemsets", c_int64), ("h_tables", c_void_p), ("h_tables_bytes", c_size_t),
+                ("allreduce_i32", c_void_p), ("allreduce_ctx", c_void_p)]
+
+
+# int (*allreduce_i32)(void* ctx, int32_t* d_buf, int64_t n, kmls_stream_t stream)
+ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, c_void_p, c_void_p, c_int64, c_void_p)
 
 
 class MineResultC(ctypes.Structure):

@@ -59,11 +59,14 @@ __global__ void k_post(const int64_t* a, const int64_t* b, const int32_t* c, con
 }
 
 // per parent: a = candidates, b = slot words, c = work units of the AND kernel (prefix-summed)
-struct I2 {
-  long long a, b, c;
+// (16 bytes: candidates and units of one level stay below 2^31 - k_join_size sums the
+// candidates in 64 bits as well and the host refuses a level that would exceed that)
+struct __align__(16) I2 {
+  long long b;
+  int a, c;
 };
 struct I2Sum {
-  __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.a + y.a, x.b + y.b, x.c + y.c}; }
+  __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.b + y.b, x.a + y.a, x.c + y.c}; }
 };
 
 // ---- level 1 helpers --------------------------------------------------------------------
@@ -145,10 +148,11 @@ k_pair_parents(const int32_t* __restrict__ items2, int64_t n2, int32_t* __restri
 // of a class-partitioned job; deeper levels hold only owned subtrees anyway).
 __global__ void __launch_bounds__(256)
 k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
-            const int32_t* __restrict__ counts, int64_t n, int keep_words, int n_parts, int part,
+            const int32_t* __restrict__ counts, int64_t n, int keep_words, int squeeze_pct, int n_parts, int part,
             int part_block, int32_t* __restrict__ ncand, int32_t* __restrict__ wnew,
             int32_t* __restrict__ n_wide) {
   int wide = 0;
+  unsigned long long cands = 0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
     const int32_t w_old = roww[p];
     int32_t m = 0, w = 0;
@@ -167,13 +171,26 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
         if (__ldg(par + mid) == cls) lo = mid; else hi = mid;
       }
       m = (int32_t)(lo - p);
-      w = w_old <= keep_words ? w_old : ((((__ldg(counts + p) + 31) >> 5) + 3) & ~3);
-      if (m > 0 && w_old > keep_words) wide += (m + 7) >> 3;   // chunks of kChunk = 8 candidates
+      // squeeze only rows that are wide AND shrink enough to pay for the bit extract: a dense
+      // wide row (a very popular prefix) stays in its column space and takes the AND route
+      const int32_t ws = (((__ldg(counts + p) + 31) >> 5) + 3) & ~3;
+      const bool squeeze = w_old > keep_words && (int64_t)ws * 100 <= (int64_t)w_old * squeeze_pct;
+      w = squeeze ? ws : w_old;
+      if (m > 0 && squeeze) wide += (m + 7) >> 3;   // chunks of kChunk = 8 candidates
     }
     ncand[p] = m;
     wnew[p] = w;
+    cands += (unsigned long long)m;
   }
-  if (wide) atomicAdd(n_wide, wide);     // work units (parent, chunk) of the bit-extract route
+  // one atomic per warp, not per thread
+  for (int o = 16; o > 0; o >>= 1) {
+    wide += __shfl_xor_sync(0xffffffffu, wide, o);
+    cands += __shfl_xor_sync(0xffffffffu, cands, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (wide) atomicAdd(n_wide, wide);   // work units (parent, chunk) of the bit-extract route
+    if (cands) atomicAdd(reinterpret_cast<unsigned long long*>(n_wide + 1), cands);
+  }
 }
 
 constexpr int kUnitCands = 4;   // candidates of one parent per work unit of the AND kernel
@@ -182,11 +199,10 @@ struct CandSlots {
   const int32_t* ncand;
   const int32_t* wnew;
   const int32_t* roww;
-  int keep_words;
   __host__ __device__ I2 operator()(int64_t p) const {
-    const long long m = ncand[p];
-    const long long units = (m > 0 && roww[p] <= keep_words) ? (m + kUnitCands - 1) / kUnitCands : 0;
-    return I2{m, m * (long long)wnew[p], units};
+    const int m = ncand[p];
+    const int units = (m > 0 && roww[p] == wnew[p]) ? (m + kUnitCands - 1) / kUnitCands : 0;   // AND route
+    return I2{(long long)m * (long long)wnew[p], m, units};
   }
 };
 
@@ -197,7 +213,8 @@ __global__ void k_i2_total(CandSlots f, int64_t n, I2* off2, const int32_t* n_wi
   box[0] = t.a;
   box[1] = t.b;
   box[2] = t.c;
-  box[3] = *n_wide;
+  box[3] = n_wide[0];
+  box[4] = *reinterpret_cast<const long long*>(n_wide + 1);   // candidates of the level, summed in 64 bits
   __threadfence_system();
 }
 
@@ -216,7 +233,7 @@ struct __align__(16) Unit {
   const uint32_t* rowq[kUnitCands]; // rows of the candidates (siblings p + 1 + i0 ...)
   int32_t p;                        // parent
   int32_t cand0;                    // number of the first candidate in the level's candidate list
-  int32_t mc_nv;                    // candidates in this unit << 16 | row width in 128-bit words
+  int32_t mc_nv;                    // candidates in this unit << 29 | row width in 128-bit words
   int32_t whole;                    // 1 = the unit holds ALL candidates of its parent
 };
 static_assert(sizeof(Unit) == 64, "Unit must be 64 bytes");
@@ -224,13 +241,14 @@ static_assert(sizeof(Unit) == 64, "Unit must be 64 bytes");
 __global__ void __launch_bounds__(256)
 k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
                const int32_t* __restrict__ roww_old, const int32_t* __restrict__ ncand,
-               const I2* __restrict__ off2, int64_t n, int keep_words, uint32_t* __restrict__ arena_new,
+               const int32_t* __restrict__ wnew, const I2* __restrict__ off2, int64_t n,
+               uint32_t* __restrict__ arena_new,
                Unit* __restrict__ units, int2* __restrict__ wide_list, int32_t* __restrict__ wide_fill) {
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
     const int m = ncand[p];
     const int w = roww_old[p];
     if (m == 0) continue;
-    if (w > keep_words) {       // bit-extract route: k_count_project walks this list (order is irrelevant)
+    if (wnew[p] != w) {         // bit-extract route: k_count_project walks this list (order is irrelevant)
       const int chunks = (m + 7) >> 3;
       const int base = atomicAdd(wide_fill, chunks);
       for (int c = 0; c < chunks; ++c) wide_list[base + c] = make_int2((int32_t)p, c << 3);
@@ -248,7 +266,7 @@ k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
         un.rowq[t] = t < mc ? arena_old + __ldg(rowptr_old + p + 1 + i0 + t) : rowp;
       un.p = (int32_t)p;
       un.cand0 = (int32_t)(o.a + i0);
-      un.mc_nv = (mc << 16) | (w >> 2);
+      un.mc_nv = (int32_t)(((uint32_t)mc << 29) | (uint32_t)(w >> 2));
       un.whole = (m <= kUnitCands) ? 1 : 0;
       uint4* d = reinterpret_cast<uint4*>(units + o.c + u);
       const uint4* sv = reinterpret_cast<const uint4*>(&un);
@@ -280,8 +298,8 @@ k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_
                                    reinterpret_cast<const uint4*>(((uint64_t)d1.w << 32) | d1.z),
                                    reinterpret_cast<const uint4*>(((uint64_t)d2.y << 32) | d2.x),
                                    reinterpret_cast<const uint4*>(((uint64_t)d2.w << 32) | d2.z)};
-    const int mc = (int)d3.z >> 16, nv = (int)d3.z & 0xffff;
-    const bool h0 = lane < nv, h1 = lane + 32 < nv;
+    const int mc = (int)(d3.z >> 29), nv = (int)(d3.z & 0x1fffffffu);
+    const bool h0 = lane < nv;
     const uint4 m0 = h0 ? ldg4(rowp + lane) : or4z();
     uint4 r0[kUnitCands];
 #pragma unroll
@@ -292,12 +310,13 @@ k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_
       r0[t] = and4(r0[t], m0);
       cnt[t] = popc4(r0[t]);
     }
-    uint4 m1 = or4z();
-    if (nv > 32) {                               // warp-uniform
-      if (h1) m1 = ldg4(rowp + lane + 32);
+    for (int seg = 32; seg < nv; seg += 32) {    // rows wider than 128 words: warp-uniform trip count
+      if (lane + seg < nv) {
+        const uint4 m1 = ldg4(rowp + lane + seg);
 #pragma unroll
-      for (int t = 0; t < kUnitCands; ++t)
-        if (h1 && t < mc) cnt[t] += popc4(and4(ldg4(rq[t] + lane + 32), m1));
+        for (int t = 0; t < kUnitCands; ++t)
+          if (t < mc) cnt[t] += popc4(and4(ldg4(rq[t] + lane + seg), m1));
+      }
     }
     uint32_t surv = 0;
 #pragma unroll
@@ -319,7 +338,8 @@ k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_
       if ((surv >> t) & 1u) {                    // warp-uniform
         uint4* d = dst + (size_t)t * nv;
         if (h0) d[lane] = r0[t];
-        if (h1) d[lane + 32] = and4(ldg4(rq[t] + lane + 32), m1);
+        for (int seg = 32; seg < nv; seg += 32)   // formed again from the (L1/L2-resident) rows
+          if (lane + seg < nv) d[lane + seg] = and4(ldg4(rq[t] + lane + seg), ldg4(rowp + lane + seg));
       }
     }
   }
@@ -328,7 +348,8 @@ k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_
 constexpr int kAndIlp = 4;   // candidates of a parent in flight per warp (AND route)
 constexpr int kChunk = 8;    // candidates of a parent handled together (bit-extract route)
 static_assert(kChunk == 8, "k_join_size and k_expand_units count chunks of 8");
-constexpr int kKeepWordsMax = 256;
+constexpr int kKeepWordsMax = 1024;     // widest row the AND route takes
+constexpr int kKeepWordsDefaultMine = 256;
 
 // Count + project for parents whose rows are WIDER than keep_words, one warp per parent p (see
 // the file header). Candidate i of p is its i-th later sibling q = p + 1 + i; its number in the
@@ -357,7 +378,7 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
     const int w_old = __ldg(roww_old + p), w_new = __ldg(wnew + p);
     const I2 o = off2[p];
     const uint32_t* rowp = arena_old + __ldg(rowptr_old + p);
-    if (w_old <= keep_words) continue;       // narrow rows: k_count_and
+    if (w_old == w_new) continue;            // rows that keep their column space: k_count_and
     // ---- bit-extract route ----
     const int nv = w_old >> 2;
     const uint4* msk4 = reinterpret_cast<const uint4*>(rowp);
@@ -480,14 +501,15 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
 // work figures for the profiler (launched only while it is on)
 // out[0] / out[1]: words read on the AND / bit-extract route (row(p) once + one row per candidate)
 __global__ void __launch_bounds__(256)
-k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww, int64_t n, int keep_words,
+k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww,
+             const int32_t* __restrict__ wnew, int64_t n,
              unsigned long long* __restrict__ out) {
   unsigned long long acc = 0, acc_w = 0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
     const long long m = ncand[p];
     if (m) {
       const unsigned long long w = (unsigned long long)((m + 1) * (long long)roww[p]);
-      if (roww[p] <= keep_words) acc += w; else acc_w += w;
+      if (roww[p] == wnew[p]) acc += w; else acc_w += w;
     }
   }
   for (int o = 16; o > 0; o >>= 1) {
@@ -502,12 +524,12 @@ k_level_work(const int32_t* __restrict__ ncand, const int32_t* __restrict__ roww
 // out[0] / out[1]: row words of the new level whose parent took the AND / bit-extract route
 __global__ void __launch_bounds__(256)
 k_written_work(const int32_t* __restrict__ roww_new, const int32_t* __restrict__ par_new,
-               const int32_t* __restrict__ roww_old, int64_t n, int keep_words,
+               const int32_t* __restrict__ roww_old, const int32_t* __restrict__ wnew_old, int64_t n,
                unsigned long long* __restrict__ out) {
   unsigned long long acc = 0, acc_w = 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const unsigned long long w = (unsigned long long)roww_new[i];
-    if (roww_old[par_new[i]] <= keep_words) acc += w; else acc_w += w;
+    if (roww_old[par_new[i]] == wnew_old[par_new[i]]) acc += w; else acc_w += w;
   }
   for (int o = 16; o > 0; o >>= 1) {
     acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -697,8 +719,11 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   R->tk = R->thr_k = tk;
   KMLS_REQUIRE(n_playlists >= 0 && n_items >= 0 && n_total >= n_playlists && t1 >= 0 && tk >= 0,
                "kmls_mine: bad sizes or thresholds");
-  const int keep_words = opt.keep_words > 0 ? opt.keep_words : kKeepWordsMax;
-  KMLS_REQUIRE(keep_words <= kKeepWordsMax && (keep_words & 3) == 0, "kmls_mine: keep_words must be a multiple of 4, at most 256");
+  const int keep_words = opt.keep_words > 0 ? opt.keep_words : kKeepWordsDefaultMine;
+  KMLS_REQUIRE(keep_words <= kKeepWordsMax && (keep_words & 3) == 0, "kmls_mine: keep_words must be a multiple of 4, at most 1024");
+  const int squeeze_pct = opt.squeeze_pct > 0 ? opt.squeeze_pct : 50;
+  KMLS_REQUIRE(squeeze_pct <= 100, "kmls_mine: squeeze_pct is a percentage");
+  KMLS_REQUIRE(kmls_bitmap_row_words(n_playlists) / 4 < (1 << 29), "kmls_mine: too many playlists for one row");
   KMLS_REQUIRE(opt.n_parts <= 1 || (opt.part >= 0 && opt.part < opt.n_parts && opt.part_block >= 1),
                "kmls_mine: bad class partition");
   const int64_t max_itemsets = opt.max_itemsets > 0 ? opt.max_itemsets : 200000000;
@@ -889,15 +914,26 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   }
   if (impl == 1) {
     int rec = -1;
+    // a rank of a class-partitioned job counts the pairs of ITS share of the playlists only and
+    // the ranks' matrices are summed (the job's host side supplies the allreduce)
+    const bool shared_pairs = opt.allreduce_i32 != nullptr && opt.n_parts > 1;
+    const int64_t pl_lo = shared_pairs ? n_playlists * opt.part / opt.n_parts : 0;
+    const int64_t pl_hi = shared_pairs ? n_playlists * (opt.part + 1) / opt.n_parts : n_playlists;
     {
       ProfScope ps("k_pair_counts_csr", s, 0.0, 2);
       rec = ps.idx;
-      KMLS_TRY(kmls_pair_counts_csr(d_offsets, d_items, n_playlists, row_of_item, n_rows, pair, flags + 4, s));
+      KMLS_TRY(kmls_pair_counts_csr(d_offsets + pl_lo, d_items, pl_hi - pl_lo, row_of_item, n_rows, pair, flags + 4, s));
     }
     if (rec >= 0) {   // work = counter updates made = sum of the upper triangle, 4 bytes each
       KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
       k_sum_upper<<<grid_for((int64_t)n_rows * n_rows, 256, 8), 256, 0, s>>>(pair, n_rows, (unsigned long long*)(flags + 6));
       KMLS_LAUNCHED("k_sum_upper");
+    }
+    if (shared_pairs) {
+      ProfScope ps("allreduce_pair_counts", s, 4.0 * (double)n_rows * (double)n_rows, 2);
+      if (opt.allreduce_i32(opt.allreduce_ctx, pair, (int64_t)n_rows * n_rows, s) != 0 ||
+          opt.allreduce_i32(opt.allreduce_ctx, flags + 4, 1, s) != 0)
+        return fail(kArgError, "kmls_mine: the allreduce callback failed");
     }
     k_post<<<1, 1, 0, s>>>(rec >= 0 ? (const int64_t*)(flags + 6) : nullptr, nullptr, flags + 4, nullptr, M.box);
     KMLS_LAUNCHED("k_post");
@@ -1029,23 +1065,23 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&off2, n_k + 1));
     const bool parted = k == 2 && opt.n_parts > 1;
     const bool prof = profiler().on;
-    KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, sizeof(int32_t), s));
+    KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, 3 * sizeof(int32_t), s));
     {
       ProfScope ps("k_join_size", s, 20.0 * (double)n_k, k + 1);
-      k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words,
+      k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words, squeeze_pct,
                                                          parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
                                                          ncand, wnew, flags + 5);
       KMLS_LAUNCHED("k_join_size");
     }
     if (prof) {
       KMLS_CUDA(cudaMemsetAsync(flags + 8, 0, 16, s));
-      k_level_work<<<grid_for(n_k, 256, 8), 256, 0, s>>>(ncand, roww_k, n_k, keep_words, (unsigned long long*)(flags + 8));
+      k_level_work<<<grid_for(n_k, 256, 8), 256, 0, s>>>(ncand, roww_k, wnew, n_k, (unsigned long long*)(flags + 8));
       KMLS_LAUNCHED("k_level_work");
     }
     {
       cub::CountingInputIterator<int64_t> idx(0);
       cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(
-          idx, CandSlots{ncand, wnew, roww_k, keep_words});
+          idx, CandSlots{ncand, wnew, roww_k});
       size_t need = 0;
       KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       char* tmp = nullptr;
@@ -1054,10 +1090,11 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       M.ws.release(tmp);
     }
-    k_i2_total<<<1, 1, 0, s>>>(CandSlots{ncand, wnew, roww_k, keep_words}, n_k, off2, flags + 5, M.box);
+    k_i2_total<<<1, 1, 0, s>>>(CandSlots{ncand, wnew, roww_k}, n_k, off2, flags + 5, M.box);
     KMLS_LAUNCHED("k_i2_total");
     M.launches += 4;
     KMLS_TRY(M.sync());
+    KMLS_REQUIRE(M.box[4] <= 0x7fffffff, "kmls_mine: more than 2^31-1 candidates at level %d", k + 1);
     const int64_t n_cand = M.box[0], slot_words = M.box[1], n_units = M.box[2], n_wide = M.box[3];
     double read_and = 0.0, read_wide = 0.0;
     if (prof) {
@@ -1091,8 +1128,8 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, sizeof(int32_t), s));
     {
       ProfScope ps("k_expand_units", s, 64.0 * (double)n_units + 24.0 * (double)n_k, k + 1);
-      k_expand_units<<<grid_for(n_k, 256, 16), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, off2, n_k, keep_words,
-                                                            arena_n, units, wide_list, flags + 5);
+      k_expand_units<<<grid_for(n_k, 256, 16), 256, 0, s>>>(arena_k, rowptr_k, roww_k, ncand, wnew, off2, n_k, arena_n,
+                                                            units, wide_list, flags + 5);
       KMLS_LAUNCHED("k_expand_units");
       ++M.launches;
     }
@@ -1148,7 +1185,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     if (rec_cp >= 0 || rec_and >= 0) {   // rows written = widths of the new itemsets that own a row
       unsigned long long h[2] = {0, 0};
       KMLS_CUDA(cudaMemsetAsync(flags + 8, 0, 16, s));
-      k_written_work<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, par_n, roww_k, n_next, keep_words,
+      k_written_work<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, par_n, roww_k, wnew, n_next,
                                                              (unsigned long long*)(flags + 8));
       KMLS_LAUNCHED("k_written_work");
       KMLS_CUDA(cudaMemcpyAsync(h, flags + 8, 16, cudaMemcpyDeviceToHost, s));

@@ -520,7 +520,8 @@ k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* _
 // that every store instruction of the warp writes one contiguous run.
 __global__ void __launch_bounds__(256)
 k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
-              const int32_t* __restrict__ part, const int64_t* __restrict__ rule_off,
+              const int32_t* __restrict__ pa, const int32_t* __restrict__ pc,
+              const int64_t* __restrict__ rule_off,
               int2* __restrict__ out_rule, double* __restrict__ out_confidence,
               double* __restrict__ out_lift, int32_t* __restrict__ bad) {
   // `bad` counts the itemsets whose kept rules here differ in number from what pass 1 sized
@@ -532,8 +533,6 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
   const uint32_t full = (1u << k) - 1u;
   const int64_t lvl_first = a.id_off[k];
   const double rcp_n = __drcp_rn(n_total);
-  const int32_t* pa = part;
-  const int32_t* pc = part + lvl_count * n_sub;
   if (n_sub <= 16) {
     // short itemsets: 32 / n_sub itemsets per warp, lane = (itemset in the group, slot), so
     // that the lanes are not left idle by the few splits a small itemset has
@@ -830,6 +829,20 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
                                 const void* d_part, const int64_t* d_rule_off, int32_t* d_out_rule,
                                 double* d_out_confidence, double* d_out_lift, int32_t* d_mismatch,
                                 kmls_stream_t stream) {
+  KMLS_REQUIRE(k >= 2 && k <= kMaxRuleK && lvl_count >= 0, "kmls_rules_write: level out of range");
+  const int32_t* pa = (const int32_t*)d_part;
+  return kmls_rules_write_planes(d_counts, level_sizes, max_k, k, lvl_begin, lvl_count, n_playlists_total,
+                                 min_confidence, pa, pa ? pa + lvl_count * ((int64_t)1 << (k - 1)) : nullptr,
+                                 d_rule_off, d_out_rule, d_out_confidence, d_out_lift, d_mismatch, stream);
+}
+
+extern "C" int kmls_rules_write_planes(const int32_t* d_counts, const int64_t* level_sizes, int32_t max_k,
+                                       int32_t k, int64_t lvl_begin, int64_t lvl_count,
+                                       int64_t n_playlists_total, double min_confidence,
+                                       const int32_t* d_plane_a, const int32_t* d_plane_c,
+                                       const int64_t* d_rule_off, int32_t* d_out_rule,
+                                       double* d_out_confidence, double* d_out_lift, int32_t* d_mismatch,
+                                       kmls_stream_t stream) {
   Arena a;
   int rc = make_arena(a, nullptr, d_counts, nullptr, level_sizes, max_k);
   if (rc) return rc;
@@ -837,11 +850,11 @@ extern "C" int kmls_rules_write(const int32_t* d_counts, const int64_t* level_si
   KMLS_REQUIRE(lvl_begin >= 0 && lvl_count >= 0 && lvl_begin + lvl_count <= level_sizes[k],
                "kmls_rules_write: itemset range out of bounds");
   if (lvl_count == 0) return 0;
-  KMLS_REQUIRE(d_part && d_rule_off && d_out_rule && d_out_confidence && d_out_lift && d_mismatch &&
+  KMLS_REQUIRE(d_plane_a && d_plane_c && d_rule_off && d_out_rule && d_out_confidence && d_out_lift && d_mismatch &&
                    ((uintptr_t)d_out_rule & 7) == 0, "kmls_rules_write: null or misaligned pointer");
   int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
-      a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, (const int32_t*)d_part,
+      a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, d_plane_a, d_plane_c,
       d_rule_off, (int2*)d_out_rule, d_out_confidence, d_out_lift, d_mismatch);
   KMLS_LAUNCHED("k_rules_write");
   return 0;

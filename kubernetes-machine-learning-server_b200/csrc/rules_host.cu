@@ -61,7 +61,6 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
   R->rule_off = R->confidence_off = R->lift_off = R->arena_items_off = R->arena_counts_off = -1;
   KMLS_REQUIRE(n_parts >= 1 && part >= 0 && part < n_parts, "kmls_rules: bad part");
   KMLS_REQUIRE(pass1 >= 0 && pass1 <= 2, "kmls_rules: pass1 must be 0 (auto), 1 (gather) or 2 (search)");
-  KMLS_REQUIRE(pass1 != 1 || n_parts == 1, "kmls_rules: the gather route needs the whole table (n_parts == 1)");
   KMLS_REQUIRE(d_workspace && ((uintptr_t)d_workspace & 255) == 0, "kmls_rules: workspace must be 256-byte aligned device memory");
   if (max_rules <= 0) max_rules = 4000000000ll;
   const int max_k = mined->max_k;
@@ -145,6 +144,12 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
   const int64_t n_x = x_end - x_begin;
   if (n_x <= 0) return 0;
 
+  // Pass 1 by gathering reads the WHOLE previous level's output, so with n_parts > 1 it runs
+  // over whole levels on every rank (replicated work: worth it for 2 ranks, where it still
+  // beats searching half the table) and only pass 2 is restricted to the slice.
+  if (pass1 == 0) pass1 = n_parts <= 2 ? 1 : 2;
+  R->pass1_used = pass1;
+  const bool full_pass1 = pass1 == 1 && n_parts > 1;
   struct Lvl {
     int k;
     int64_t begin, count, out0;
@@ -168,27 +173,44 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
   }
   R->n_splits = splits;
   // what the whole call will need at least: say so before pass 1 spends time
-  R->workspace_needed_bytes = H.ws.in_use + (size_t)splits * 8 + (size_t)n_x * 12 + (size_t)n_plan * 512 + (1u << 20);
+  Lvl fplan[KMLS_MAX_LEVELS + 2];     // whole levels (pass 1 of a replicated gather)
+  int n_fplan = 0;
+  int64_t fsplits = 0;
+  if (full_pass1) {
+    int64_t lvl_start = 0;
+    for (int k = 2; k <= max_k; ++k) {
+      if (sizes[k] > 0) {
+        const int64_t ppi = kmls_rules_parts_per_itemset(k);
+        if (ppi < 0) return fail(kArgError, "kmls_rules: rule generation supports itemsets of at most 15 members, got %d", k);
+        fplan[n_fplan++] = Lvl{k, 0, sizes[k], lvl_start, nullptr};
+        fsplits += sizes[k] * ppi;
+      }
+      lvl_start += sizes[k];
+    }
+  }
+  const int64_t p1_splits = full_pass1 ? fsplits : splits, p1_x = full_pass1 ? n_x_all : n_x;
+  R->workspace_needed_bytes = H.ws.in_use + (size_t)p1_splits * 8 + (size_t)p1_x * 12 + (size_t)n_plan * 512 + (1u << 20);
   if (R->workspace_needed_bytes > workspace_bytes)
     return fail(kCapacityError,
                 "kmls_rules: workspace too small: %lld (itemset, antecedent) splits need %zu bytes before the rule "
                 "table itself, %zu given (raise min_support, shard over more GPUs, or give more memory; nothing "
                 "was truncated)", (long long)splits, R->workspace_needed_bytes, workspace_bytes);
-  for (int i = 0; i < n_plan; ++i)
-    KMLS_TRY(H.take(&plan[i].part_buf, plan[i].count * kmls_rules_parts_per_itemset(plan[i].k) * 2, true,
+  Lvl* const p1 = full_pass1 ? fplan : plan;       // the ranges pass 1 runs over
+  const int n_p1 = full_pass1 ? n_fplan : n_plan;
+  for (int i = 0; i < n_p1; ++i)
+    KMLS_TRY(H.take(&p1[i].part_buf, p1[i].count * kmls_rules_parts_per_itemset(p1[i].k) * 2, true,
                     "the subset counts of pass 1"));
-  int32_t *rule_cnt = nullptr, *missing = nullptr;
-  KMLS_TRY(H.take(&rule_cnt, n_x, true, "the rule counts"));
+  int32_t *rule_cnt_p1 = nullptr, *missing = nullptr;
+  KMLS_TRY(H.take(&rule_cnt_p1, p1_x, true, "the rule counts"));
   KMLS_TRY(H.take(&missing, 2, true, "flags"));
   KMLS_CUDA(cudaMemsetAsync(missing, 0, 2 * sizeof(int32_t), s));
+  int32_t* const rule_cnt = full_pass1 ? rule_cnt_p1 + x_begin : rule_cnt_p1;   // this part's slice
 
-  if (pass1 == 0) pass1 = n_parts == 1 ? 1 : 2;
-  R->pass1_used = pass1;
   if (pass1 == 1) {
     int32_t* sub_prev = nullptr;
     const int32_t* part_prev = nullptr;
-    for (int i = 0; i < n_plan; ++i) {
-      const Lvl& L = plan[i];
+    for (int i = 0; i < n_p1; ++i) {
+      const Lvl& L = p1[i];
       int32_t* sub = nullptr;
       KMLS_TRY(H.take(&sub, L.count * (L.k - 1), true, "the subset links of pass 1"));
       {
@@ -200,7 +222,7 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
         // two 4-byte counts read + 8 bytes written per split
         ProfScope ps("k_rules_gather", s, 16.0 * (double)L.count * (double)((int64_t)1 << (L.k - 1)), L.k);
         KMLS_TRY(kmls_rules_count_gather(a_items, a_counts, a_par, sizes, max_k, L.k, sub, part_prev, n_total,
-                                         min_confidence, L.part_buf, rule_cnt + L.out0, missing, s));
+                                         min_confidence, L.part_buf, rule_cnt_p1 + L.out0, missing, s));
       }
       launches += 2;
       H.ws.release(sub_prev);          // stream order: the kernels that read it are already enqueued
@@ -237,7 +259,7 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
     return fail(kCapacityError, "kmls_rules: %lld rules exceed max_rules=%lld (never truncated)", (long long)n_rules,
                 (long long)max_rules);
   H.ws.release(scratch);
-  H.ws.release(rule_cnt);
+  H.ws.release(rule_cnt_p1);
   H.ws.release(nodes);
   R->workspace_needed_bytes = H.ws.in_use + (size_t)n_rules * 24 + 4096;
   int32_t* o_rule = nullptr;
@@ -260,8 +282,17 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
       // 8 bytes read per split + 24 bytes written per kept rule
       ProfScope ps("k_rules_write", s, 8.0 * (double)L.count * (double)((int64_t)1 << (L.k - 1)) +
                                            24.0 * (double)(lvl_rules[i + 1] - lvl_rules[i]), L.k);
-      KMLS_TRY(kmls_rules_write(a_counts, sizes, max_k, L.k, L.begin, L.count, n_total, min_confidence, L.part_buf,
-                                rule_off + L.out0, o_rule, o_conf, o_lift, missing + 1, s));
+      const int64_t n_sub = (int64_t)1 << (L.k - 1);
+      const int32_t *pa = L.part_buf, *pc = L.part_buf ? L.part_buf + L.count * n_sub : nullptr;
+      if (full_pass1) {       // the slice's rows inside the whole level's planes
+        const int32_t* whole = nullptr;
+        for (int f = 0; f < n_fplan; ++f)
+          if (fplan[f].k == L.k) whole = fplan[f].part_buf;
+        pa = whole + L.begin * n_sub;
+        pc = whole + sizes[L.k] * n_sub + L.begin * n_sub;
+      }
+      KMLS_TRY(kmls_rules_write_planes(a_counts, sizes, max_k, L.k, L.begin, L.count, n_total, min_confidence, pa, pc,
+                                       rule_off + L.out0, o_rule, o_conf, o_lift, missing + 1, s));
       ++launches;
     }
     k_post2<<<1, 1, 0, s>>>(nullptr, missing + 1, H.box);

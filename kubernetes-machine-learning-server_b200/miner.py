@@ -16,6 +16,7 @@ so the only exchange is one integer sum-allreduce per level.
 """
 from __future__ import annotations
 
+import ctypes
 import dataclasses
 import math
 from typing import List, Optional, Tuple
@@ -66,6 +67,7 @@ class MineResult:
     workspace: Optional[object] = None      # keeps the native path's device memory alive
     occurrences: Optional[torch.Tensor] = None
     host_layout: Optional[dict] = None
+    merge_marks: Optional[list] = None      # (phase, CUDA event) pairs of a multi-GPU merge
 
     @property
     def n_itemsets(self) -> int:
@@ -303,7 +305,7 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
                 max_itemsets: int = 200_000_000, keep_pair_counts: bool = False, pair_impl: str = "auto",
                 keep_words: Optional[int] = None, workspace: Optional[Workspace] = None,
                 part: Tuple[int, int] = (0, 1), part_block: int = 64,
-                host_tables: Optional[torch.Tensor] = None) -> MineResult:
+                host_tables: Optional[torch.Tensor] = None, allreduce=None, retry_sync=None) -> MineResult:
     """All levels through ONE call into the library (``kmls_mine``): the level loop, its
     sizing and its buffers live in C++; this function only marshals. ``workspace``: device
     memory for the call (a fresh one by default; the returned tables are views of it, so a
@@ -324,12 +326,30 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
     opt = _lib.MineOptions()
     opt.max_len = int(max_len or 0)
     opt.pair_impl = _PAIR_IMPL[pair_impl]
+    if keep_words is None:
+        import os
+        keep_words = int(os.environ.get("KMLS_KEEP_WORDS", 0)) or None    # tuning switch
     opt.keep_words = int(keep_words or 0)
+    import os as _os
+    opt.squeeze_pct = int(_os.environ.get("KMLS_SQUEEZE_PCT", 0))               # tuning switch (0 = library default)
     opt.n_parts, opt.part, opt.part_block = int(part[1]), int(part[0]), int(part_block)
     opt.max_itemsets = int(max_itemsets)
     if host_tables is not None:
         opt.h_tables, opt.h_tables_bytes = host_tables.data_ptr(), int(host_tables.numel())
     ws = workspace if workspace is not None else Workspace(device)
+    cb = None
+    if allreduce is not None and part[1] > 1:
+        # the library hands back an address inside the workspace: wrap it as a tensor view and
+        # let the caller's collective (torch.distributed over NCCL) sum it in place
+        def _ar(_ctx, ptr, n, _stream):
+            try:
+                off = int(ptr) - ws.buf.data_ptr()
+                allreduce(ws.buf[off:off + 4 * int(n)].view(torch.int32))
+                return 0
+            except Exception:      # noqa: BLE001 - reported by the library as a failed callback
+                return 1
+        cb = _lib.ALLREDUCE_FN(_ar)
+        opt.allreduce_i32 = ctypes.cast(cb, ctypes.c_void_p).value
     hint_key = (device.index, "mine")
     if ws.nbytes == 0:
         ws.ensure(max(1 << 28, 48 * int(items.numel()), _SIZE_HINT.get(hint_key, 0)))
@@ -338,11 +358,15 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
         rc, msg = _lib.call_rc("kmls_mine", offsets, items, n_local, int(n_items), n_total, t1, tk, opt,
                                ws.buf, ws.nbytes, out, _stream())
         _lib.CALLS["kmls_mine"] = _lib.CALLS.get("kmls_mine", 0) + 1
-        if rc == 0:
+        too_small = rc == -2 and "workspace too small" in msg
+        if rc != 0 and not too_small:
+            raise _lib.KmlsError(f"kmls_mine failed with code {rc}: {msg}")
+        # ranks that share collectives inside the call must repeat it TOGETHER or not at all
+        again = retry_sync(too_small) if retry_sync is not None else too_small
+        if not again:
             break
-        if rc == -2 and "workspace too small" in msg and ws.grow():
-            continue
-        raise _lib.KmlsError(f"kmls_mine failed with code {rc}: {msg}")
+        if too_small and not ws.grow():
+            raise _lib.KmlsError(f"kmls_mine failed with code {rc}: {msg} (and the device has no more memory to give)")
     _lib.EXTRA_LAUNCHES += int(out.kernel_launches) - 1
     _SIZE_HINT[hint_key] = max(_SIZE_HINT.get(hint_key, 0), int(out.workspace_peak_bytes * 1.1) + (1 << 20))
     stats = {"levels": [], "t1": t1, "tk": tk, "thr_k": int(out.thr_k), "n_playlists": n_total,
@@ -398,7 +422,7 @@ def mine_csr(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_suppo
     always frequent). ``first_projection``: "gather" or "pext" for the level 1 -> 2 rows."""
     native_ok = (group is None and prepared is None and on_level is None and count_impl == "projected"
                  and not prune and first_projection == "gather"
-                 and (keep_words is None or (0 < keep_words <= 256 and keep_words % 4 == 0)))
+                 and (keep_words is None or (0 < keep_words <= 1024 and keep_words % 4 == 0)))
     if impl == "native" and not native_ok:
         raise ValueError("impl='native' does not take group / prepared / on_level / fullwidth / prune")
     if impl in ("auto", "native") and native_ok:
@@ -700,8 +724,6 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
         return generate_rules_python(res, min_confidence, max_rules, part, pass1)
     if pass1 not in _PASS1:
         raise ValueError(f"unknown pass1 {pass1!r}")
-    if pass1 == "gather" and tuple(part) != (0, 1):
-        raise ValueError("pass1='gather' needs the whole table on this GPU (part=(0, 1))")
     device = res.row_items.device
     sizes = [0] + [int(ct.numel()) for _, ct in res.levels]
     e_i32 = torch.empty(0, dtype=torch.int32, device=device)
@@ -716,7 +738,7 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
     hint_key = (device.index, "rules")
     if ws.nbytes == 0:
         n_all = sum(sizes)
-        splits = sum(sizes[k] << (k - 1) for k in range(2, len(sizes))) // max(part[1], 1)
+        splits = sum(sizes[k] << (k - 1) for k in range(2, len(sizes))) // (max(part[1], 1) if part[1] > 2 else 1)
         guess = 4 * sum(sizes[k] * k for k in range(1, len(sizes))) + 28 * n_all + 32 * splits + (64 << 20)
         free = torch.cuda.mem_get_info(device)[0] + torch.cuda.memory_reserved(device) - torch.cuda.memory_allocated(device)
         ws.ensure(min(max(guess, _SIZE_HINT.get(hint_key, 0)), int(0.9 * free)))

@@ -31,12 +31,30 @@ def mine_partitioned(offsets: torch.Tensor, items: torch.Tensor, n_items: int, m
     set). Returns, on every rank, the complete job-wide result."""
     import torch.distributed as dist
     world, rank = dist.get_world_size(group), dist.get_rank(group)
+
+    def allreduce(t):
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+
+    def any_rank(flag: bool) -> bool:
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=offsets.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        return bool(t.item())
+
     res = miner.mine_native(offsets, items, n_items, min_support, part=(rank, world), part_block=block,
-                            workspace=workspace, **kwargs)
+                            workspace=workspace, allreduce=allreduce if world > 1 else None,
+                            retry_sync=any_rank if world > 1 else None, **kwargs)
     if world == 1:
         return res
     device = offsets.device
     s = torch.cuda.current_stream().cuda_stream
+    marks = []
+
+    def mark(name):      # CUDA events between the merge's phases (read by bench.py after the step)
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        marks.append((name, e))
+
+    mark("mined")
     n2 = int(res.levels[1][1].numel()) if len(res.levels) >= 2 else 0
     # deepest level over all ranks
     kk = torch.tensor([len(res.levels)], dtype=torch.int64, device=device)
@@ -59,6 +77,7 @@ def mine_partitioned(offsets: torch.Tensor, items: torch.Tensor, n_items: int, m
     global_cnt = local_cnt.clone()
     dist.all_reduce(global_cnt, op=dist.ReduceOp.SUM, group=group)
     sizes = global_cnt.sum(dim=1, dtype=torch.int64).tolist()          # job-wide level sizes (one read-back)
+    mark("roots+counts")
     while sizes and sizes[-1] == 0:
         sizes.pop()
     max_k = 2 + len(sizes)
@@ -86,8 +105,10 @@ def mine_partitioned(offsets: torch.Tensor, items: torch.Tensor, n_items: int, m
         g_prev = g_here
         levels.append((it_g, ct_g))
         parents.append(par_g)
+    mark("placed")
     if total:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)      # every entry is written by exactly one rank
+    mark("allreduced")
     stats = dict(res.stats or {})
     stats["partition"] = {"kind": "classes", "world": world, "block": block,
                           "local_itemsets": int(sum(int(c.numel()) for _, c in res.levels[2:])),
@@ -95,4 +116,5 @@ def mine_partitioned(offsets: torch.Tensor, items: torch.Tensor, n_items: int, m
     out = miner.MineResult(res.n_playlists, res.t1, res.tk, res.row_items, levels, res.pair_counts, stats, parents)
     out.workspace = (res.workspace, flat)     # the first two levels still live in the mining workspace
     out.occurrences = res.occurrences
+    out.merge_marks = marks
     return out

@@ -30,7 +30,7 @@ def oracle_dict(off, items, n_items, s, max_len=0):
     return fpgrowth_c.fpgrowth(off, items, n_items, t1, tk, max_len=max_len).as_dict()
 
 
-@pytest.mark.parametrize("keep_words", [4, 8, 64, 256])
+@pytest.mark.parametrize("keep_words", [4, 8, 64, 256, 1024])
 @pytest.mark.parametrize("pair_impl", ["auto", "csr", "popc"])
 def test_native_loop_equals_oracle_and_python_loop(keep_words, pair_impl):
     # small keep_words push every level through the bit-extract route, 256 through the AND route
@@ -193,14 +193,16 @@ def test_rules_one_call_slices_add_up_and_workspace_grows():
     d_off, d_items = to_dev(off, items)
     res = miner.mine_native(d_off, d_items, 2000, 0.008)
     whole = miner.generate_rules(res, 0.3)
-    total, cs = 0, 0
-    for part in range(3):
-        ws = miner.Workspace(dev(), 1 << 16)                  # too small: grown to what the call says it needs
-        r = miner.generate_rules(res, 0.3, part=(part, 3), workspace=ws)
-        assert ws.nbytes > (1 << 16)
-        total += r.n_rules
-        cs = (cs + miner.rule_checksum(res, r)) & ((1 << 64) - 1)
-    assert total == whole.n_rules and cs == miner.rule_checksum(res, whole)
+    for pass1, n_parts in (("auto", 3), ("gather", 3), ("auto", 2), ("search", 2)):
+        total, cs = 0, 0
+        for part in range(n_parts):
+            ws = miner.Workspace(dev(), 1 << 16)              # too small: grown to what the call says it needs
+            r = miner.generate_rules(res, 0.3, part=(part, n_parts), workspace=ws, pass1=pass1)
+            assert ws.nbytes > (1 << 16)
+            assert r.stats["pass1"] == {"auto": "gather" if n_parts <= 2 else "search"}.get(pass1, pass1)
+            total += r.n_rules
+            cs = (cs + miner.rule_checksum(res, r)) & ((1 << 64) - 1)
+        assert total == whole.n_rules and cs == miner.rule_checksum(res, whole)
     with pytest.raises(_lib.KmlsError, match="max_rules"):
         miner.generate_rules(res, 0.3, max_rules=10)
     # the bare C call: a capacity error that names the bytes needed
