@@ -21,7 +21,11 @@ k_subtree_roots(const int32_t* __restrict__ par, int64_t n, const int32_t* __res
     const int32_t p = par[o];
     const int32_t r = root_prev ? __ldg(root_prev + p) : p;
     root[o] = r;
-    atomicAdd(per_root + r, 1);   // itemsets of one root are contiguous: mostly same-address, L2-combined
+    // itemsets of one root are contiguous, so most lanes of a warp hold the same root: one
+    // atomic per distinct root in the warp instead of one per lane
+    const uint32_t active = __activemask();
+    const uint32_t same = __match_any_sync(active, r);
+    if ((int)(threadIdx.x & 31) == __ffs(same) - 1) atomicAdd(per_root + r, __popc(same));
   }
 }
 

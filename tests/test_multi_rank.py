@@ -75,6 +75,75 @@ def test_sharded_counts_sum_to_global_counts_gloo():
     assert out.get(timeout=5) is True
 
 
+def _merge_worker(rank, world, port, out):
+    """The class partition's host logic in numpy over gloo: ownership of the frequent pairs by
+    interleaved blocks, per-root counts summed over the ranks, their scans, the placement of a
+    rank's itemsets at job-wide positions and the sum that completes the tables
+    (kmls_b200/multi.py does the same with kmls_subtree_roots / kmls_place_level on the GPU)."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from kmls_b200 import synth
+    from oracle import fpgrowth_c, mlxtend_restated as M
+    n, t, s, block = 4000, 120, 0.02, 3
+    off, ids = synth.zipf_playlists(n, t, mean_draws=12, alpha=0.8, seed=4)
+    t1, tk = M.thresholds(s, n)
+    full = fpgrowth_c.fpgrowth(off, ids, t, t1, tk).as_dict()
+    max_k = max(len(k) for k in full)
+    tables = [sorted(tuple(sorted(k)) for k in full if len(k) == kk) for kk in range(1, max_k + 1)]
+    index = [{x: i for i, x in enumerate(tb)} for tb in tables]
+    n2 = len(tables[1])
+    # what this rank mined: levels >= 3 restricted to the subtrees of its own pairs, parents local
+    own = [[x for x in tables[kk - 1] if (index[1][x[:2]] // block) % world == rank] for kk in range(3, max_k + 1)]
+    lidx = [{x: i for i, x in enumerate(tb)} for tb in own]
+    roots, local_cnt = [], np.zeros((max_k - 2, n2), np.int64)
+    for li, tb in enumerate(own):
+        par = np.array([index[1][x[:2]] if li == 0 else lidx[li - 1][x[:-1]] for x in tb], dtype=np.int64)
+        root = par if li == 0 else roots[li - 1][par] if len(par) else par
+        roots.append(root)
+        local_cnt[li] = np.bincount(root, minlength=n2) if len(root) else 0
+    g_cnt = torch.from_numpy(local_cnt.copy())
+    dist.all_reduce(g_cnt)
+    g_cnt = g_cnt.numpy()
+    ok = True
+    g_prev = None
+    for li, tb in enumerate(own):
+        kk = li + 3
+        n_glob = int(g_cnt[li].sum())
+        ok &= n_glob == len(tables[kk - 1])
+        g_start = np.concatenate([[0], np.cumsum(g_cnt[li])])[:-1]
+        l_start = np.concatenate([[0], np.cumsum(local_cnt[li])])[:-1]
+        g = g_start[roots[li]] + (np.arange(len(tb)) - l_start[roots[li]]) if len(tb) else np.zeros(0, np.int64)
+        items = np.zeros((n_glob, kk), np.int64)
+        par_g = np.zeros(n_glob, np.int64)
+        if len(tb):
+            items[g] = np.array(tb, dtype=np.int64)
+            lpar = np.array([index[1][x[:2]] if li == 0 else lidx[li - 1][x[:-1]] for x in tb], dtype=np.int64)
+            par_g[g] = lpar if li == 0 else g_prev[lpar]
+        ti, tp = torch.from_numpy(items), torch.from_numpy(par_g)
+        dist.all_reduce(ti)
+        dist.all_reduce(tp)
+        ok &= ti.numpy().tolist() == [list(x) for x in tables[kk - 1]]                    # the sorted job-wide table
+        ok &= tp.numpy().tolist() == [index[kk - 2][x[:-1]] for x in tables[kk - 1]]      # job-wide parent links
+        g_prev = g
+    if rank == 0:
+        out.put(bool(ok) and max_k >= 4)
+    dist.destroy_process_group()
+
+
+def test_class_partition_merge_gloo():
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_merge_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=180)
+        assert p.exitcode == 0
+    assert out.get(timeout=5) is True
+
+
 def _gpu_worker(rank, world, port, out, partition):
     sys.path.insert(0, ROOT)
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
