@@ -700,6 +700,49 @@ def run_gpu(args):
                              "to pinned host memory in 64 MB pieces"}
         del rules_pinned
 
+    # ---- the dense level-2 path (tcgen05 int8 GEMM) on a workload that takes it: one extra,
+    # small, separately reported measurement so that the tensor-core kernel has a number and a
+    # parity check in every default run (config 3's one-hot matrix is 1 % dense and takes the
+    # per-playlist route)
+    dense = None
+    if world == 1 and rank == 0 and not args.no_dense and name == "zipf_1Mx100k_s0.001":
+        try:
+            dname = "dense_200kx4k_s0.02"
+            o2, i2, t2, s2, c2 = make_data(dname, shard=0)
+            d_o2, d_i2 = torch.from_numpy(o2).to(device), torch.from_numpy(i2).to(device)
+            dspaces = {"mine": miner.Workspace(device), "rules": miner.Workspace(device)}
+            for _ in range(2):
+                r2 = miner.mine_native(d_o2, d_i2, t2, s2, workspace=dspaces["mine"])
+                del r2
+            torch.cuda.synchronize()
+            _lib.profile_begin()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+            for _ in range(args.steps):
+                r2 = miner.mine_native(d_o2, d_i2, t2, s2, workspace=dspaces["mine"])
+                ru2 = miner.generate_rules(r2, c2, workspace=dspaces["rules"])
+                if _ < args.steps - 1:
+                    del r2, ru2
+            ev1.record()
+            torch.cuda.synchronize()
+            prof2 = _lib.profile_report()
+            gemm = [(ms, w) for nm, lv, ms, w in prof2 if nm == "k_pair_gemm_i8"]
+            got2 = {"level_sizes": [int(c.numel()) for _, c in r2.levels], "itemset_checksum": str(miner.itemset_checksum(r2)),
+                    "n_rules": ru2.n_rules, "rule_checksum": str(miner.rule_checksum(r2, ru2))}
+            want2 = golden_for(dname, s2, len(o2) - 1)
+            dense = {"workload": dname, "pair_impl": r2.stats.get("pair_impl"), "ms_per_step": ev0.elapsed_time(ev1) / args.steps,
+                     "parity": None if want2 is None else all(got2[k_] == want2[k_] for k_ in got2)}
+            if gemm:
+                ms_g, w_g = sum(g[0] for g in gemm) / len(gemm), sum(g[1] for g in gemm) / len(gemm)
+                dense["k_pair_gemm_i8"] = {"ms": ms_g, "int8_ops": w_g, "achieved_tops": w_g / ms_g / 1e9,
+                                           "peak_tops": int8_peak, "frac": w_g / ms_g / 1e9 / int8_peak,
+                                           "peak_source": "2 x bf16_tflops of MEASURED_PEAKS.json",
+                                           "ops_counted": "2 * N * F(F+1)/2: upper triangle incl. diagonal"}
+            del r2, ru2, dspaces, d_o2, d_i2
+            log(f"[bench] dense extra: {dense}")
+        except Exception as e:      # noqa: BLE001 - the extra must never take the headline down
+            dense = {"error": repr(e)}
+
     verify = None
     if args.verify and world == 1:
         from oracle import fpgrowth_c, mlxtend_restated as M
@@ -777,6 +820,7 @@ def run_gpu(args):
             "merge_ms": info.get("merge_ms"),
             "top_kernel": top,
             "parity": parity,
+            "dense_extra": dense,
             "verify_full_size": verify,
         }
         emit(line)
@@ -810,6 +854,7 @@ def main():
     ap.add_argument("--verify", action="store_true",
                     help="after the run, mine the FULL workload with the CPU oracle (minutes) and compare level "
                          "sizes, the itemset checksum and the number of rules")
+    ap.add_argument("--no-dense", action="store_true", help="skip the extra measurement of the dense (tensor-core) level-2 path")
     ap.add_argument("--no-parity", action="store_true", help="skip the comparison with the committed oracle result")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong (default): the job's playlists are the same at every --gpus N, sliced over the "

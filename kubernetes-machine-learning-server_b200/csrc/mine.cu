@@ -138,6 +138,42 @@ k_pair_parents(const int32_t* __restrict__ items2, int64_t n2, int32_t* __restri
   }
 }
 
+// Class partition: which conditional rows of the pairs does THIS part need? A pair's row is
+// needed if the pair is one of the part's own (blocks part, part + n_parts, ... of `block` pairs)
+// or a later sibling of an own pair - i.e. if some own pair lies between the start of its class
+// and itself. Rows nobody here will read get width 0; need_row[a] marks the tracks whose
+// playlist lists the remaining rows are sampled at.
+__global__ void __launch_bounds__(256)
+k_level2_needs(const int32_t* __restrict__ par, int64_t n2, int block, int n_parts, int part,
+               int32_t* __restrict__ roww, int32_t* __restrict__ need_row) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += (int64_t)gridDim.x * blockDim.x) {
+    if (roww[i] == 0) continue;
+    const int32_t a = __ldg(par + i);
+    int64_t hi = i, step = 1;                      // par[hi] == a; gallop back to the class start
+    while (hi - step >= 0 && __ldg(par + hi - step) == a) {
+      hi -= step;
+      step <<= 1;
+    }
+    int64_t lo = max(hi - step, (int64_t)-1);      // par[lo] != a or lo == -1
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(par + mid) == a) hi = mid; else lo = mid;
+    }
+    const int64_t cs = hi;                         // first pair of the class
+    bool needed = false;
+    for (int64_t b = cs / block; b <= i / block && !needed; ++b) needed = (int)(b % n_parts) == part;
+    if (needed) need_row[a] = 1;
+    else roww[i] = 0;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+k_mask_counts(const int32_t* __restrict__ counts, const int32_t* __restrict__ need, int32_t n,
+              int32_t* __restrict__ out) {
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n; r += gridDim.x * blockDim.x)
+    out[r] = need[r] ? counts[r] : 0;
+}
+
 // ---- levels >= 3 --------------------------------------------------------------------------
 // Join sizing, one thread per itemset p of level k. Its candidates are its later siblings
 // (same parent; the table is sorted, so they follow it). ncand[p] = their number, wnew[p] =
@@ -1025,8 +1061,23 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&scratch, (int64_t)sbytes));
     KMLS_TRY(M.take(&tid_off, n_rows + 1));
     KMLS_TRY(kmls_row_alloc(par_k, n2, counts1, nullptr, keep_words, roww_k, s));
+    const int32_t* tid_counts = counts1;
+    int32_t *need_row = nullptr, *masked = nullptr;
+    if (opt.n_parts > 1) {
+      // a part of a class-partitioned job builds only the rows its own subtrees read
+      KMLS_TRY(M.take(&need_row, n_rows));
+      KMLS_TRY(M.take(&masked, n_rows));
+      KMLS_CUDA(cudaMemsetAsync(need_row, 0, sizeof(int32_t) * (size_t)n_rows, s));
+      k_level2_needs<<<grid_for(n2, 256, 8), 256, 0, s>>>(par_k, n2, std::max(opt.part_block, 1), opt.n_parts, opt.part,
+                                                          roww_k, need_row);
+      KMLS_LAUNCHED("k_level2_needs");
+      k_mask_counts<<<grid_for(n_rows, 256, 4), 256, 0, s>>>(counts1, need_row, n_rows, masked);
+      KMLS_LAUNCHED("k_mask_counts");
+      tid_counts = masked;
+      M.launches += 2;
+    }
     KMLS_TRY(kmls_exclusive_scan_i32(roww_k, n2, rowptr_k, scratch, sbytes, s));
-    KMLS_TRY(kmls_exclusive_scan_i32(counts1, n_rows, tid_off, scratch, sbytes, s));
+    KMLS_TRY(kmls_exclusive_scan_i32(tid_counts, n_rows, tid_off, scratch, sbytes, s));
     k_post<<<1, 1, 0, s>>>(rowptr_k + n2, tid_off + n_rows, nullptr, nullptr, M.box);
     KMLS_LAUNCHED("k_post");
     M.launches += 8;
@@ -1046,6 +1097,8 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     M.ws.release(tids);
     M.ws.release(tid_off);
     M.ws.release(scratch);
+    M.ws.release(need_row);
+    M.ws.release(masked);
   }
   M.ws.release(second2);
   M.ws.release(bitmap);

@@ -225,6 +225,7 @@ k_row_tidlists(const uint32_t* __restrict__ bitmap, int64_t row_words,
                const int64_t* __restrict__ tid_off, int32_t* __restrict__ tids) {
   __shared__ int warp_tot[8];
   __shared__ int carry;
+  if (tid_off[blockIdx.x + 1] == tid_off[blockIdx.x]) return;   // no list wanted for this row (block-uniform)
   const uint32_t* row = bitmap + (int64_t)blockIdx.x * row_words;
   int32_t* out = tids + tid_off[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;

@@ -31,6 +31,9 @@ CASES = {
     "zipf_1Mx100k_s0.001": ("zipf_1Mx100k_s0.001", None, True),
     "zipf_200kx20k_s0.004": ("zipf_200kx20k_s0.004", None, True),
     "dense_200kx4k_s0.02": ("dense_200kx4k_s0.02", None, True),
+    # BASELINE.json configs 1 and 2: stand-ins for the absent ds1 / ds2 CSVs
+    "mpd_standin_seed1_s0.05": ("mpd_standin_seed1_s0.05", None, True),
+    "mpd_standin_seed2_s0.05": ("mpd_standin_seed2_s0.05", None, True),
     # BASELINE.json config 4: the low-support sweep on the 1M set (mining only below 0.001: the
     # rule table of the lowest support does not fit anywhere)
     "zipf_1Mx100k_s0.05": ("zipf_1Mx100k_s0.001", 0.05, True),
