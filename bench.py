@@ -713,7 +713,8 @@ def run_gpu(args):
             dspaces = {"mine": miner.Workspace(device), "rules": miner.Workspace(device)}
             for _ in range(2):
                 r2 = miner.mine_native(d_o2, d_i2, t2, s2, workspace=dspaces["mine"])
-                del r2
+                ru2 = miner.generate_rules(r2, c2, workspace=dspaces["rules"])
+                del r2, ru2
             torch.cuda.synchronize()
             _lib.profile_begin()
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

@@ -475,6 +475,18 @@ int kmls_place_level(const int32_t* d_items, const int32_t* d_counts, const int3
                      const int64_t* d_local_start, const int32_t* d_gprev, int32_t* d_items_out,
                      int32_t* d_counts_out, int32_t* d_par_out, int32_t* d_g_out, kmls_stream_t stream);
 
+/* The same merge with 12 bytes per itemset on the wire instead of 4k + 8: only (last member,
+ * count, parent) are placed and summed over the ranks; kmls_rebuild_items then recreates the
+ * member lists of level k on every rank from the merged parent links, level after level:
+ * d_items[g] = d_items_prev[d_par[g]] (k-1 members) followed by d_last[g]. */
+int kmls_place_level_compact(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
+                             int64_t n, int32_t k, const int32_t* d_root, const int64_t* d_global_start,
+                             const int64_t* d_local_start, const int32_t* d_gprev, int32_t* d_last_out,
+                             int32_t* d_counts_out, int32_t* d_par_out, int32_t* d_g_out,
+                             kmls_stream_t stream);
+int kmls_rebuild_items(const int32_t* d_items_prev, int32_t k, const int32_t* d_par, const int32_t* d_last,
+                       int64_t n, int32_t* d_items, kmls_stream_t stream);
+
 /* ---- measurement plumbing (no counterpart in the reference) --------------------------------
  * kmls_profile_begin switches per-kernel timing on for the calling host thread: from then on
  * kmls_mine and kmls_rules bracket every kernel they launch with two CUDA events on the

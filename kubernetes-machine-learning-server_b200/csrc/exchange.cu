@@ -78,3 +78,68 @@ extern "C" int kmls_place_level(const int32_t* d_items, const int32_t* d_counts,
   KMLS_LAUNCHED("k_place_level");
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------
+// Compact form of the merge: an itemset is its parent plus one member, so the ranks exchange
+// only (last member, count, parent) per itemset - 12 bytes instead of 4k + 8 - and every rank
+// rebuilds the member lists level by level from the merged parent links.
+// ---------------------------------------------------------------------------------------
+namespace kmls {
+
+__global__ void __launch_bounds__(256)
+k_place_level_compact(const int32_t* __restrict__ items, const int32_t* __restrict__ counts,
+                      const int32_t* __restrict__ par, int64_t n, int k, const int32_t* __restrict__ root,
+                      const int64_t* __restrict__ global_start, const int64_t* __restrict__ local_start,
+                      const int32_t* __restrict__ gprev, int32_t* __restrict__ last_out,
+                      int32_t* __restrict__ counts_out, int32_t* __restrict__ par_out, int32_t* __restrict__ g_out) {
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < n; o += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t r = root[o];
+    const int64_t g = __ldg(global_start + r) + (o - __ldg(local_start + r));
+    g_out[o] = (int32_t)g;
+    last_out[g] = items[o * k + (k - 1)];
+    counts_out[g] = counts[o];
+    par_out[g] = gprev ? __ldg(gprev + par[o]) : par[o];
+  }
+}
+
+// items[g] = items_prev[par[g]] ++ last[g]
+__global__ void __launch_bounds__(256)
+k_rebuild_items(const int32_t* __restrict__ items_prev, int k, const int32_t* __restrict__ par,
+                const int32_t* __restrict__ last, int64_t n, int32_t* __restrict__ items) {
+  const int64_t total = n * k;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t g = e / k;
+    const int t = (int)(e - g * k);
+    items[e] = t < k - 1 ? __ldg(items_prev + (int64_t)__ldg(par + g) * (k - 1) + t) : __ldg(last + g);
+  }
+}
+
+}  // namespace kmls
+
+extern "C" int kmls_place_level_compact(const int32_t* d_items, const int32_t* d_counts, const int32_t* d_par,
+                                        int64_t n, int32_t k, const int32_t* d_root,
+                                        const int64_t* d_global_start, const int64_t* d_local_start,
+                                        const int32_t* d_gprev, int32_t* d_last_out, int32_t* d_counts_out,
+                                        int32_t* d_par_out, int32_t* d_g_out, kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && k >= 3, "kmls_place_level_compact: bad arguments");
+  if (n == 0) return 0;
+  KMLS_REQUIRE(d_items && d_counts && d_par && d_root && d_global_start && d_local_start && d_last_out &&
+                   d_counts_out && d_par_out && d_g_out, "kmls_place_level_compact: null pointer");
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
+  k_place_level_compact<<<grid, 256, 0, (cudaStream_t)stream>>>(d_items, d_counts, d_par, n, k, d_root,
+                                                               d_global_start, d_local_start, d_gprev, d_last_out,
+                                                               d_counts_out, d_par_out, d_g_out);
+  KMLS_LAUNCHED("k_place_level_compact");
+  return 0;
+}
+
+extern "C" int kmls_rebuild_items(const int32_t* d_items_prev, int32_t k, const int32_t* d_par,
+                                  const int32_t* d_last, int64_t n, int32_t* d_items, kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && k >= 2, "kmls_rebuild_items: bad arguments");
+  if (n == 0) return 0;
+  KMLS_REQUIRE(d_items_prev && d_par && d_last && d_items, "kmls_rebuild_items: null pointer");
+  int grid = (int)std::min<int64_t>((n * k + 255) / 256, (int64_t)num_sms() * 16);
+  k_rebuild_items<<<grid, 256, 0, (cudaStream_t)stream>>>(d_items_prev, k, d_par, d_last, n, d_items);
+  KMLS_LAUNCHED("k_rebuild_items");
+  return 0;
+}

@@ -174,6 +174,12 @@ k_mask_counts(const int32_t* __restrict__ counts, const int32_t* __restrict__ ne
     out[r] = need[r] ? counts[r] : 0;
 }
 
+// Bit-extract route: a row wider than this is squeezed in SEGMENTS of this many words, one work
+// unit each, so that one very wide row (a very popular prefix: hundreds of thousands of words at
+// 10M playlists) is not a single warp's serial job. Multiple of 32.
+constexpr int kSegWords = 8192;
+__host__ __device__ __forceinline__ int seg_count(int w_old) { return (w_old + kSegWords - 1) / kSegWords; }
+
 // ---- levels >= 3 --------------------------------------------------------------------------
 // Join sizing, one thread per itemset p of level k. Its candidates are its later siblings
 // (same parent; the table is sorted, so they follow it). ncand[p] = their number, wnew[p] =
@@ -212,7 +218,7 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
       const int32_t ws = (((__ldg(counts + p) + 31) >> 5) + 3) & ~3;
       const bool squeeze = w_old > keep_words && (int64_t)ws * 100 <= (int64_t)w_old * squeeze_pct;
       w = squeeze ? ws : w_old;
-      if (m > 0 && squeeze) wide += (m + 7) >> 3;   // chunks of kChunk = 8 candidates
+      if (m > 0 && squeeze) wide += ((m + 7) >> 3) * seg_count(w_old);   // (chunk of 8 candidates) x (row segment)
     }
     ncand[p] = m;
     wnew[p] = w;
@@ -285,9 +291,10 @@ k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
     const int w = roww_old[p];
     if (m == 0) continue;
     if (wnew[p] != w) {         // bit-extract route: k_count_project walks this list (order is irrelevant)
-      const int chunks = (m + 7) >> 3;
-      const int base = atomicAdd(wide_fill, chunks);
-      for (int c = 0; c < chunks; ++c) wide_list[base + c] = make_int2((int32_t)p, c << 3);
+      const int chunks = (m + 7) >> 3, segs = seg_count(w);
+      int at = atomicAdd(wide_fill, chunks * segs);
+      for (int c = 0; c < chunks; ++c)
+        for (int sg = 0; sg < segs; ++sg) wide_list[at++] = make_int2((int32_t)p, c | (sg << 16));
       continue;
     }
     const I2 o = off2[p];
@@ -407,7 +414,7 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
   __shared__ int64_t s_src[8][kChunk], s_dst[8][kChunk];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t li = (int64_t)blockIdx.x * 8 + warp; li < n_wide; li += (int64_t)gridDim.x * 8) {
-    const int2 unit = __ldg(wide_list + li);   // (parent, first candidate of the chunk)
+    const int2 unit = __ldg(wide_list + li);   // (parent, chunk of 8 candidates | row segment << 16)
     const int64_t p = unit.x;
     const int m = __ldg(ncand + p);
     if (m == 0) continue;                        // warp-uniform
@@ -419,7 +426,9 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
     const int nv = w_old >> 2;
     const uint4* msk4 = reinterpret_cast<const uint4*>(rowp);
     {
-      const int i0 = unit.y;
+      const int i0 = (unit.y & 0xffff) << 3;
+      const int seg = unit.y >> 16;
+      const int seg_lo = seg * kSegWords, seg_hi = min(seg_lo + kSegWords, w_old);   // this unit's mask words
       const int mc = min(kChunk, m - i0);
       const int64_t my_src = lane < mc ? __ldg(rowptr_old + p + 1 + i0 + lane) : 0;
       int acc[kChunk];
@@ -429,25 +438,36 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
         acc[t] = 0;
         rows[t] = reinterpret_cast<const uint4*>(arena_old + __shfl_sync(0xffffffffu, my_src, t));
       }
+      // every segment's unit counts the WHOLE row (cheap next to the squeeze, and it needs the
+      // number of mask bits before its segment anyway: that is where its output starts)
+      int bits_lo = 0, bits_hi = 0;
       for (int v = lane; v < nv; v += 32) {
         const uint4 mw = ldg4(msk4 + v);
+        const int pm = popc4(mw);
+        if (4 * v < seg_lo) bits_lo += pm;
+        if (4 * v < seg_hi) bits_hi += pm;
 #pragma unroll
         for (int t = 0; t < kChunk; ++t)
           if (t < mc) acc[t] += popc4(and4(ldg4(rows[t] + v), mw));
       }
+      bits_lo = warp_sum(bits_lo);
+      bits_hi = warp_sum(bits_hi);
+      const bool last_seg = seg_hi >= w_old;
+      // output words this unit owns: those whose first bit lies in its segment's bit range
+      const int own_lo = (bits_lo + 31) >> 5, own_hi = last_seg ? w_new : (bits_hi + 31) >> 5;
       uint32_t surv = 0;
 #pragma unroll
       for (int t = 0; t < kChunk; ++t) {
         if (t < mc) {
           const int cnt = warp_sum(acc[t]);
-          if (lane == 0) {
+          if (lane == 0 && seg == 0) {
             cand_cnt[o.a + i0 + t] = cnt;
             cand_p[o.a + i0 + t] = (int32_t)p;
           }
           if (cnt >= thr) surv |= 1u << t;
         }
       }
-      if (surv == 0) continue;
+      if (surv == 0 || own_lo >= own_hi) continue;
       const int ns = __popc(surv);
       __syncwarp();
       if (lane < mc && ((surv >> lane) & 1u)) {
@@ -457,8 +477,9 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
       }
       for (int i = lane; i < ns * 36; i += 32) sbuf[warp][i / 36][i % 36] = 0;
       __syncwarp();
-      int base = 0;                            // bits emitted so far (the same for every row)
-      for (int blk = 0; blk < w_old; blk += 32) {
+      int base = bits_lo;                      // bits emitted before this block (the same for every row)
+      // past the segment's end only until the last owned word is complete
+      for (int blk = seg_lo; blk < w_old && (blk < seg_hi || (base >> 5) < own_hi); blk += 32) {
         const int w = blk + lane;
         const uint32_t mw = w < w_old ? __ldg(rowp + w) : 0u;
         uint32_t xs[kChunk];
@@ -514,8 +535,8 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
           const uint32_t v0 = buf[lane], v1 = lane < 4 ? buf[32 + lane] : 0u;
           const uint32_t partial = buf[full];
           __syncwarp();
-          if (lane < full && w0 + lane < w_new) dst[w0 + lane] = v0;
-          if (lane < 4 && 32 + lane < full && w0 + 32 + lane < w_new) dst[w0 + 32 + lane] = v1;
+          if (lane < full && w0 + lane >= own_lo && w0 + lane < own_hi) dst[w0 + lane] = v0;
+          if (lane < 4 && 32 + lane < full && w0 + 32 + lane >= own_lo && w0 + 32 + lane < own_hi) dst[w0 + 32 + lane] = v1;
           buf[lane] = lane == 0 ? partial : 0u;
           if (lane < 4) buf[32 + lane] = 0u;
         }
@@ -525,9 +546,10 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
       for (int t = 0; t < ns; ++t) {
         uint32_t* dst = arena_new + s_dst[warp][t];
         int done = base >> 5;
-        if ((base & 31) && lane == 0 && done < w_new) dst[done] = sbuf[warp][t][0];
+        if ((base & 31) && lane == 0 && done >= own_lo && done < own_hi) dst[done] = sbuf[warp][t][0];
         if (base & 31) ++done;
-        for (int i = done + lane; i < w_new; i += 32) dst[i] = 0u;
+        if (last_seg)
+          for (int i = max(done, own_lo) + lane; i < w_new; i += 32) dst[i] = 0u;
       }
       __syncwarp();
     }
@@ -819,8 +841,17 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   const int64_t nnz = M.box[0];
   KMLS_REQUIRE(nnz >= 0, "kmls_mine: offsets are not ascending");
   {
-    ProfScope ps("k_item_histogram", s, 4.0 * (double)nnz, 1);
-    KMLS_TRY(kmls_item_histogram(d_items, nnz, n_items, occ, s));
+    // ranks of a class-partitioned job that can sum over the ranks each count a share of the
+    // occurrences (cut at multiples of 4 ids: the kernel loads 128 bits at a time)
+    const bool shared_hist = opt.allreduce_i32 != nullptr && opt.n_parts > 1;
+    const int64_t i_lo = shared_hist ? (nnz * opt.part / opt.n_parts) & ~(int64_t)3 : 0;
+    const int64_t i_hi = shared_hist && opt.part + 1 < opt.n_parts ? (nnz * (opt.part + 1) / opt.n_parts) & ~(int64_t)3 : nnz;
+    {
+      ProfScope ps("k_item_histogram", s, 4.0 * (double)(i_hi - i_lo), 1);
+      KMLS_TRY(kmls_item_histogram(d_items + i_lo, i_hi - i_lo, n_items, occ, s));
+    }
+    if (shared_hist && opt.allreduce_i32(opt.allreduce_ctx, occ, n_items, s) != 0)
+      return fail(kArgError, "kmls_mine: the allreduce callback failed");
   }
   ++M.launches;
   const int32_t thr1 = std::max(t1, 1);

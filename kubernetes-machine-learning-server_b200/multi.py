@@ -8,7 +8,8 @@ blocks r, r + R, r + 2R, ... of ``block`` consecutive pairs with NO communicatio
 Afterwards the ranks' tables are merged into the job-wide tables - in the order of the root
 pair, which is the sorted order a single GPU produces, so the result (and everything derived
 from it: rule ids, checksums) is bit-identical to the 1-GPU result. Cost of the merge: one
-small allreduce of per-pair itemset counts and one sum-allreduce of the tables themselves.
+small allreduce of per-pair itemset counts and one sum-allreduce of (last member, count, parent)
+per itemset - 12 bytes each; the member lists are rebuilt locally from the merged parent links.
 
 The alternative - sharding the PLAYLISTS and summing every level's candidate counts with an
 allreduce (``miner.mine_csr(group=...)``, BASELINE.json's sketch) - replicates all per-candidate
@@ -81,40 +82,51 @@ def mine_partitioned(offsets: torch.Tensor, items: torch.Tensor, n_items: int, m
     while sizes and sizes[-1] == 0:
         sizes.pop()
     max_k = 2 + len(sizes)
-    # one flat buffer for all merged tables: level k takes n*(k+2) int32 (members, count, parent)
-    total = sum(n * (k + 2) for k, n in zip(range(3, max_k + 1), sizes))
+    # one flat buffer for what is exchanged: level k takes 3n int32 (last member, count, parent) -
+    # an itemset is its parent plus one member, so the member lists are rebuilt locally afterwards
+    total = sum(3 * n for n in sizes)
     flat = torch.zeros(max(total, 1), dtype=torch.int32, device=device)
     scratch = torch.empty(int(_lib.value("kmls_scan_scratch_bytes", n2)), dtype=torch.uint8, device=device)
     g_start = torch.empty(n2 + 1, dtype=torch.int64, device=device)
     l_start = torch.empty(n2 + 1, dtype=torch.int64, device=device)
     levels, parents = list(res.levels[:2]), list(res.parents[:1])
-    at, g_prev = 0, None
+    at, g_prev, merged = 0, None, []
     for k, n_glob in zip(range(3, max_k + 1), sizes):
-        it_g = flat[at:at + n_glob * k].view(n_glob, k)
-        ct_g = flat[at + n_glob * k:at + n_glob * (k + 1)]
-        par_g = flat[at + n_glob * (k + 1):at + n_glob * (k + 2)]
-        at += n_glob * (k + 2)
+        last_g = flat[at:at + n_glob]
+        ct_g = flat[at + n_glob:at + 2 * n_glob]
+        par_g = flat[at + 2 * n_glob:at + 3 * n_glob]
+        at += 3 * n_glob
         n_loc = int(roots[k - 3].numel())
         g_here = torch.empty(max(n_loc, 1), dtype=torch.int32, device=device)[:n_loc]
         if n_loc:
             _lib.call("kmls_exclusive_scan_i32", global_cnt[k - 3], n2, g_start, scratch, scratch.numel(), s)
             _lib.call("kmls_exclusive_scan_i32", local_cnt[k - 3], n2, l_start, scratch, scratch.numel(), s)
             it_l, ct_l = res.levels[k - 1]
-            _lib.call("kmls_place_level", it_l, ct_l, res.parents[k - 2], n_loc, k, roots[k - 3], g_start, l_start,
-                      g_prev if k > 3 else 0, it_g, ct_g, par_g, g_here, s)
+            _lib.call("kmls_place_level_compact", it_l, ct_l, res.parents[k - 2], n_loc, k, roots[k - 3], g_start,
+                      l_start, g_prev if k > 3 else 0, last_g, ct_g, par_g, g_here, s)
         g_prev = g_here
-        levels.append((it_g, ct_g))
-        parents.append(par_g)
+        merged.append((k, n_glob, last_g, ct_g, par_g))
     mark("placed")
     if total:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)      # every entry is written by exactly one rank
     mark("allreduced")
+    members = torch.empty(max(sum(n * k for k, n in zip(range(3, max_k + 1), sizes)), 1), dtype=torch.int32,
+                          device=device)
+    at, prev_items = 0, res.levels[1][0]
+    for k, n_glob, last_g, ct_g, par_g in merged:
+        it_g = members[at:at + n_glob * k].view(n_glob, k)
+        at += n_glob * k
+        _lib.call("kmls_rebuild_items", prev_items, k, par_g, last_g, n_glob, it_g, s)
+        levels.append((it_g, ct_g))
+        parents.append(par_g)
+        prev_items = it_g
+    mark("rebuilt")
     stats = dict(res.stats or {})
     stats["partition"] = {"kind": "classes", "world": world, "block": block,
                           "local_itemsets": int(sum(int(c.numel()) for _, c in res.levels[2:])),
                           "merged_bytes": int(total) * 4}
     out = miner.MineResult(res.n_playlists, res.t1, res.tk, res.row_items, levels, res.pair_counts, stats, parents)
-    out.workspace = (res.workspace, flat)     # the first two levels still live in the mining workspace
+    out.workspace = (res.workspace, flat, members)   # the first two levels still live in the mining workspace
     out.occurrences = res.occurrences
     out.merge_marks = marks
     return out

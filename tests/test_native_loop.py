@@ -56,6 +56,29 @@ def test_native_loop_wide_rows():
     assert any(l.get("row_words_total", 0) for l in res.stats["levels"])
 
 
+def test_native_loop_rows_wider_than_one_segment():
+    # 600k playlists: the popular tracks' conditional rows are > 8192 words, so the bit-extract
+    # route splits them into several segment units whose outputs must tile the new row exactly
+    n, t, s_ = 600_000, 400, 0.02
+    off, items = synth.zipf_playlists(n, t, mean_draws=10, alpha=1.0, seed=9)
+    d_off, d_items = to_dev(off, items)
+    res = miner.mine_native(d_off, d_items, t, s_)
+    t1, tk = M.thresholds(s_, n)
+    ref = fpgrowth_c.fpgrowth(off, items, t, t1, tk, store=False)
+    assert [int(c.numel()) for _, c in res.levels] == ref.level_counts[1:len(res.levels) + 1].tolist()
+    assert miner.itemset_checksum(res) == ref.checksum
+    assert len(res.levels) >= 4 and max(l.get("row_words_total", 0) for l in res.stats["levels"]) > 0
+    # the same result when nothing is squeezed at all and when everything is
+    for kw, sq in ((1024, 0), (4, 100)):
+        import os
+        os.environ["KMLS_SQUEEZE_PCT"] = str(sq)
+        try:
+            r2 = miner.mine_native(d_off, d_items, t, s_, keep_words=kw)
+        finally:
+            os.environ.pop("KMLS_SQUEEZE_PCT", None)
+        assert miner.itemset_checksum(r2) == ref.checksum
+
+
 @pytest.mark.parametrize("seed", range(8))
 def test_native_loop_random_small(seed):
     rng = np.random.default_rng(100 + seed)
