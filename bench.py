@@ -203,7 +203,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([x.strip() for x in out.strip().split(",")])
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(0.05)
 
     def summary(self):
         self.stop_flag.set()
@@ -369,6 +369,14 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------ GPU arm
+def partition_of(args):
+    """--partition auto: the candidate space is split (classes) unless the job is config 5, whose
+    10M playlists make the per-playlist work dominate: there the playlists are sharded."""
+    if args.partition != "auto":
+        return args.partition
+    return "playlists" if WORKLOADS[args.workload][0] >= 4_000_000 else "classes"
+
+
 def load_job_data(args, rank, world, barrier):
     """(offsets, items, n_tracks, min_support, min_confidence, n_total, strong) of this rank.
     partition "classes": every rank holds the job's WHOLE playlist set (the candidate space is
@@ -376,7 +384,7 @@ def load_job_data(args, rank, world, barrier):
     name = args.workload
     fixed = name in TOTAL_IS_FIXED
     strong = fixed or args.scaling == "strong"
-    whole = args.partition == "classes" or world == 1
+    whole = partition_of(args) == "classes" or world == 1
     if fixed:
         # generated in 8 shards; every rank first makes "its" shards (they land in the cache)
         if 8 % world:
@@ -434,7 +442,8 @@ def run_gpu(args):
     h_off = torch.from_numpy(off).pin_memory()
     h_items = torch.from_numpy(items).pin_memory()
     d_off, d_items = h_off.to(device), h_items.to(device)
-    by_playlists = world > 1 and args.partition == "playlists"
+    partition = partition_of(args)
+    by_playlists = world > 1 and partition == "playlists"
     # device memory of the one-call entry points, kept across steps (the tables a step returns
     # are views of it and are dropped before the next step)
     spaces = {"mine": miner.Workspace(device, int(args.mine_ws_gb * (1 << 30))),
@@ -489,7 +498,10 @@ def run_gpu(args):
         sampler.start()
     _lib.CALLS.clear()
     _lib.EXTRA_LAUNCHES = 0
-    _lib.TRACE = []
+    # the Python-driven loop (playlist sharding) makes hundreds of library calls per step: their
+    # per-call events would weigh on the timed region, so that path is traced in extra steps
+    trace_in_loop = not by_playlists
+    _lib.TRACE = [] if trace_in_loop else None
     _lib.profile_begin()          # per-kernel CUDA events inside kmls_mine / kmls_rules
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -500,9 +512,16 @@ def run_gpu(args):
     e1.record()
     barrier()
     clocks = sampler.summary()
+    launches_timed = _lib.kernel_launches()
+    if not trace_in_loop:
+        _lib.TRACE = []
+        for _ in range(args.steps):
+            res, rules = step(d_off, d_items)
+            del res, rules
+        torch.cuda.synchronize()
     trace, _lib.TRACE = _lib.TRACE, None
     prof = _lib.profile_report()
-    launches = _lib.kernel_launches()
+    launches = launches_timed
     step_s = max_over_ranks(e0.elapsed_time(e1) / 1e3 / args.steps)
 
     # ---- per-kernel times and roofline objects ---------------------------------------------
@@ -593,7 +612,8 @@ def run_gpu(args):
     def e2e_step():
         res, rules = kmls_b200.mine_ids(h_off, h_items, n_tracks, s, None if args.no_rules else conf,
                                         host_tables=host_tables if rank == 0 else None, split_rules=True,
-                                        partition=args.partition, workspaces=spaces, pair_impl=args.pair_impl)
+                                        partition=partition, workspaces=spaces, pair_impl=args.pair_impl,
+                                        sharded=by_playlists, n_playlists_total=n_total)
         n_rules = rules.n_rules if rules is not None else 0
         torch.cuda.synchronize()
         del res, rules
@@ -630,7 +650,10 @@ def run_gpu(args):
             d2h, _ = e2e_step()
         barrier()
         e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
-        h2d = h_off.numel() * 8 + h_items.numel() * 4
+        # per rank: the offsets, and - when every rank needs all playlists - 1/R of the ids (the
+        # ranks exchange their pieces over NVLink, api.mine_ids)
+        ids_up = h_items.numel() if (world == 1 or by_playlists) else (h_items.numel() + world - 1) // world
+        h2d = h_off.numel() * 8 + ids_up * 4
 
     # ---- parity: one more (untimed) pass, compared on the device with the CPU oracle's
     # committed result for this whole job (tests/golden/full_size.json) - at every N
@@ -680,8 +703,8 @@ def run_gpu(args):
     if args.rules_to_host and not args.no_rules:
         def rules_step():
             res, rules = kmls_b200.mine_ids(h_off, h_items, n_tracks, s, conf, host_tables=host_tables if rank == 0 else None,
-                                            split_rules=True, partition=args.partition, workspaces=spaces,
-                                            pair_impl=args.pair_impl)
+                                            split_rules=True, partition=partition, workspaces=spaces,
+                                            pair_impl=args.pair_impl, sharded=by_playlists, n_playlists_total=n_total)
             hr = kmls_b200.api.rules_to_pinned(rules, rules_pinned)
             torch.cuda.synchronize()
             n = rules.n_rules
@@ -817,7 +840,7 @@ def run_gpu(args):
             "level_sizes": info.get("levels"),
             "kernels": {k: {"ms_per_step": v["ms"] / args.steps, "calls_per_step": v["calls"] / args.steps}
                         for k, v in sorted(per.items(), key=lambda kv: -kv[1]["ms"])},
-            "partition": info.get("stats", {}).get("partition"),
+            "partition": info.get("stats", {}).get("partition") or ({"kind": "playlists", "world": world} if by_playlists else None),
             "merge_ms": info.get("merge_ms"),
             "top_kernel": top,
             "parity": parity,
@@ -860,7 +883,7 @@ def main():
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"],
                     help="strong (default): the job's playlists are the same at every --gpus N, sliced over the "
                          "ranks; weak: every rank generates its own set of the workload's size")
-    ap.add_argument("--partition", default="classes", choices=["classes", "playlists"],
+    ap.add_argument("--partition", default="auto", choices=["auto", "classes", "playlists"],
                     help="multi-GPU: classes (default) = every rank holds all playlists and mines its share of the "
                          "candidate space, no per-level exchange; playlists = row-sharded playlists with one count "
                          "allreduce per level")
