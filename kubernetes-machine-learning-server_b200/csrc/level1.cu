@@ -15,24 +15,51 @@ namespace kmls {
 // track's support (a track repeated inside a playlist is counted twice here), used only to
 // decide which rows are worth materialising; exact supports come from K1 below.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_item_histogram(const int32_t* __restrict__ items,
-                                                        int64_t nnz, int32_t n_items,
-                                                        int32_t* __restrict__ occ) {
+// Popular tracks make this a contended histogram (the most frequent track of a Zipfian
+// catalogue is in most playlists: a million increments of one address), so every CTA first
+// counts into a direct-mapped cache of kHistSlots (track id, count) pairs in shared memory and
+// only ids that lose their slot to another id go straight to the global counters; the cache
+// is flushed once at the end. Few, large CTAs keep the number of flushes small.
+constexpr int kHistSlots = 4096;
+constexpr int kHistThreads = 1024;
+
+__device__ __forceinline__ void hist_add(int32_t v, int32_t n_items, int32_t* tag, int32_t* cnt,
+                                         int32_t* __restrict__ occ) {
+  if ((uint32_t)v >= (uint32_t)n_items) return;
+  const int slot = v & (kHistSlots - 1);
+  int32_t owner = tag[slot];                 // -1 -> an id exactly once, never changed afterwards
+  if (owner == -1) {
+    owner = atomicCAS(tag + slot, -1, v);
+    if (owner == -1) owner = v;              // this thread claimed the slot
+  }
+  if (owner == v) atomicAdd(cnt + slot, 1);
+  else atomicAdd(occ + v, 1);
+}
+
+__global__ void __launch_bounds__(kHistThreads) k_item_histogram(const int32_t* __restrict__ items,
+                                                                 int64_t nnz, int32_t n_items,
+                                                                 int32_t* __restrict__ occ) {
+  __shared__ int32_t tag[kHistSlots], cnt[kHistSlots];
+  for (int i = threadIdx.x; i < kHistSlots; i += blockDim.x) {
+    tag[i] = -1;
+    cnt[i] = 0;
+  }
+  __syncthreads();
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int64_t n4 = nnz >> 2;
   const int4* items4 = reinterpret_cast<const int4*>(items);
   for (int64_t i = tid; i < n4; i += stride) {
-    int4 v = __ldg(items4 + i);
-    if ((uint32_t)v.x < (uint32_t)n_items) atomicAdd(occ + v.x, 1);
-    if ((uint32_t)v.y < (uint32_t)n_items) atomicAdd(occ + v.y, 1);
-    if ((uint32_t)v.z < (uint32_t)n_items) atomicAdd(occ + v.z, 1);
-    if ((uint32_t)v.w < (uint32_t)n_items) atomicAdd(occ + v.w, 1);
+    const int4 v = __ldg(items4 + i);
+    hist_add(v.x, n_items, tag, cnt, occ);
+    hist_add(v.y, n_items, tag, cnt, occ);
+    hist_add(v.z, n_items, tag, cnt, occ);
+    hist_add(v.w, n_items, tag, cnt, occ);
   }
-  for (int64_t i = (n4 << 2) + tid; i < nnz; i += stride) {
-    int32_t v = __ldg(items + i);
-    if ((uint32_t)v < (uint32_t)n_items) atomicAdd(occ + v, 1);
-  }
+  for (int64_t i = (n4 << 2) + tid; i < nnz; i += stride) hist_add(__ldg(items + i), n_items, tag, cnt, occ);
+  __syncthreads();
+  for (int i = threadIdx.x; i < kHistSlots; i += blockDim.x)
+    if (cnt[i]) atomicAdd(occ + tag[i], cnt[i]);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -149,9 +176,9 @@ extern "C" int kmls_item_histogram(const int32_t* d_items, int64_t nnz, int32_t 
   if (nnz == 0) return 0;
   KMLS_REQUIRE(d_items != nullptr, "kmls_item_histogram: d_items is null");
   KMLS_REQUIRE(((uintptr_t)d_items & 15) == 0, "kmls_item_histogram: d_items must be 16-byte aligned");
-  int64_t want = (nnz / 4 + 255) / 256;
-  int grid = (int)std::min<int64_t>(std::max<int64_t>(want, 1), (int64_t)num_sms() * 16);
-  k_item_histogram<<<grid, 256, 0, s>>>(d_items, nnz, n_items, d_occ);
+  int64_t want = (nnz / 4 + kHistThreads - 1) / kHistThreads;
+  int grid = (int)std::min<int64_t>(std::max<int64_t>(want, 1), (int64_t)num_sms() * 2);
+  k_item_histogram<<<grid, kHistThreads, 0, s>>>(d_items, nnz, n_items, d_occ);
   KMLS_LAUNCHED("k_item_histogram");
   return 0;
 }
