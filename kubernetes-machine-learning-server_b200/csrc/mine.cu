@@ -218,7 +218,7 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
       const int32_t ws = (((__ldg(counts + p) + 31) >> 5) + 3) & ~3;
       const bool squeeze = w_old > keep_words && (int64_t)ws * 100 <= (int64_t)w_old * squeeze_pct;
       w = squeeze ? ws : w_old;
-      if (m > 0 && squeeze) wide += ((m + 7) >> 3) * seg_count(w_old);   // (chunk of 8 candidates) x (row segment)
+      if (m > 0 && squeeze) wide += seg_count(w_old);   // one work unit per row segment
     }
     ncand[p] = m;
     wnew[p] = w;
@@ -291,10 +291,9 @@ k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
     const int w = roww_old[p];
     if (m == 0) continue;
     if (wnew[p] != w) {         // bit-extract route: k_count_project walks this list (order is irrelevant)
-      const int chunks = (m + 7) >> 3, segs = seg_count(w);
-      int at = atomicAdd(wide_fill, chunks * segs);
-      for (int c = 0; c < chunks; ++c)
-        for (int sg = 0; sg < segs; ++sg) wide_list[at++] = make_int2((int32_t)p, c | (sg << 16));
+      const int segs = seg_count(w);
+      int at = atomicAdd(wide_fill, segs);
+      for (int sg = 0; sg < segs; ++sg) wide_list[at++] = make_int2((int32_t)p, sg);
       continue;
     }
     const I2 o = off2[p];
@@ -411,10 +410,10 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
                 int keep_words, uint32_t* __restrict__ arena_new, int32_t* __restrict__ cand_cnt,
                 int32_t* __restrict__ cand_p) {
   __shared__ uint32_t sbuf[8][kChunk][36];
-  __shared__ int64_t s_src[8][kChunk], s_dst[8][kChunk];
+  __shared__ int64_t s_src[8][2 * kChunk], s_dst[8][2 * kChunk];   // queue of surviving candidates
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int64_t li = (int64_t)blockIdx.x * 8 + warp; li < n_wide; li += (int64_t)gridDim.x * 8) {
-    const int2 unit = __ldg(wide_list + li);   // (parent, chunk of 8 candidates | row segment << 16)
+    const int2 unit = __ldg(wide_list + li);   // (parent, row segment)
     const int64_t p = unit.x;
     const int m = __ldg(ncand + p);
     if (m == 0) continue;                        // warp-uniform
@@ -422,59 +421,17 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
     const I2 o = off2[p];
     const uint32_t* rowp = arena_old + __ldg(rowptr_old + p);
     if (w_old == w_new) continue;            // rows that keep their column space: k_count_and
-    // ---- bit-extract route ----
     const int nv = w_old >> 2;
     const uint4* msk4 = reinterpret_cast<const uint4*>(rowp);
-    {
-      const int i0 = (unit.y & 0xffff) << 3;
-      const int seg = unit.y >> 16;
-      const int seg_lo = seg * kSegWords, seg_hi = min(seg_lo + kSegWords, w_old);   // this unit's mask words
-      const int mc = min(kChunk, m - i0);
-      const int64_t my_src = lane < mc ? __ldg(rowptr_old + p + 1 + i0 + lane) : 0;
-      int acc[kChunk];
-      const uint4* rows[kChunk];
-#pragma unroll
-      for (int t = 0; t < kChunk; ++t) {
-        acc[t] = 0;
-        rows[t] = reinterpret_cast<const uint4*>(arena_old + __shfl_sync(0xffffffffu, my_src, t));
-      }
-      // every segment's unit counts the WHOLE row (cheap next to the squeeze, and it needs the
-      // number of mask bits before its segment anyway: that is where its output starts)
-      int bits_lo = 0, bits_hi = 0;
-      for (int v = lane; v < nv; v += 32) {
-        const uint4 mw = ldg4(msk4 + v);
-        const int pm = popc4(mw);
-        if (4 * v < seg_lo) bits_lo += pm;
-        if (4 * v < seg_hi) bits_hi += pm;
-#pragma unroll
-        for (int t = 0; t < kChunk; ++t)
-          if (t < mc) acc[t] += popc4(and4(ldg4(rows[t] + v), mw));
-      }
-      bits_lo = warp_sum(bits_lo);
-      bits_hi = warp_sum(bits_hi);
-      const bool last_seg = seg_hi >= w_old;
-      // output words this unit owns: those whose first bit lies in its segment's bit range
-      const int own_lo = (bits_lo + 31) >> 5, own_hi = last_seg ? w_new : (bits_hi + 31) >> 5;
-      uint32_t surv = 0;
-#pragma unroll
-      for (int t = 0; t < kChunk; ++t) {
-        if (t < mc) {
-          const int cnt = warp_sum(acc[t]);
-          if (lane == 0 && seg == 0) {
-            cand_cnt[o.a + i0 + t] = cnt;
-            cand_p[o.a + i0 + t] = (int32_t)p;
-          }
-          if (cnt >= thr) surv |= 1u << t;
-        }
-      }
-      if (surv == 0 || own_lo >= own_hi) continue;
-      const int ns = __popc(surv);
-      __syncwarp();
-      if (lane < mc && ((surv >> lane) & 1u)) {
-        const int slot = __popc(surv & ((1u << lane) - 1u));
-        s_src[warp][slot] = my_src;
-        s_dst[warp][slot] = o.b + (int64_t)(i0 + lane) * w_new;
-      }
+    const int seg = unit.y;
+    const int seg_lo = seg * kSegWords, seg_hi = min(seg_lo + kSegWords, w_old);   // this unit's mask words
+    const bool last_seg = seg_hi >= w_old;
+    int own_lo = 0, own_hi = 0, bits_lo = 0;
+    int queued = 0;                            // survivors waiting in s_src / s_dst (warp-uniform)
+
+    // The squeeze of the first `ns` queued rows: 32 mask words per step; the compress network's
+    // move masks are derived once per mask word for all `ns` rows.
+    auto squeeze = [&](int ns) {
       for (int i = lane; i < ns * 36; i += 32) sbuf[warp][i / 36][i % 36] = 0;
       __syncwarp();
       int base = bits_lo;                      // bits emitted before this block (the same for every row)
@@ -552,7 +509,82 @@ k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restric
           for (int i = max(done, own_lo) + lane; i < w_new; i += 32) dst[i] = 0u;
       }
       __syncwarp();
+    };
+
+    for (int i0 = 0; i0 < m; i0 += kChunk) {
+      const int mc = min(kChunk, m - i0);
+      const int64_t my_src = lane < mc ? __ldg(rowptr_old + p + 1 + i0 + lane) : 0;
+      int acc[kChunk];
+      const uint4* rows[kChunk];
+#pragma unroll
+      for (int t = 0; t < kChunk; ++t) {
+        acc[t] = 0;
+        rows[t] = reinterpret_cast<const uint4*>(arena_old + __shfl_sync(0xffffffffu, my_src, t));
+      }
+      // every segment's unit counts the WHOLE row (cheap next to the squeeze); the first chunk
+      // also counts the mask bits before its segment: that is where its output starts
+      int b_lo = 0, b_hi = 0;
+      for (int v = lane; v < nv; v += 32) {
+        const uint4 mw = ldg4(msk4 + v);
+        if (i0 == 0) {
+          const int pm = popc4(mw);
+          if (4 * v < seg_lo) b_lo += pm;
+          if (4 * v < seg_hi) b_hi += pm;
+        }
+#pragma unroll
+        for (int t = 0; t < kChunk; ++t)
+          if (t < mc) acc[t] += popc4(and4(ldg4(rows[t] + v), mw));
+      }
+      if (i0 == 0) {
+        bits_lo = warp_sum(b_lo);
+        const int bits_hi = warp_sum(b_hi);
+        // output words this unit owns: those whose first bit lies in its segment's bit range
+        own_lo = (bits_lo + 31) >> 5;
+        own_hi = last_seg ? w_new : (bits_hi + 31) >> 5;
+      }
+      uint32_t surv = 0;
+#pragma unroll
+      for (int t = 0; t < kChunk; ++t) {
+        if (t < mc) {
+          const int cnt = warp_sum(acc[t]);
+          if (lane == 0 && seg == 0) {
+            cand_cnt[o.a + i0 + t] = cnt;
+            cand_p[o.a + i0 + t] = (int32_t)p;
+          }
+          if (cnt >= thr) surv |= 1u << t;
+        }
+      }
+      if (own_lo >= own_hi) {                  // this segment owns no output word: count only
+        if (seg != 0) break;
+        continue;
+      }
+      if (surv == 0) continue;
+      __syncwarp();
+      if (lane < mc && ((surv >> lane) & 1u)) {
+        const int slot = queued + __popc(surv & ((1u << lane) - 1u));
+        s_src[warp][slot] = my_src;
+        s_dst[warp][slot] = o.b + (int64_t)(i0 + lane) * w_new;
+      }
+      queued += __popc(surv);
+      __syncwarp();
+      if (queued >= kChunk) {                  // a full batch: squeeze it, keep the rest queued
+        squeeze(kChunk);
+        const int rest = queued - kChunk;
+        int64_t a_src = 0, a_dst = 0;
+        if (lane < rest) {
+          a_src = s_src[warp][kChunk + lane];
+          a_dst = s_dst[warp][kChunk + lane];
+        }
+        __syncwarp();
+        if (lane < rest) {
+          s_src[warp][lane] = a_src;
+          s_dst[warp][lane] = a_dst;
+        }
+        queued = rest;
+        __syncwarp();
+      }
     }
+    if (queued > 0) squeeze(queued);
   }
 }
 
