@@ -178,6 +178,7 @@ k_mask_counts(const int32_t* __restrict__ counts, const int32_t* __restrict__ ne
 // unit each, so that one very wide row (a very popular prefix: hundreds of thousands of words at
 // 10M playlists) is not a single warp's serial job. Multiple of 32.
 constexpr int kSegWords = 8192;
+constexpr int kUnitCands = 4;   // candidates of one parent per work unit of the AND kernel
 __host__ __device__ __forceinline__ int seg_count(int w_old) { return (w_old + kSegWords - 1) / kSegWords; }
 
 // ---- levels >= 3 --------------------------------------------------------------------------
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(256)
 k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
             const int32_t* __restrict__ counts, int64_t n, int keep_words, int squeeze_pct, int n_parts, int part,
             int part_block, int32_t* __restrict__ ncand, int32_t* __restrict__ wnew,
-            int32_t* __restrict__ n_wide) {
+            I2* __restrict__ tuple, int32_t* __restrict__ n_wide) {
   int wide = 0;
   unsigned long long cands = 0;
   for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
@@ -222,6 +223,8 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
     }
     ncand[p] = m;
     wnew[p] = w;
+    // what the scan sums: slot words, candidates, work units of the AND route
+    tuple[p] = I2{(long long)m * (long long)w, m, (m > 0 && w == w_old) ? (m + kUnitCands - 1) / kUnitCands : 0};
     cands += (unsigned long long)m;
   }
   // one atomic per warp, not per thread
@@ -235,7 +238,6 @@ k_join_size(const int32_t* __restrict__ par, const int32_t* __restrict__ roww,
   }
 }
 
-constexpr int kUnitCands = 4;   // candidates of one parent per work unit of the AND kernel
 
 struct CandSlots {
   const int32_t* ncand;
@@ -1186,7 +1188,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       ProfScope ps("k_join_size", s, 20.0 * (double)n_k, k + 1);
       k_join_size<<<grid_for(n_k, 256, 16), 256, 0, s>>>(par_k, roww_k, counts_k, n_k, keep_words, squeeze_pct,
                                                          parted ? opt.n_parts : 1, opt.part, std::max(opt.part_block, 1),
-                                                         ncand, wnew, flags + 5);
+                                                         ncand, wnew, off2, flags + 5);
       KMLS_LAUNCHED("k_join_size");
     }
     if (prof) {
@@ -1195,15 +1197,13 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_LAUNCHED("k_level_work");
     }
     {
-      cub::CountingInputIterator<int64_t> idx(0);
-      cub::TransformInputIterator<I2, CandSlots, cub::CountingInputIterator<int64_t>> it(
-          idx, CandSlots{ncand, wnew, roww_k});
+      // in place over the tuples k_join_size wrote (one coalesced 16-byte stream)
       size_t need = 0;
-      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(nullptr, need, off2, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       char* tmp = nullptr;
       KMLS_TRY(M.take(&tmp, (int64_t)need));
-      ProfScope ps("scan_slots", s, 24.0 * (double)n_k, k + 1);
-      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, it, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
+      ProfScope ps("scan_slots", s, 32.0 * (double)n_k, k + 1);
+      KMLS_CUDA(cub::DeviceScan::ExclusiveScan(tmp, need, off2, off2, I2Sum(), I2{0, 0, 0}, (int)n_k, s));
       M.ws.release(tmp);
     }
     k_i2_total<<<1, 1, 0, s>>>(CandSlots{ncand, wnew, roww_k}, n_k, off2, flags + 5, M.box);
