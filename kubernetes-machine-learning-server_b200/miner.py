@@ -749,9 +749,11 @@ def generate_rules(res: MineResult, min_confidence: float, max_rules: int = 4_00
         _lib.CALLS["kmls_rules"] = _lib.CALLS.get("kmls_rules", 0) + 1
         if rc == 0:
             break
-        if rc == -2 and "workspace too small" in msg and ws.grow(int(out.workspace_needed_bytes * 1.02) + (16 << 20)
-                                                                  if out.workspace_needed_bytes else None):
-            continue
+        if rc == -2 and "workspace too small" in msg:
+            want = int(out.workspace_needed_bytes * 1.02) + (16 << 20)
+            # the library's figure is a lower bound while it is still sizing: never ask for less than 1.25x
+            if ws.grow(max(want, int(ws.nbytes * 1.25))):
+                continue
         raise _lib.KmlsError(f"kmls_rules failed with code {rc}: {msg}")
     _lib.EXTRA_LAUNCHES += int(out.kernel_launches) - 1
     _SIZE_HINT[hint_key] = max(_SIZE_HINT.get(hint_key, 0), int(out.workspace_peak_bytes * 1.02) + (16 << 20))
