@@ -11,7 +11,8 @@ import os
 from ctypes import c_double, c_int32, c_int64, c_size_t, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libkmls_b200.so")
+# (KMLS_LIB: another build of the same library, for A/B measurements of kernel variants)
+LIB_PATH = os.environ.get("KMLS_LIB") or os.path.join(_HERE, "libkmls_b200.so")
 
 _P, _I32, _I64, _SZ, _F64 = c_void_p, c_int32, c_int64, c_size_t, c_double
 

@@ -328,7 +328,13 @@ k_expand_units(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
 // the L1-resident rows). When the unit holds all candidates of its parent and exactly one
 // survives, nothing is stored: an only child is never joined again (k_emit_rows gives it
 // width 0).
+// (KMLS_AND_MINB / KMLS_CP_MINB: minimum resident CTAs per SM asked of ptxas, for A/B builds with
+// tools/build_variant.sh; unset = ptxas' own choice, the measured best)
+#ifdef KMLS_AND_MINB
+__global__ void __launch_bounds__(256, KMLS_AND_MINB)
+#else
 __global__ void __launch_bounds__(256)
+#endif
 k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_t* __restrict__ cand_cnt,
             int32_t* __restrict__ cand_p) {
   const int lane = threadIdx.x & 31;
@@ -404,7 +410,11 @@ constexpr int kKeepWordsDefaultMine = 256;
 // compress network's move masks (Hacker's Delight 7-4) derived ONCE per mask word for all
 // survivors of the chunk, output words assembled in shared memory. (Rows of at most keep_words
 // words take k_expand_units + k_count_and.)
+#ifdef KMLS_CP_MINB
+__global__ void __launch_bounds__(256, KMLS_CP_MINB)
+#else
 __global__ void __launch_bounds__(256)
+#endif
 k_count_project(const uint32_t* __restrict__ arena_old, const int64_t* __restrict__ rowptr_old,
                 const int32_t* __restrict__ roww_old, const int32_t* __restrict__ ncand,
                 const int32_t* __restrict__ wnew, const I2* __restrict__ off2,
