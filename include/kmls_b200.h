@@ -91,6 +91,23 @@ int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_wo
                         int32_t* d_pair, void* d_scratch, size_t scratch_bytes,
                         kmls_stream_t stream);
 
+/* Hybrid of the two for a Zipf-like catalogue (what kmls_mine runs by default on a sparse
+ * input with enough rows): rows are in ascending-support order, so the LAST n_hot rows are
+ * the most frequent tracks and their n_hot x n_hot block takes a large share of all counter
+ * updates. kmls_pair_counts_csr_cold counts everything EXCEPT the pairs and diagonal entries
+ * inside that block (which it leaves zero); kmls_pair_counts_i8_block then fills the block on
+ * the tensor cores: d_bitmap = first hot row, row_words = words of the playlist range counted
+ * (a multiple of 4), row_stride = words between rows, d_pair = the block's top-left entry,
+ * ld = the whole matrix's row length. The block must be zero on entry (counts are stored, or
+ * added with atomics when the playlist dimension is split). Same kernels as
+ * k_pair_counts_csr / k_pair_gemm_i8_ts (reference: k = 2 of fpgrowth.fpg_step). */
+int kmls_pair_counts_csr_cold(const int64_t* d_offsets, const int32_t* d_items, int64_t n_playlists,
+                              const int32_t* d_row_of_item, int32_t n_rows, int32_t n_hot,
+                              int32_t* d_pair, int32_t* d_overflow, kmls_stream_t stream);
+int kmls_pair_counts_i8_block(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                              int64_t row_stride, int32_t* d_pair, int64_t ld, void* d_scratch,
+                              size_t scratch_bytes, kmls_stream_t stream);
+
 /* Frequent-pair table: all (a, b), a < b, with d_pair[a][b] >= thr, sorted by (a, b).
  * d_row_off[n_rows+1] receives the exclusive scan of per-row counts (d_row_off[n_rows] =
  * number of pairs). With capacity == 0 only d_row_off is produced (sizing pass); otherwise
@@ -364,7 +381,10 @@ typedef struct kmls_mine_options {
   int32_t part_block;     /* of part_block consecutive pairs; n_parts <= 1 = everything        */
   int32_t squeeze_pct;    /* a row wider than keep_words is squeezed (bit extract) only if that
                              leaves at most this percentage of its width; 0 = default (50)     */
-  int32_t reserved;
+  int32_t hot_rows;       /* level 2, per-playlist route: the block of the hot_rows most frequent
+                             rows is counted on the tensor cores instead (kmls_pair_counts_csr_cold
+                             + kmls_pair_counts_i8_block). 0 = choose by cost (1024 rows or none),
+                             > 0 = this many (rounded up to 128), < 0 = never                   */
   int64_t max_itemsets;   /* guard: fail (never truncate) beyond this many itemsets; 0 = 2e8   */
   void* h_tables;         /* optional PINNED host buffer: every level table is copied there on */
   size_t h_tables_bytes;  /* a side stream as soon as it is final, while mining continues      */
@@ -383,7 +403,7 @@ typedef struct kmls_mine_result {
   int32_t t1, tk, thr_k;  /* thresholds used: level 1, levels >= 2, and the one applied */
   int32_t n_rows;         /* frequent tracks = rows of the bitmap, in ascending-support order */
   int32_t max_k;          /* longest frequent itemset */
-  int32_t pair_impl_used;
+  int32_t pair_impl_used; /* 1, 2, 3 as in the options; 4 = 1 with the hot block on the tensor cores */
   int64_t n_itemsets;
   int64_t kernel_launches;
   size_t workspace_peak_bytes;

@@ -54,6 +54,8 @@ SIGNATURES = {
     "kmls_rules_count": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _I64, _I64, _P, _I64, _F64, _P, _P,
                                         _P, _P]),
     "kmls_pair_counts_csr": (ctypes.c_int, [_P, _P, _I64, _P, _I32, _P, _P, _P]),
+    "kmls_pair_counts_csr_cold": (ctypes.c_int, [_P, _P, _I64, _P, _I32, _I32, _P, _P, _P]),
+    "kmls_pair_counts_i8_block": (ctypes.c_int, [_P, _I32, _I64, _I64, _P, _I64, _P, _SZ, _P]),
     "kmls_words_to_host": (ctypes.c_int, [_P, _I32, _P, _P]),
     "kmls_rules_subsets": (ctypes.c_int, [_P, _P, _P, _I32, _I32, _P, _P, _P, _P, _P]),
     "kmls_rules_count_gather": (ctypes.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P, _I64, _F64, _P, _P, _P, _P]),
@@ -83,7 +85,7 @@ class MineOptions(ctypes.Structure):
     """struct kmls_mine_options (include/kmls_b200.h)."""
     _fields_ = [("max_len", c_int32), ("pair_impl", c_int32), ("keep_words", c_int32),
                 ("n_parts", c_int32), ("part", c_int32), ("part_block", c_int32),
-                ("squeeze_pct", c_int32), ("reserved", c_int32),
+                ("squeeze_pct", c_int32), ("hot_rows", c_int32),
                 ("max_itemsets", c_int64), ("h_tables", c_void_p), ("h_tables_bytes", c_size_t),
                 ("allreduce_i32", c_void_p), ("allreduce_ctx", c_void_p)]
 
@@ -142,7 +144,7 @@ def load() -> ctypes.CDLL:
 # and selections count as the kernels they launch from inside this library).
 KERNELS_PER_CALL = {
     "kmls_item_histogram": 1, "kmls_encode_bitmap": 1, "kmls_row_popcount": 1, "kmls_gather_rows": 1,
-    "kmls_pair_counts": 1, "kmls_pair_counts_i8": 2, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
+    "kmls_pair_counts": 1, "kmls_pair_counts_i8": 2, "kmls_pair_counts_i8_block": 2, "kmls_pair_select": 2, "kmls_supports_f64": 1, "kmls_exclusive_scan_i32": 3,
     "kmls_exclusive_scan_i32_noalloc": 3,
     "kmls_itemset_set_build": 1, "kmls_join_count": 4, "kmls_join_write": 4, "kmls_count_candidates": 1,
     "kmls_emit_count": 3, "kmls_emit_level": 1, "kmls_trie_index_build": 1, "kmls_rules_count": 1,

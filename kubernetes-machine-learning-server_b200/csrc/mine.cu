@@ -69,6 +69,8 @@ struct I2Sum {
   __host__ __device__ I2 operator()(const I2& x, const I2& y) const { return I2{x.b + y.b, x.a + y.a, x.c + y.c}; }
 };
 
+constexpr int kHotRows = 1024;      // level 2 hybrid: rows of the block counted on the tensor cores
+
 // ---- level 1 helpers --------------------------------------------------------------------
 struct OccAtLeast {
   const int32_t* occ;
@@ -99,18 +101,21 @@ k_number_rows(const int32_t* __restrict__ cand, int32_t n_rows, int32_t* __restr
 }
 
 // flags[0] += 1 for every row whose exact support differs from the occurrence count it was
-// ordered by; flags[1] (64-bit, at flags + 2) += the supports (mean kept tracks per playlist)
+// ordered by; flags[1] (64-bit, at flags + 2) += the supports (mean kept tracks per playlist);
+// 64-bit at flags + 8 += the supports of the rows from hot0 on (the most frequent tracks)
 __global__ void __launch_bounds__(256)
 k_check_counts(const int32_t* __restrict__ counts, const int32_t* __restrict__ keys, int32_t n_rows,
-               int32_t* __restrict__ flags) {
-  long long sum = 0;
+               int32_t hot0, int32_t* __restrict__ flags) {
+  long long sum = 0, hot = 0;
   int bad = 0;
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < n_rows; r += gridDim.x * blockDim.x) {
     bad += counts[r] != keys[r];
     sum += counts[r];
+    if (r >= hot0) hot += counts[r];
   }
   if (bad) atomicAdd(flags, bad);
   if (sum) atomicAdd((unsigned long long*)(flags + 2), (unsigned long long)sum);
+  if (hot) atomicAdd((unsigned long long*)(flags + 8), (unsigned long long)hot);
 }
 
 // mlxtend's root single-path shortcut: the root FP-tree is one path iff
@@ -927,13 +932,13 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     ProfScope ps("k_row_popcount", s, 4.0 * (double)n_rows * (double)row_words, 1);
     KMLS_TRY(kmls_row_popcount(bitmap, n_rows, row_words, counts1, s));
   }
-  k_check_counts<<<grid_for(n_rows, 256, 4), 256, 0, s>>>(counts1, keys, n_rows, flags);
+  k_check_counts<<<grid_for(n_rows, 256, 4), 256, 0, s>>>(counts1, keys, n_rows, n_rows - kHotRows, flags);
   KMLS_LAUNCHED("k_check_counts");
-  k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), nullptr, flags, nullptr, M.box);
+  k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), (const int64_t*)(flags + 8), flags, nullptr, M.box);
   KMLS_LAUNCHED("k_post");
   M.launches += 6;
   KMLS_TRY(M.sync());
-  int64_t sum_counts = M.box[0];
+  int64_t sum_counts = M.box[0], sum_hot = M.box[1];
   if (M.box[2] != 0) {
     // some playlist repeats a track: exact supports are below the occurrence
     // counts, so drop the rows that fell under T1 and restore ascending-support order
@@ -952,13 +957,14 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     k_gather_i32<<<grid_for(n_keep, 256, 8), 256, 0, s>>>(cand, src, n_keep, cand2);
     KMLS_LAUNCHED("k_gather_i32");
     KMLS_CUDA(cudaMemcpyAsync(counts1, keys2, sizeof(int32_t) * (size_t)n_keep, cudaMemcpyDeviceToDevice, s));
-    KMLS_CUDA(cudaMemsetAsync(flags, 0, 8 * sizeof(int32_t), s));
-    k_check_counts<<<grid_for(n_keep, 256, 4), 256, 0, s>>>(counts1, keys2, n_keep, flags);
+    KMLS_CUDA(cudaMemsetAsync(flags, 0, 16 * sizeof(int32_t), s));
+    k_check_counts<<<grid_for(n_keep, 256, 4), 256, 0, s>>>(counts1, keys2, n_keep, n_keep - kHotRows, flags);
     KMLS_LAUNCHED("k_check_counts");
-    k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), nullptr, nullptr, nullptr, M.box);
+    k_post<<<1, 1, 0, s>>>((const int64_t*)(flags + 2), (const int64_t*)(flags + 8), nullptr, nullptr, M.box);
     KMLS_LAUNCHED("k_post");
     KMLS_TRY(M.sync());
     sum_counts = M.box[0];
+    sum_hot = M.box[1];
     M.launches += 5;
     M.ws.release(bitmap);
     M.ws.release(cand);
@@ -1009,6 +1015,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   KMLS_TRY(M.take(&pair, (int64_t)n_rows * n_rows, false));
   R->pair_off = off_of(pair);
   int impl = opt.pair_impl;
+  bool hybrid = false;
   const bool big = n_rows >= 256 && row_words >= 512;
   if (impl == 0) {
     // tensor cores once there are enough tiles and playlists to feed them, unless the
@@ -1026,19 +1033,50 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   if (impl == 1) {
     int rec = -1;
     // a rank of a class-partitioned job counts the pairs of ITS share of the playlists only and
-    // the ranks' matrices are summed (the job's host side supplies the allreduce)
+    // the ranks' matrices are summed (the job's host side supplies the allreduce); the shares
+    // start at multiples of 128 playlists (one K block of the tensor-core kernel)
     const bool shared_pairs = opt.allreduce_i32 != nullptr && opt.n_parts > 1;
-    const int64_t pl_lo = shared_pairs ? n_playlists * opt.part / opt.n_parts : 0;
-    const int64_t pl_hi = shared_pairs ? n_playlists * (opt.part + 1) / opt.n_parts : n_playlists;
+    const int64_t pl_lo = shared_pairs ? (n_playlists * opt.part / opt.n_parts) & ~(int64_t)127 : 0;
+    const int64_t pl_hi = shared_pairs && opt.part + 1 < opt.n_parts
+                              ? (n_playlists * (opt.part + 1) / opt.n_parts) & ~(int64_t)127 : n_playlists;
+    // Hybrid: the block of the kHotRows most frequent rows on the tensor cores, the rest per
+    // playlist. Under a Zipf law that block holds about (hot rows' share of all occurrences)^2
+    // of the counter updates; it pays when those updates (~1.5e11/s) cost more than the block's
+    // 20 tiles x 128 x 256 x playlists int8 multiply-adds (~2.2e15 ops/s, x 1.5 for the tail wave).
+    int n_hot = 0;
+    if ((row_words & 3) != 0 || pl_hi <= pl_lo) n_hot = 0;
+    else if (opt.hot_rows > 0) n_hot = std::min<int>((opt.hot_rows + 127) / 128 * 128, n_rows);
+    else if (opt.hot_rows == 0 && n_rows >= 2 * kHotRows && pl_hi - pl_lo >= 65536) {
+      const double m_mean = (double)sum_counts / (double)n_playlists;
+      const double share = ((double)sum_hot / (double)sum_counts) * ((double)sum_hot / (double)sum_counts);
+      const double t_saved = share * 0.65 * m_mean * m_mean * (double)(pl_hi - pl_lo) / 1.5e11;
+      const double t_block = 1.5 * 20.0 * 128.0 * 256.0 * 2.0 * (double)(pl_hi - pl_lo) / 2.2e15;
+      if (t_saved > 1.5 * t_block) n_hot = kHotRows;
+    }
     {
       ProfScope ps("k_pair_counts_csr", s, 0.0, 2);
       rec = ps.idx;
-      KMLS_TRY(kmls_pair_counts_csr(d_offsets + pl_lo, d_items, pl_hi - pl_lo, row_of_item, n_rows, pair, flags + 4, s));
+      KMLS_TRY(kmls_pair_counts_csr_cold(d_offsets + pl_lo, d_items, pl_hi - pl_lo, row_of_item, n_rows, n_hot, pair,
+                                         flags + 4, s));
     }
     if (rec >= 0) {   // work = counter updates made = sum of the upper triangle, 4 bytes each
       KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
       k_sum_upper<<<grid_for((int64_t)n_rows * n_rows, 256, 8), 256, 0, s>>>(pair, n_rows, (unsigned long long*)(flags + 6));
       KMLS_LAUNCHED("k_sum_upper");
+    }
+    if (n_hot > 0 && pl_hi > pl_lo) {
+      const int64_t w_lo = pl_lo >> 5, w_hi = pl_hi == n_playlists ? row_words : pl_hi >> 5;
+      const size_t gbytes = kmls_pair_gemm_scratch_bytes(n_hot, w_hi - w_lo);
+      char* gscratch = nullptr;
+      KMLS_TRY(M.take(&gscratch, (int64_t)gbytes));
+      const int64_t h0 = n_rows - n_hot;
+      {
+        ProfScope ps("k_pair_gemm_i8", s, (double)n_hot * (n_hot + 1.0) * (double)(pl_hi - pl_lo), 2);
+        KMLS_TRY(kmls_pair_counts_i8_block(bitmap + h0 * row_words + w_lo, n_hot, w_hi - w_lo, row_words,
+                                           pair + h0 * n_rows + h0, n_rows, gscratch, gbytes, s));
+      }
+      M.launches += 2;
+      M.ws.release(gscratch);
     }
     if (shared_pairs) {
       ProfScope ps("allreduce_pair_counts", s, 4.0 * (double)n_rows * (double)n_rows, 2);
@@ -1052,6 +1090,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.sync());
     if (rec >= 0) profiler().records[rec].work = 4.0 * (double)M.box[0];
     if (M.box[2] != 0) impl = big ? 3 : 2;   // a playlist with more than 1024 kept tracks
+    else if (n_hot > 0) hybrid = true;
   }
   if (impl == 2) {
     ProfScope ps("k_pair_counts", s, 4.0 * (double)n_rows * (double)row_words, 2);
@@ -1070,7 +1109,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
   } else if (impl != 1) {
     return fail(kArgError, "kmls_mine: unknown pair_impl %d", impl);
   }
-  R->pair_impl_used = impl;
+  R->pair_impl_used = hybrid ? 4 : impl;
   M.ws.release(row_of_item);
   int32_t thr = tk;
   if (t1 < tk) {

@@ -98,7 +98,7 @@ constexpr uint32_t kIdescI8 = (2u << 4) | (0u << 7) | (0u << 10) | ((uint32_t)(k
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_bits_kblock_major(const uint32_t* __restrict__ bitmap, int32_t n_rows, int32_t rows_pad,
-                    int64_t row_words, uint4* __restrict__ out) {
+                    int64_t row_words, int64_t row_stride, uint4* __restrict__ out) {
   // tile: 32 rows x 32 k-blocks through shared memory so that both sides are coalesced
   __shared__ uint4 tile[32][33];
   const int64_t kb0 = (int64_t)blockIdx.x * 32;
@@ -109,7 +109,7 @@ k_bits_kblock_major(const uint32_t* __restrict__ bitmap, int32_t n_rows, int32_t
     const int r = r0 + rr;
     const int64_t kb = kb0 + tx;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (r < n_rows && kb < n_kb) v = ldg4(reinterpret_cast<const uint4*>(bitmap + (int64_t)r * row_words) + kb);
+    if (r < n_rows && kb < n_kb) v = ldg4(reinterpret_cast<const uint4*>(bitmap + (int64_t)r * row_stride) + kb);
     tile[rr][tx] = v;
   }
   __syncthreads();
@@ -125,7 +125,7 @@ k_bits_kblock_major(const uint32_t* __restrict__ bitmap, int32_t n_rows, int32_t
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kGThreads, 1)
 k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_pad, int64_t n_kb_total,
-               int64_t kb_per_split, int32_t* __restrict__ C) {
+               int64_t kb_per_split, int32_t* __restrict__ C, int64_t ld) {
   const int tj = blockIdx.x, ti = blockIdx.y;
   if (tj * kGN + (kGN - 1) < ti * kGM) return;  // tile entirely below the diagonal
   // blockIdx.z selects a slice of the playlist dimension; with more than one slice the
@@ -272,7 +272,7 @@ k_pair_gemm_i8(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_p
             : "r"(taddr) : "memory");
         asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
         if (row < n_rows) {
-          int32_t* crow = C + (int64_t)row * n_rows;
+          int32_t* crow = C + (int64_t)row * ld;
           const int col0 = tj * kGN + c0;
 #pragma unroll
           for (int t = 0; t < 32; ++t)
@@ -322,7 +322,7 @@ __device__ __forceinline__ void tc_mma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, u
 
 __global__ void __launch_bounds__(kTThreads, 1)
 k_pair_gemm_i8_ts(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t rows_pad, int64_t n_kb_total,
-                  int64_t kb_per_split, int32_t* __restrict__ C) {
+                  int64_t kb_per_split, int32_t* __restrict__ C, int64_t ld) {
   const int tj = blockIdx.x, ti = blockIdx.y;
   if (tj * kGN + (kGN - 1) < ti * kGM) return;
   const int64_t kb0 = (int64_t)blockIdx.z * kb_per_split;
@@ -447,7 +447,7 @@ k_pair_gemm_i8_ts(const uint4* __restrict__ bits_km, int32_t n_rows, int32_t row
           : "r"(taddr) : "memory");
       asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
       if (row < n_rows) {
-        int32_t* crow = C + (int64_t)row * n_rows;
+        int32_t* crow = C + (int64_t)row * ld;
         const int col0 = tj * kGN + c0;
 #pragma unroll
         for (int t = 0; t < 32; ++t)
@@ -518,25 +518,21 @@ extern "C" size_t kmls_pair_gemm_scratch_bytes(int32_t n_rows, int64_t row_words
   return (size_t)(row_words / 4) * (size_t)rows_pad * 16;
 }
 
-extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
-                                   int32_t* d_pair, void* d_scratch, size_t scratch_bytes,
-                                   kmls_stream_t stream) {
-  KMLS_REQUIRE(n_rows >= 0 && row_words >= 0 && (row_words & 3) == 0,
-               "kmls_pair_counts_i8: row_words must be a multiple of 4");
-  if (n_rows == 0 || row_words == 0) return 0;
-  KMLS_REQUIRE(d_bitmap && d_pair && d_scratch, "kmls_pair_counts_i8: null pointer");
-  KMLS_REQUIRE(((uintptr_t)d_scratch & 15) == 0 && ((uintptr_t)d_bitmap & 15) == 0,
-               "kmls_pair_counts_i8: buffers must be 16-byte aligned");
+// Shared host side of the two entry points. `block`: C is a sub-block (leading dimension ld)
+// of a larger, already zeroed matrix - no memset here, and the playlist dimension is split as
+// finely as the SM count asks for (a block has few tiles).
+static int pair_gemm_run(const char* who, const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                         int64_t row_stride, int32_t* d_pair, int64_t ld, bool block, void* d_scratch,
+                         size_t scratch_bytes, cudaStream_t s) {
   const size_t need = kmls_pair_gemm_scratch_bytes(n_rows, row_words);
   if (scratch_bytes < need)
-    return fail(kCapacityError, "kmls_pair_counts_i8: scratch too small (%zu > %zu bytes)", need, scratch_bytes);
-  cudaStream_t s = (cudaStream_t)stream;
+    return fail(kCapacityError, "%s: scratch too small (%zu > %zu bytes)", who, need, scratch_bytes);
   const int32_t rows_pad = (n_rows + kGN - 1) / kGN * kGN;
   const int64_t n_kb = row_words / 4;
   {
     dim3 grid((unsigned)((n_kb + 31) / 32), (unsigned)(rows_pad / 32));
     KMLS_REQUIRE(grid.y <= 65535, "kmls_pair_counts_i8: too many rows");
-    k_bits_kblock_major<<<grid, 256, 0, s>>>(d_bitmap, n_rows, rows_pad, row_words, (uint4*)d_scratch);
+    k_bits_kblock_major<<<grid, 256, 0, s>>>(d_bitmap, n_rows, rows_pad, row_words, row_stride, (uint4*)d_scratch);
     KMLS_LAUNCHED("k_bits_kblock_major");
   }
   KMLS_CUDA(cudaFuncSetAttribute(k_pair_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, kGSmemBytes));
@@ -548,14 +544,25 @@ extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int
     for (int j = 0; j < tx; ++j) tiles += (j * kGN + (kGN - 1) >= i * kGM);
   const int sms = num_sms();
   int ksplit = 1;
-  for (int ks = 1; ks <= 16; ks *= 2) {
-    if (n_kb / ks < 128 && ks > 1) break;
-    ksplit = ks;
-    const int64_t units = tiles * ks, waves = (units + sms - 1) / sms;
-    if ((double)units / (double)(waves * sms) >= 0.93) break;
+  if (!block) {
+    for (int ks = 1; ks <= 16; ks *= 2) {
+      if (n_kb / ks < 128 && ks > 1) break;
+      ksplit = ks;
+      const int64_t units = tiles * ks, waves = (units + sms - 1) / sms;
+      if ((double)units / (double)(waves * sms) >= 0.93) break;
+    }
+  } else {
+    // shortest makespan = waves / ks, the smallest such ks
+    double best = 1e30;
+    for (int ks = 1; ks <= 64; ++ks) {
+      if (n_kb / ks < 64 && ks > 1) break;
+      const int64_t units = tiles * ks, waves = (units + sms - 1) / sms;
+      const double span = (double)waves / (double)ks;
+      if (span < best * 0.98) best = span, ksplit = ks;
+    }
   }
   const int64_t kb_per_split = (n_kb + ksplit - 1) / ksplit;
-  if (ksplit > 1) KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
+  if (ksplit > 1 && !block) KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
   dim3 grid((unsigned)tx, (unsigned)ty, (unsigned)ksplit);
   // default: the variant with the A operand in tensor memory; KMLS_PAIR_GEMM=ss selects the
   // one that stages both operands in shared memory
@@ -563,12 +570,39 @@ extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int
   if (!(variant && variant[0] == 's')) {
     KMLS_CUDA(cudaFuncSetAttribute(k_pair_gemm_i8_ts, cudaFuncAttributeMaxDynamicSharedMemorySize, kTSmemBytes));
     k_pair_gemm_i8_ts<<<grid, kTThreads, kTSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb,
-                                                           kb_per_split, d_pair);
+                                                           kb_per_split, d_pair, ld);
     KMLS_LAUNCHED("k_pair_gemm_i8_ts");
     return 0;
   }
   k_pair_gemm_i8<<<grid, kGThreads, kGSmemBytes, s>>>((const uint4*)d_scratch, n_rows, rows_pad, n_kb,
-                                                      kb_per_split, d_pair);
+                                                      kb_per_split, d_pair, ld);
   KMLS_LAUNCHED("k_pair_gemm_i8");
   return 0;
+}
+
+extern "C" int kmls_pair_counts_i8(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                                   int32_t* d_pair, void* d_scratch, size_t scratch_bytes,
+                                   kmls_stream_t stream) {
+  KMLS_REQUIRE(n_rows >= 0 && row_words >= 0 && (row_words & 3) == 0,
+               "kmls_pair_counts_i8: row_words must be a multiple of 4");
+  if (n_rows == 0 || row_words == 0) return 0;
+  KMLS_REQUIRE(d_bitmap && d_pair && d_scratch, "kmls_pair_counts_i8: null pointer");
+  KMLS_REQUIRE(((uintptr_t)d_scratch & 15) == 0 && ((uintptr_t)d_bitmap & 15) == 0,
+               "kmls_pair_counts_i8: buffers must be 16-byte aligned");
+  return pair_gemm_run("kmls_pair_counts_i8", d_bitmap, n_rows, row_words, row_words, d_pair, n_rows, false,
+                       d_scratch, scratch_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int kmls_pair_counts_i8_block(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
+                                         int64_t row_stride, int32_t* d_pair, int64_t ld, void* d_scratch,
+                                         size_t scratch_bytes, kmls_stream_t stream) {
+  KMLS_REQUIRE(n_rows >= 0 && row_words >= 0 && (row_words & 3) == 0 && (row_stride & 3) == 0 &&
+                   row_stride >= row_words && ld >= n_rows,
+               "kmls_pair_counts_i8_block: row_words and row_stride must be multiples of 4, ld >= n_rows");
+  if (n_rows == 0 || row_words == 0) return 0;
+  KMLS_REQUIRE(d_bitmap && d_pair && d_scratch, "kmls_pair_counts_i8_block: null pointer");
+  KMLS_REQUIRE(((uintptr_t)d_scratch & 15) == 0 && ((uintptr_t)d_bitmap & 15) == 0,
+               "kmls_pair_counts_i8_block: buffers must be 16-byte aligned");
+  return pair_gemm_run("kmls_pair_counts_i8_block", d_bitmap, n_rows, row_words, row_stride, d_pair, ld, true,
+                       d_scratch, scratch_bytes, (cudaStream_t)stream);
 }

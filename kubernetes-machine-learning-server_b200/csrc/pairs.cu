@@ -188,11 +188,16 @@ constexpr int kCsrMaxRows = 16384;   // rows the per-warp bit set covers
 
 constexpr int kCsrHot = 64;          // the kCsrHot most frequent rows' pairs are counted in shared memory
 
-template <bool HOT>
+// MODE 0: every pair is one RED.ADD into the matrix. MODE 1: the pairs among the kCsrHot most
+// frequent rows are counted in shared memory per CTA and flushed once. MODE 2: the pairs (and
+// diagonal entries) among the last n_hot rows are LEFT OUT - the caller counts that block on
+// the tensor cores (kmls_pair_counts_i8_block); a playlist's rows are kept as cold rows from
+// the front and hot rows from the back of its list, so the left-out pairs cost no iterations.
+template <int MODE>
 __global__ void __launch_bounds__(256)
 k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict__ items, int64_t n,
-                  const int32_t* __restrict__ row_of_item, int32_t n_rows, int32_t* __restrict__ pair,
-                  int32_t* __restrict__ overflow) {
+                  const int32_t* __restrict__ row_of_item, int32_t n_rows, int32_t n_hot,
+                  int32_t* __restrict__ pair, int32_t* __restrict__ overflow) {
   extern __shared__ uint32_t csr_smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int seen_words = (n_rows + 31) >> 5;
@@ -200,19 +205,19 @@ k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict
   int32_t* rows = reinterpret_cast<int32_t*>(csr_smem + (size_t)8 * seen_words) + (size_t)warp * kCsrMaxLen;
   for (int i = lane; i < seen_words; i += 32) seen[i] = 0u;
   __syncwarp();
-  // Rows are in ascending-support order, so the last kCsrHot rows are the most frequent
-  // tracks; under a Zipf law their pairs take a large share of all updates and would
-  // serialise on a few L2 atomic units. They are counted per CTA here and flushed once.
-  __shared__ int32_t hot[HOT ? kCsrHot * kCsrHot : 1];
-  const int hot0 = n_rows - kCsrHot;        // first hot row (HOT only when n_rows >= kCsrHot)
-  if (HOT) {
+  // Rows are in ascending-support order, so the last rows are the most frequent tracks; under
+  // a Zipf law their pairs take a large share of all updates and would serialise on a few L2
+  // atomic units.
+  __shared__ int32_t hot[MODE == 1 ? kCsrHot * kCsrHot : 1];
+  const int hot0 = n_rows - (MODE == 1 ? kCsrHot : MODE == 2 ? n_hot : 0);        // first hot row
+  if (MODE == 1) {
     for (int i = threadIdx.x; i < kCsrHot * kCsrHot; i += blockDim.x) hot[i] = 0;
     __syncthreads();
   }
   const uint32_t below = (1u << lane) - 1u;
   for (int64_t p = (int64_t)blockIdx.x * 8 + warp; p < n; p += (int64_t)gridDim.x * 8) {
     const int64_t b = __ldg(offsets + p), e = __ldg(offsets + p + 1);
-    int m = 0;
+    int m = 0, mh = 0;          // rows kept from the front, (MODE 2) hot rows kept from the back
     bool over = false;
     for (int64_t q = b; q < e; q += 32) {
       int32_t r = -1;
@@ -222,19 +227,28 @@ k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict
         const uint32_t bit = 1u << (r & 31);
         uniq = !(atomicOr(seen + (r >> 5), bit) & bit);     // first occurrence in this playlist
       }
-      const uint32_t mask = __ballot_sync(0xffffffffu, uniq);
-      const int pos = m + __popc(mask & below);
-      if (uniq && pos < kCsrMaxLen) rows[pos] = r;
-      m += __popc(mask);
+      if (MODE == 2) {
+        const bool is_hot = uniq && r >= hot0;
+        const uint32_t mask_c = __ballot_sync(0xffffffffu, uniq && !is_hot);
+        const uint32_t mask_h = __ballot_sync(0xffffffffu, is_hot);
+        const int m1 = m + __popc(mask_c), mh1 = mh + __popc(mask_h);
+        if (m1 + mh1 <= kCsrMaxLen) {
+          if (uniq && !is_hot) rows[m + __popc(mask_c & below)] = r;
+          if (is_hot) rows[kCsrMaxLen - 1 - (mh + __popc(mask_h & below))] = r;
+        }
+        m = m1;
+        mh = mh1;
+      } else {
+        const uint32_t mask = __ballot_sync(0xffffffffu, uniq);
+        const int pos = m + __popc(mask & below);
+        if (uniq && pos < kCsrMaxLen) rows[pos] = r;
+        m += __popc(mask);
+      }
     }
     __syncwarp();
-    if (m > kCsrMaxLen) {
-      over = true;
-      m = kCsrMaxLen;
-    }
-    for (int t = lane; t < m; t += 32) seen[rows[t] >> 5] = 0u;     // leave the bit set clean
+    if (m + mh > kCsrMaxLen) over = true;
     if (over) {
-      // (the dropped rows' bits must be cleared as well: rebuild from the items)
+      // the dropped rows' bits must be cleared as well: rebuild from the items
       for (int64_t q = b + lane; q < e; q += 32) {
         const int32_t r = __ldg(row_of_item + __ldg(items + q));
         if (r >= 0) seen[r >> 5] = 0u;
@@ -243,26 +257,31 @@ k_pair_counts_csr(const int64_t* __restrict__ offsets, const int32_t* __restrict
       __syncwarp();
       continue;
     }
+    const int mt = m + mh;                  // list: cold rows [0, m), then hot rows from the array's end
+    const int shift = kCsrMaxLen - mt;      // entry j >= m lives at rows[j + shift]
+    for (int t = lane; t < mt; t += 32) seen[rows[t < m ? t : t + shift] >> 5] = 0u;     // leave the bit set clean
     __syncwarp();
-    // diagonal, then all pairs i < j of the list: lane t takes pairs t, t+32, ... of the
-    // row-major enumeration (i, c) with j = i + 1 + c
+    // diagonal, then all pairs i < j of the list with i < m: lane t takes pairs t, t+32, ...
+    // of the row-major enumeration (i, c) with j = i + 1 + c
     for (int t = lane; t < m; t += 32) {
       const int64_t r = rows[t];
       atomicAdd(pair + r * n_rows + r, 1);
     }
+    const int mi = min(m, mt - 1);          // first members that open pairs
     int i = 0, c = lane;
-    while (i < m - 1 && c >= m - 1 - i) { c -= m - 1 - i; ++i; }
-    while (i < m - 1) {
-      const int32_t ra = rows[i], rb = rows[i + 1 + c];
+    while (i < mi && c >= mt - 1 - i) { c -= mt - 1 - i; ++i; }
+    while (i < mi) {
+      const int j = i + 1 + c;
+      const int32_t ra = rows[i], rb = rows[j < m ? j : j + shift];
       const int64_t lo = min(ra, rb), hi = max(ra, rb);
-      if (HOT && lo >= hot0) atomicAdd(hot + (lo - hot0) * kCsrHot + (hi - hot0), 1);
+      if (MODE == 1 && lo >= hot0) atomicAdd(hot + (lo - hot0) * kCsrHot + (hi - hot0), 1);
       else atomicAdd(pair + lo * n_rows + hi, 1);
       c += 32;
-      while (i < m - 1 && c >= m - 1 - i) { c -= m - 1 - i; ++i; }
+      while (i < mi && c >= mt - 1 - i) { c -= mt - 1 - i; ++i; }
     }
     __syncwarp();
   }
-  if (HOT) {
+  if (MODE == 1) {
     __syncthreads();
     for (int i = threadIdx.x; i < kCsrHot * kCsrHot; i += blockDim.x) {
       const int v = hot[i];
@@ -300,28 +319,44 @@ extern "C" int kmls_pair_counts(const uint32_t* d_bitmap, int32_t n_rows, int64_
   return 0;
 }
 
-extern "C" int kmls_pair_counts_csr(const int64_t* d_offsets, const int32_t* d_items,
-                                    int64_t n_playlists, const int32_t* d_row_of_item,
-                                    int32_t n_rows, int32_t* d_pair, int32_t* d_overflow,
-                                    kmls_stream_t stream) {
+static int pair_counts_csr_run(const char* who, const int64_t* d_offsets, const int32_t* d_items,
+                               int64_t n_playlists, const int32_t* d_row_of_item, int32_t n_rows, int32_t n_hot,
+                               int32_t* d_pair, int32_t* d_overflow, cudaStream_t s) {
   KMLS_REQUIRE(n_playlists >= 0 && n_rows >= 0, "kmls_pair_counts_csr: negative size");
   KMLS_REQUIRE(n_rows <= kCsrMaxRows, "kmls_pair_counts_csr: more than 16384 rows (use kmls_pair_counts_i8)");
+  KMLS_REQUIRE(n_hot >= 0 && n_hot <= n_rows, "kmls_pair_counts_csr_cold: n_hot out of range");
   if (n_rows == 0) return 0;
   KMLS_REQUIRE(d_pair && d_overflow, "kmls_pair_counts_csr: null pointer");
-  cudaStream_t s = (cudaStream_t)stream;
   KMLS_CUDA(cudaMemsetAsync(d_pair, 0, sizeof(int32_t) * (size_t)n_rows * n_rows, s));
   KMLS_CUDA(cudaMemsetAsync(d_overflow, 0, sizeof(int32_t), s));
   if (n_playlists == 0) return 0;
   KMLS_REQUIRE(d_offsets && d_items && d_row_of_item, "kmls_pair_counts_csr: null pointer");
+  (void)who;
   const size_t smem = sizeof(uint32_t) * 8 * (size_t)((n_rows + 31) / 32) + sizeof(int32_t) * 8 * kCsrMaxLen;
   static const bool no_hot = [] { const char* e = getenv("KMLS_PAIR_CSR_HOT"); return e && e[0] == '0'; }();
-  const bool use_hot = !no_hot && n_rows >= kCsrHot;
-  auto kern = use_hot ? k_pair_counts_csr<true> : k_pair_counts_csr<false>;
+  const int mode = n_hot > 0 ? 2 : (!no_hot && n_rows >= kCsrHot) ? 1 : 0;
+  auto kern = mode == 2 ? k_pair_counts_csr<2> : mode == 1 ? k_pair_counts_csr<1> : k_pair_counts_csr<0>;
   KMLS_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-  int grid = (int)std::min<int64_t>((n_playlists + 7) / 8, (int64_t)num_sms() * (use_hot ? 4 : 16));
-  kern<<<grid, 256, smem, s>>>(d_offsets, d_items, n_playlists, d_row_of_item, n_rows, d_pair, d_overflow);
+  int grid = (int)std::min<int64_t>((n_playlists + 7) / 8, (int64_t)num_sms() * (mode == 1 ? 4 : 16));
+  kern<<<grid, 256, smem, s>>>(d_offsets, d_items, n_playlists, d_row_of_item, n_rows, n_hot, d_pair, d_overflow);
   KMLS_LAUNCHED("k_pair_counts_csr");
   return 0;
+}
+
+extern "C" int kmls_pair_counts_csr(const int64_t* d_offsets, const int32_t* d_items,
+                                    int64_t n_playlists, const int32_t* d_row_of_item,
+                                    int32_t n_rows, int32_t* d_pair, int32_t* d_overflow,
+                                    kmls_stream_t stream) {
+  return pair_counts_csr_run("kmls_pair_counts_csr", d_offsets, d_items, n_playlists, d_row_of_item, n_rows, 0,
+                             d_pair, d_overflow, (cudaStream_t)stream);
+}
+
+extern "C" int kmls_pair_counts_csr_cold(const int64_t* d_offsets, const int32_t* d_items,
+                                         int64_t n_playlists, const int32_t* d_row_of_item,
+                                         int32_t n_rows, int32_t n_hot, int32_t* d_pair,
+                                         int32_t* d_overflow, kmls_stream_t stream) {
+  return pair_counts_csr_run("kmls_pair_counts_csr_cold", d_offsets, d_items, n_playlists, d_row_of_item, n_rows,
+                             n_hot, d_pair, d_overflow, (cudaStream_t)stream);
 }
 
 extern "C" int kmls_pair_select(const int32_t* d_pair, int32_t n_rows, int32_t thr,

@@ -297,6 +297,7 @@ class Workspace:
 
 
 _PAIR_IMPL = {"auto": 0, "csr": 1, "popc": 2, "i8": 3}
+_PAIR_IMPL_USED = {1: "csr", 2: "popc", 3: "i8", 4: "csr+i8"}   # 4: csr with the hot rows' block on the tensor cores
 _SIZE_HINT = {}   # (device index, "mine" | "rules") -> bytes the last call needed: first guess of the next
 
 
@@ -305,7 +306,8 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
                 max_itemsets: int = 200_000_000, keep_pair_counts: bool = False, pair_impl: str = "auto",
                 keep_words: Optional[int] = None, workspace: Optional[Workspace] = None,
                 part: Tuple[int, int] = (0, 1), part_block: int = 64,
-                host_tables: Optional[torch.Tensor] = None, allreduce=None, retry_sync=None) -> MineResult:
+                host_tables: Optional[torch.Tensor] = None, allreduce=None, retry_sync=None,
+                hot_rows: Optional[int] = None) -> MineResult:
     """All levels through ONE call into the library (``kmls_mine``): the level loop, its
     sizing and its buffers live in C++; this function only marshals. ``workspace``: device
     memory for the call (a fresh one by default; the returned tables are views of it, so a
@@ -313,7 +315,9 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
     is grown and the call repeated - the library never truncates. ``part = (i, n)``: mine only
     the subtrees of the i-th of n interleaved blocks of ``part_block`` frequent pairs (levels 1
     and 2 are always complete): the class partition of a multi-GPU job. ``host_tables``: a
-    pinned uint8 tensor the level tables are also streamed into while mining continues."""
+    pinned uint8 tensor the level tables are also streamed into while mining continues.
+    ``hot_rows``: with the per-playlist pair counts, the block of this many most frequent tracks
+    is counted on the tensor cores instead (None/0 = the library decides, -1 = never)."""
     if min_support <= 0.0:
         thresholds(min_support, 1)  # raises the reference's ValueError
     if not (offsets.is_cuda and items.is_cuda):
@@ -332,6 +336,7 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
     opt.keep_words = int(keep_words or 0)
     import os as _os
     opt.squeeze_pct = int(_os.environ.get("KMLS_SQUEEZE_PCT", 0))               # tuning switch (0 = library default)
+    opt.hot_rows = int(hot_rows if hot_rows is not None else _os.environ.get("KMLS_PAIR_HOT_ROWS", 0))
     opt.n_parts, opt.part, opt.part_block = int(part[1]), int(part[0]), int(part_block)
     opt.max_itemsets = int(max_itemsets)
     if host_tables is not None:
@@ -371,7 +376,7 @@ def mine_native(offsets: torch.Tensor, items: torch.Tensor, n_items: int, min_su
     _SIZE_HINT[hint_key] = max(_SIZE_HINT.get(hint_key, 0), int(out.workspace_peak_bytes * 1.1) + (1 << 20))
     stats = {"levels": [], "t1": t1, "tk": tk, "thr_k": int(out.thr_k), "n_playlists": n_total,
              "nnz_local": int(items.numel()), "workspace_peak_bytes": int(out.workspace_peak_bytes),
-             "pair_impl": {v: k for k, v in _PAIR_IMPL.items()}.get(int(out.pair_impl_used)),
+             "pair_impl": _PAIR_IMPL_USED.get(int(out.pair_impl_used)),
              "h_bytes": int(out.h_bytes)}
     e32 = torch.empty(0, dtype=torch.int32, device=device)
     n_rows, max_k = int(out.n_rows), int(out.max_k)

@@ -249,3 +249,65 @@ def test_profile_report_names_the_kernels():
     assert all(ms >= 0 for _, _, ms, _ in rec)
     assert any(nm in ("k_count_and", "k_count_project") and work > 0 for nm, _, _, work in rec)
     assert miner.mine_native(d_off, d_items, 700, 0.012).as_dict() == res.as_dict()   # profiling off again: same result
+
+
+# ---- level 2 hybrid: hot rows' block on the tensor cores, the rest per playlist ------------
+
+def _row_order(off, items, n_items, thr):
+    """row_of_item for the tracks with at least thr occurrences, rows in ascending-count order."""
+    occ = np.bincount(items, minlength=n_items)
+    keep = np.flatnonzero(occ >= thr)
+    keep = keep[np.argsort(occ[keep], kind="stable")]
+    row_of = np.full(n_items, -1, np.int32)
+    row_of[keep] = np.arange(len(keep), dtype=np.int32)
+    return row_of, len(keep)
+
+
+@pytest.mark.parametrize("n_hot", [128, 200, 512])
+@pytest.mark.parametrize("stride_extra", [0, 8])
+def test_pair_counts_cold_plus_block_equal_csr(n_hot, stride_extra):
+    # kmls_pair_counts_csr_cold leaves the hot block zero; kmls_pair_counts_i8_block fills it
+    n, t = 40_000, 1500
+    off, items = synth.zipf_playlists(n, t, mean_draws=25, alpha=1.0, seed=17)
+    row_of, n_rows = _row_order(off, items, t, 40)
+    assert n_rows > 600
+    d_off, d_items = to_dev(off, items)
+    d_row_of = torch.from_numpy(row_of).to(dev())
+    s = torch.cuda.current_stream().cuda_stream
+    want = torch.empty((n_rows, n_rows), dtype=torch.int32, device=dev())
+    ovf = torch.zeros(1, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts_csr", d_off, d_items, n, d_row_of, n_rows, want, ovf, s)
+    assert int(ovf.item()) == 0
+    got = torch.full((n_rows, n_rows), -1, dtype=torch.int32, device=dev())
+    _lib.call("kmls_pair_counts_csr_cold", d_off, d_items, n, d_row_of, n_rows, n_hot, got, ovf, s)
+    h0 = n_rows - n_hot
+    assert int(got[h0:, h0:].abs().sum().item()) == 0              # the block is left out, and zero
+    iu = torch.triu(torch.ones((n_rows, n_rows), dtype=torch.bool, device=dev()))
+    outside = iu.clone()
+    outside[h0:, h0:] = False
+    assert torch.equal(got[outside], want[outside])
+    # bitmap of the hot rows with a row stride larger than the words counted
+    row_words = int(_lib.value("kmls_bitmap_row_words", n))
+    stride = row_words + stride_extra
+    bitmap = torch.zeros((n_rows, stride), dtype=torch.int32, device=dev())
+    enc = torch.zeros((n_rows, row_words), dtype=torch.int32, device=dev())
+    _lib.call("kmls_encode_bitmap", d_off, d_items, n, d_row_of, t, n_rows, enc, row_words, s)
+    bitmap[:, :row_words] = enc
+    need = int(_lib.value("kmls_pair_gemm_scratch_bytes", n_hot, row_words))
+    scratch = torch.empty(need, dtype=torch.uint8, device=dev())
+    _lib.call("kmls_pair_counts_i8_block", bitmap[h0:], n_hot, row_words, stride, got[h0:, h0:], n_rows,
+              scratch, need, s)
+    assert torch.equal(got[iu], want[iu])
+
+
+@pytest.mark.parametrize("hot_rows", [-1, 128, 300, 4096])
+def test_native_loop_hybrid_pair_counts(hot_rows):
+    off, items = synth.zipf_playlists(60000, 3000, mean_draws=40, alpha=1.0, seed=5)
+    d_off, d_items = to_dev(off, items)
+    res = miner.mine_native(d_off, d_items, 3000, 0.004, pair_impl="csr", hot_rows=hot_rows, keep_pair_counts=True)
+    assert res.as_dict() == oracle_dict(off, items, 3000, 0.004)
+    assert res.stats["pair_impl"] == ("csr" if hot_rows < 0 else "csr+i8")
+    base = miner.mine_native(d_off, d_items, 3000, 0.004, pair_impl="popc", keep_pair_counts=True)
+    n_rows = base.pair_counts.shape[0]
+    iu = torch.triu(torch.ones((n_rows, n_rows), dtype=torch.bool, device=dev()))
+    assert torch.equal(res.pair_counts[iu], base.pair_counts[iu])
