@@ -520,6 +520,11 @@ int kmls_rebuild_items(const int32_t* d_items_prev, int32_t k, const int32_t* d_
  * (counter updates per second; tools/redg_peak.py times it). */
 int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_updates, uint64_t seed,
                          kmls_stream_t stream);
+/* The same with the addresses of one warp instruction confined to one stretch of `span`
+ * consecutive counters at a random multiple of span (the pattern of k_pair_counts_csr, whose
+ * warp keeps the matrix row while the column varies; span = 32: one 128-byte line). */
+int kmls_redg_microbench_span(int32_t* d_buf, int64_t n_words, int64_t n_updates, int64_t span,
+                              uint64_t seed, kmls_stream_t stream);
 int kmls_profile_begin(void);
 int64_t kmls_profile_report(char* buf, size_t capacity);
 

@@ -515,6 +515,17 @@ k_redg_microbench(int32_t* __restrict__ buf, uint64_t n_words, int64_t n_updates
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_updates; i += (int64_t)gridDim.x * blockDim.x)
     atomicAdd(buf + mix64(seed + (uint64_t)i) % n_words, 1);
 }
+// The kernel's own pattern: the 32 updates of a warp instruction fall into ONE stretch of `span`
+// consecutive counters (a pair (i, j) of a playlist keeps i - the matrix row - for many j) that
+// starts at a random multiple of `span`; span = 32: one 128-byte line per warp instruction.
+__global__ void __launch_bounds__(256)
+k_redg_microbench_span(int32_t* __restrict__ buf, uint64_t n_words, int64_t n_updates, uint64_t span, uint64_t seed) {
+  const uint64_t n_spans = n_words / span;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_updates; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint64_t base = (mix64(seed + (uint64_t)(i >> 5)) % n_spans) * span;
+    atomicAdd(buf + base + mix64(~seed + (uint64_t)i) % span, 1);
+  }
+}
 }  // namespace kmls
 
 extern "C" int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_updates, uint64_t seed,
@@ -524,5 +535,16 @@ extern "C" int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_u
   const int grid = (int)std::min<int64_t>((n_updates + 255) / 256, (int64_t)kmls::num_sms() * 32);
   kmls::k_redg_microbench<<<grid, 256, 0, (cudaStream_t)stream>>>(d_buf, (uint64_t)n_words, n_updates, seed);
   KMLS_LAUNCHED("k_redg_microbench");
+  return 0;
+}
+
+extern "C" int kmls_redg_microbench_span(int32_t* d_buf, int64_t n_words, int64_t n_updates, int64_t span,
+                                         uint64_t seed, kmls_stream_t stream) {
+  KMLS_REQUIRE(d_buf && span > 0 && n_words >= span && n_updates >= 0, "kmls_redg_microbench_span: bad arguments");
+  if (n_updates == 0) return 0;
+  const int grid = (int)std::min<int64_t>((n_updates + 255) / 256, (int64_t)kmls::num_sms() * 32);
+  kmls::k_redg_microbench_span<<<grid, 256, 0, (cudaStream_t)stream>>>(d_buf, (uint64_t)n_words, n_updates,
+                                                                       (uint64_t)span, seed);
+  KMLS_LAUNCHED("k_redg_microbench_span");
   return 0;
 }

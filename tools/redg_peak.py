@@ -32,6 +32,24 @@ def main():
             best = max(best, n_upd / (e0.elapsed_time(e1) / 1e3))
         out["cases"].append({"counter_matrix_rows": n_rows, "bytes": words * 4, "updates": n_upd,
                              "updates_per_s": best})
+    # the kernel's pattern: one warp instruction's updates inside one stretch of `span` counters
+    words = 5961 * 5961
+    buf = torch.zeros(words, dtype=torch.int32, device=dev)
+    for span in (32, 256, 1024, 5961):
+        n_upd = 1 << 30
+        for _ in range(2):
+            _lib.call("kmls_redg_microbench_span", buf, words, n_upd, span, 1, s)
+        torch.cuda.synchronize()
+        best = 0.0
+        for rep in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.call("kmls_redg_microbench_span", buf, words, n_upd, span, 2 + rep, s)
+            e1.record()
+            torch.cuda.synchronize()
+            best = max(best, n_upd / (e0.elapsed_time(e1) / 1e3))
+        out["cases"].append({"counter_matrix_rows": 5961, "bytes": words * 4, "updates": n_upd,
+                             "warp_span_counters": span, "updates_per_s": best})
     out["peak_updates_per_s"] = max(c["updates_per_s"] for c in out["cases"])
     print(json.dumps(out, indent=1))
 
