@@ -24,6 +24,8 @@
 // have global ids id_off[k] .. id_off[k+1]-1, counts are indexed by global id; `par` holds,
 // for every itemset of size >= 2 (indexed by global id - id_off[2]), the index of its parent
 // inside level k-1.
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kmls_b200.h"
 
@@ -513,6 +515,136 @@ k_rules_gather(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* _
   }
 }
 
+// The slow side of conf_keep, out of line: taken by a handful of splits per million.
+__device__ __noinline__ bool conf_keep_exact(int32_t cx, int32_t ca, double n_total, double min_conf) {
+  return __ddiv_rn(__ddiv_rn((double)cx, n_total), __ddiv_rn((double)ca, n_total)) >= min_conf;
+}
+
+// Gather route for k >= 6 (32 or more slots per itemset), built for memory-level parallelism:
+// a warp works on IPW consecutive itemsets at a time, BPI blocks of 32 slots of each
+// (IPW * BPI = 4 blocks = 8 independent 128-byte loads in flight per warp), and the header
+// words of its NEXT itemsets (count, parent, X_i rows) are loaded before the current ones are
+// processed, so that the two dependent latencies (header -> planes) of consecutive iterations
+// overlap. Inside a block of 32 slots at s >= 32 the highest set bit h of the slot is the
+// same for all lanes, so the X_i row is one shuffle per block, not per lane; only block 0 has
+// lane-dependent rows. Same outputs as the long path of k_rules_gather.
+template <int IPW>
+__global__ void __launch_bounds__(256, IPW == 4 ? 3 : 4)
+k_rules_gather_mlp(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* __restrict__ part_prev,
+                   double n_total, double min_conf, int32_t* __restrict__ part,
+                   int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
+  constexpr int BPI = 4 / IPW;
+  constexpr uint32_t kFull = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int n_sub = 1 << (k - 1), top = n_sub >> 1, nblk = n_sub >> 5;
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k], n_p = a.id_off[k] - a.id_off[k - 1];
+  const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
+  const int32_t* __restrict__ counts_k = a.counts + a.id_off[k];
+  const int32_t* __restrict__ par_k = a.par + (a.id_off[k] - a.id_off[2]);
+  const int32_t* __restrict__ pa_prev = part_prev;
+  const int32_t* __restrict__ pc_prev = part_prev + n_p * top;
+  int32_t* __restrict__ pa = part;
+  int32_t* __restrict__ pc = part + n_k * n_sub;
+  // even lanes take count(A) from the parent's plane A (slot s >> 1), odd lanes from its plane C
+  // (slot top - 1 - (s >> 1)): per lane one pointer offset and one step per block of 32 slots
+  const int ca_off = (lane & 1) ? top - 1 - (lane >> 1) : (lane >> 1);
+  const int ca_step = (lane & 1) ? -16 : 16;
+  const int h_lane = 31 - __clz(lane | 1);            // block 0: highest set bit of the slot
+
+  const int64_t stride = (int64_t)gridDim.x * 8 * IPW;
+  int64_t j0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * IPW;
+  int32_t c_x[IPW], row_p[IPW], my_sub[IPW];
+#pragma unroll
+  for (int t = 0; t < IPW; ++t) {
+    c_x[t] = row_p[t] = 0;
+    my_sub[t] = -1;
+    if (j0 + t < n_k) {
+      c_x[t] = __ldg(counts_k + j0 + t);
+      row_p[t] = __ldg(par_k + j0 + t);
+      if (lane < k - 1) my_sub[t] = __ldg(sub + (j0 + t) * (k - 1) + lane);
+    }
+  }
+  for (; j0 < n_k; j0 += stride) {
+    // next iteration's headers
+    const int64_t j1 = j0 + stride;
+    int32_t n_cx[IPW], n_rp[IPW], n_ms[IPW];
+#pragma unroll
+    for (int t = 0; t < IPW; ++t) {
+      n_cx[t] = n_rp[t] = 0;
+      n_ms[t] = -1;
+      if (j1 + t < n_k) {
+        n_cx[t] = __ldg(counts_k + j1 + t);
+        n_rp[t] = __ldg(par_k + j1 + t);
+        if (lane < k - 1) n_ms[t] = __ldg(sub + (j1 + t) * (k - 1) + lane);
+      }
+    }
+    int kept[IPW];
+#pragma unroll
+    for (int t = 0; t < IPW; ++t) kept[t] = 0;
+    for (int b0 = 0; b0 < nblk; b0 += BPI) {           // one trip unless k >= 9 (BPI = 4) or k = 8, IPW = 2
+      int32_t ca[IPW][BPI], cc[IPW][BPI];
+#pragma unroll
+      for (int t = 0; t < IPW; ++t) {
+        const bool live = j0 + t < n_k;                // warp-uniform
+        const int32_t* pa_p = pa_prev + (int64_t)row_p[t] * top;
+        const int32_t* pc_p = pc_prev + (int64_t)row_p[t] * top;
+        const int32_t* ca_ptr = ((lane & 1) ? pc_p : pa_p) + ca_off;
+#pragma unroll
+        for (int u = 0; u < BPI; ++u) {
+          const int b = b0 + u;
+          ca[t][u] = cc[t][u] = c_x[t];
+          if (!live || b >= nblk) continue;
+          if (b == 0) {
+            const int row_i = __shfl_sync(kFull, my_sub[t], (k - 2 - h_lane) & 31);
+            if (lane >= 1) {
+              ca[t][u] = __ldg(ca_ptr);
+              cc[t][u] = row_i < 0 ? -1 : __ldg(pc_prev + (int64_t)row_i * top + (lane - (1 << h_lane)));
+            }
+          } else {
+            const int hb = 31 - __clz(b);              // h = hb + 5 for every slot of the block
+            const int row_i = __shfl_sync(kFull, my_sub[t], k - 7 - hb);
+            ca[t][u] = __ldg(ca_ptr + b * ca_step);
+            cc[t][u] = row_i < 0 ? -1 : __ldg(pc_prev + (int64_t)row_i * top + (((b - (1 << hb)) << 5) + lane));
+          }
+        }
+      }
+#pragma unroll
+      for (int t = 0; t < IPW; ++t) {
+        if (j0 + t >= n_k) continue;                   // warp-uniform
+        const float fx = (float)c_x[t];
+        int32_t* pa_j = pa + (j0 + t) * n_sub + lane;
+        int32_t* pc_j = pc + (j0 + t) * n_sub + lane;
+#pragma unroll
+        for (int u = 0; u < BPI; ++u) {
+          const int b = b0 + u;
+          if (b >= nblk) continue;                     // warp-uniform
+          const int32_t va = ca[t][u], vc = cc[t][u];
+          const bool real = b > 0 || lane >= 1;        // slot 0 holds count(X) twice and makes no rule
+          const bool valid = real && (va | vc) >= 0;
+          if (real && !valid) atomicAdd(missing, 1);
+          const float fa = (float)va, fc = (float)vc;
+          bool k1 = fx > fa * thr_hi, k2 = fx > fc * thr_hi;
+          const bool u1 = valid && !k1 && !(fx < fa * thr_lo), u2 = valid && !k2 && !(fx < fc * thr_lo);
+          if (__any_sync(kFull, u1 || u2)) {           // within 1e-5 of the threshold: the exact doubles
+            if (u1) k1 = conf_keep_exact(c_x[t], va, n_total, min_conf);
+            if (u2) k2 = conf_keep_exact(c_x[t], vc, n_total, min_conf);
+          }
+          pa_j[b << 5] = va;
+          pc_j[b << 5] = vc;
+          kept[t] += __popc(__ballot_sync(kFull, k1 && valid)) + __popc(__ballot_sync(kFull, k2 && valid));
+        }
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < IPW; ++t) {
+      if (lane == 0 && j0 + t < n_k) rule_cnt[j0 + t] = kept[t];
+      c_x[t] = n_cx[t];
+      row_p[t] = n_rp[t];
+      my_sub[t] = n_ms[t];
+    }
+  }
+}
+
 // K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) planes of pass 1,
 // recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
 // rank). Order inside an itemset: per block of 32 slots (the whole itemset for k <= 6),
@@ -813,6 +945,17 @@ extern "C" int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_
   if (n_k == 0) return 0;
   KMLS_REQUIRE(d_items && d_counts && d_par && d_sub && d_part && d_rule_cnt && d_missing &&
                    (k == 2 || d_part_prev), "kmls_rules_count_gather: null pointer");
+  static const bool old_long = [] { const char* e = getenv("KMLS_RULES_GATHER"); return e && e[0] == 'o'; }();
+  if (k >= 6 && !old_long) {
+    const int ipw = k == 6 ? 4 : k == 7 ? 2 : 1;
+    const int64_t warps = (n_k + ipw - 1) / ipw;
+    const int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 16);
+    auto kern = ipw == 4 ? k_rules_gather_mlp<4> : ipw == 2 ? k_rules_gather_mlp<2> : k_rules_gather_mlp<1>;
+    kern<<<grid, 256, 0, (cudaStream_t)stream>>>(a, k, d_sub, (const int32_t*)d_part_prev, (double)n_playlists_total,
+                                                 min_confidence, (int32_t*)d_part, d_rule_cnt, d_missing);
+    KMLS_LAUNCHED("k_rules_gather_mlp");
+    return 0;
+  }
   const int per_warp = k <= 5 ? 32 >> (k - 1) : 1;
   const int64_t warps = (n_k + per_warp - 1) / per_warp;
   int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 32);

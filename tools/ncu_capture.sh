@@ -8,6 +8,12 @@ $B > gpurun_out/ncu_plain.json 2> gpurun_out/ncu_plain.err || exit 1
 if [ "$1" != "quick" ]; then
 ncu --metrics gpu__time_duration.sum --clock-control none -c 320 --csv --log-file gpurun_out/r2_launches.csv $B > gpurun_out/ncu_l.log 2>&1
 fi
+if [ "$1" = "pairs" ]; then   # the two level-2 kernels of the hybrid only
+cap2() { ncu --set full --clock-control none --import-source on -k regex:$2 --launch-skip $3 -c $4 -f -o gpurun_out/r2_$1 $B > gpurun_out/ncu_$1.log 2>&1; }
+cap2 pair_csr_cold k_pair_counts_csr 0 1
+cap2 pair_gemm_block k_pair_gemm_i8_ts 0 1
+exit 0
+fi
 cap() {  # name, kernel regex, launches to skip, launches to capture
   ncu --set full --clock-control none --import-source on -k regex:$2 --launch-skip $3 -c $4 -f -o gpurun_out/r2_$1 $B > gpurun_out/ncu_$1.log 2>&1
 }
