@@ -525,6 +525,13 @@ int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_updates, uin
  * warp keeps the matrix row while the column varies; span = 32: one 128-byte line). */
 int kmls_redg_microbench_span(int32_t* d_buf, int64_t n_words, int64_t n_updates, int64_t span,
                               uint64_t seed, kmls_stream_t stream);
+/* Measurement plumbing: a streaming kernel with `reads` (0..3) 8-byte loads and `writes`
+ * (0..3) 8-byte stores per element over separate arrays of n elements - the achievable HBM
+ * rate for the read:write mix of k_rules_write (1 : 3), which a copy (1 : 1) does not tell
+ * (tools/stream_mix_peak.py times it). */
+int kmls_stream_mix_microbench(const void* d_a, const void* d_b, const void* d_c, int64_t n,
+                               int32_t reads, int32_t writes, void* d_x, void* d_y, void* d_z,
+                               kmls_stream_t stream);
 int kmls_profile_begin(void);
 int64_t kmls_profile_report(char* buf, size_t capacity);
 

@@ -70,6 +70,7 @@ SIGNATURES = {
     "kmls_subtree_roots": (ctypes.c_int, [_P, _I64, _P, _P, _P, _P]),
     "kmls_place_level": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "kmls_redg_microbench": (ctypes.c_int, [_P, _I64, _I64, ctypes.c_uint64, _P]),
+    "kmls_stream_mix_microbench": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _I32, _P, _P, _P, _P]),
     "kmls_redg_microbench_span": (ctypes.c_int, [_P, _I64, _I64, _I64, ctypes.c_uint64, _P]),
     "kmls_profile_begin": (ctypes.c_int, []),
     "kmls_profile_report": (_I64, [_P, _SZ]),

@@ -538,6 +538,39 @@ extern "C" int kmls_redg_microbench(int32_t* d_buf, int64_t n_words, int64_t n_u
   return 0;
 }
 
+// Streaming micro-benchmark behind k_rules_write's roofline: every element is one 8-byte read
+// (`reads` of the three inputs are used: 0..3) and `writes` 8-byte writes (0..3) into separate
+// arrays, the traffic mix of pass 2 (8 bytes of plane words in, three 8-byte columns out).
+namespace kmls {
+__global__ void __launch_bounds__(256)
+k_stream_mix(const int2* __restrict__ a, const int2* __restrict__ b, const int2* __restrict__ c, int64_t n,
+             int reads, int writes, int2* __restrict__ x, int2* __restrict__ y, int2* __restrict__ z) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int2 v = make_int2((int)i, 1);
+    if (reads > 0) { const int2 t = __ldg(a + i); v.x ^= t.x; v.y += t.y; }
+    if (reads > 1) { const int2 t = __ldg(b + i); v.x ^= t.x; v.y += t.y; }
+    if (reads > 2) { const int2 t = __ldg(c + i); v.x ^= t.x; v.y += t.y; }
+    if (writes > 0) x[i] = v;
+    if (writes > 1) y[i] = make_int2(v.y, v.x);
+    if (writes > 2) z[i] = make_int2(v.x + 1, v.y);
+    if (writes == 0 && v.x == 0x7fffffff && v.y == 0x7ffffffe) x[0] = v;   // keeps the loads alive
+  }
+}
+}  // namespace kmls
+
+extern "C" int kmls_stream_mix_microbench(const void* d_a, const void* d_b, const void* d_c, int64_t n,
+                                          int32_t reads, int32_t writes, void* d_x, void* d_y, void* d_z,
+                                          kmls_stream_t stream) {
+  KMLS_REQUIRE(n >= 0 && reads >= 0 && reads <= 3 && writes >= 0 && writes <= 3 && d_a && d_b && d_c && d_x && d_y && d_z,
+               "kmls_stream_mix_microbench: bad arguments");
+  if (n == 0) return 0;
+  const int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)kmls::num_sms() * 32);
+  kmls::k_stream_mix<<<grid, 256, 0, (cudaStream_t)stream>>>((const int2*)d_a, (const int2*)d_b, (const int2*)d_c, n,
+                                                             reads, writes, (int2*)d_x, (int2*)d_y, (int2*)d_z);
+  KMLS_LAUNCHED("k_stream_mix");
+  return 0;
+}
+
 extern "C" int kmls_redg_microbench_span(int32_t* d_buf, int64_t n_words, int64_t n_updates, int64_t span,
                                          uint64_t seed, kmls_stream_t stream) {
   KMLS_REQUIRE(d_buf && span > 0 && n_words >= span && n_updates >= 0, "kmls_redg_microbench_span: bad arguments");

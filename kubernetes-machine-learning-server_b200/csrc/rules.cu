@@ -520,131 +520,6 @@ __device__ __noinline__ bool conf_keep_exact(int32_t cx, int32_t ca, double n_to
   return __ddiv_rn(__ddiv_rn((double)cx, n_total), __ddiv_rn((double)ca, n_total)) >= min_conf;
 }
 
-// Gather route for k >= 6 (32 or more slots per itemset), built for memory-level parallelism:
-// a warp works on IPW consecutive itemsets at a time, BPI blocks of 32 slots of each
-// (IPW * BPI = 4 blocks = 8 independent 128-byte loads in flight per warp), and the header
-// words of its NEXT itemsets (count, parent, X_i rows) are loaded before the current ones are
-// processed, so that the two dependent latencies (header -> planes) of consecutive iterations
-// overlap. Inside a block of 32 slots at s >= 32 the highest set bit h of the slot is the
-// same for all lanes, so the X_i row is one shuffle per block, not per lane; only block 0 has
-// lane-dependent rows. Same outputs as the long path of k_rules_gather.
-template <int IPW>
-__global__ void __launch_bounds__(256, IPW == 4 ? 3 : 4)
-k_rules_gather_mlp(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* __restrict__ part_prev,
-                   double n_total, double min_conf, int32_t* __restrict__ part,
-                   int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
-  constexpr int BPI = 4 / IPW;
-  constexpr uint32_t kFull = 0xffffffffu;
-  const int lane = threadIdx.x & 31;
-  const int n_sub = 1 << (k - 1), top = n_sub >> 1, nblk = n_sub >> 5;
-  const int64_t n_k = a.id_off[k + 1] - a.id_off[k], n_p = a.id_off[k] - a.id_off[k - 1];
-  const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
-  const int32_t* __restrict__ counts_k = a.counts + a.id_off[k];
-  const int32_t* __restrict__ par_k = a.par + (a.id_off[k] - a.id_off[2]);
-  const int32_t* __restrict__ pa_prev = part_prev;
-  const int32_t* __restrict__ pc_prev = part_prev + n_p * top;
-  int32_t* __restrict__ pa = part;
-  int32_t* __restrict__ pc = part + n_k * n_sub;
-  // even lanes take count(A) from the parent's plane A (slot s >> 1), odd lanes from its plane C
-  // (slot top - 1 - (s >> 1)): per lane one pointer offset and one step per block of 32 slots
-  const int ca_off = (lane & 1) ? top - 1 - (lane >> 1) : (lane >> 1);
-  const int ca_step = (lane & 1) ? -16 : 16;
-  const int h_lane = 31 - __clz(lane | 1);            // block 0: highest set bit of the slot
-
-  const int64_t stride = (int64_t)gridDim.x * 8 * IPW;
-  int64_t j0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * IPW;
-  int32_t c_x[IPW], row_p[IPW], my_sub[IPW];
-#pragma unroll
-  for (int t = 0; t < IPW; ++t) {
-    c_x[t] = row_p[t] = 0;
-    my_sub[t] = -1;
-    if (j0 + t < n_k) {
-      c_x[t] = __ldg(counts_k + j0 + t);
-      row_p[t] = __ldg(par_k + j0 + t);
-      if (lane < k - 1) my_sub[t] = __ldg(sub + (j0 + t) * (k - 1) + lane);
-    }
-  }
-  for (; j0 < n_k; j0 += stride) {
-    // next iteration's headers
-    const int64_t j1 = j0 + stride;
-    int32_t n_cx[IPW], n_rp[IPW], n_ms[IPW];
-#pragma unroll
-    for (int t = 0; t < IPW; ++t) {
-      n_cx[t] = n_rp[t] = 0;
-      n_ms[t] = -1;
-      if (j1 + t < n_k) {
-        n_cx[t] = __ldg(counts_k + j1 + t);
-        n_rp[t] = __ldg(par_k + j1 + t);
-        if (lane < k - 1) n_ms[t] = __ldg(sub + (j1 + t) * (k - 1) + lane);
-      }
-    }
-    int kept[IPW];
-#pragma unroll
-    for (int t = 0; t < IPW; ++t) kept[t] = 0;
-    for (int b0 = 0; b0 < nblk; b0 += BPI) {           // one trip unless k >= 9 (BPI = 4) or k = 8, IPW = 2
-      int32_t ca[IPW][BPI], cc[IPW][BPI];
-#pragma unroll
-      for (int t = 0; t < IPW; ++t) {
-        const bool live = j0 + t < n_k;                // warp-uniform
-        const int32_t* pa_p = pa_prev + (int64_t)row_p[t] * top;
-        const int32_t* pc_p = pc_prev + (int64_t)row_p[t] * top;
-        const int32_t* ca_ptr = ((lane & 1) ? pc_p : pa_p) + ca_off;
-#pragma unroll
-        for (int u = 0; u < BPI; ++u) {
-          const int b = b0 + u;
-          ca[t][u] = cc[t][u] = c_x[t];
-          if (!live || b >= nblk) continue;
-          if (b == 0) {
-            const int row_i = __shfl_sync(kFull, my_sub[t], (k - 2 - h_lane) & 31);
-            if (lane >= 1) {
-              ca[t][u] = __ldg(ca_ptr);
-              cc[t][u] = row_i < 0 ? -1 : __ldg(pc_prev + (int64_t)row_i * top + (lane - (1 << h_lane)));
-            }
-          } else {
-            const int hb = 31 - __clz(b);              // h = hb + 5 for every slot of the block
-            const int row_i = __shfl_sync(kFull, my_sub[t], k - 7 - hb);
-            ca[t][u] = __ldg(ca_ptr + b * ca_step);
-            cc[t][u] = row_i < 0 ? -1 : __ldg(pc_prev + (int64_t)row_i * top + (((b - (1 << hb)) << 5) + lane));
-          }
-        }
-      }
-#pragma unroll
-      for (int t = 0; t < IPW; ++t) {
-        if (j0 + t >= n_k) continue;                   // warp-uniform
-        const float fx = (float)c_x[t];
-        int32_t* pa_j = pa + (j0 + t) * n_sub + lane;
-        int32_t* pc_j = pc + (j0 + t) * n_sub + lane;
-#pragma unroll
-        for (int u = 0; u < BPI; ++u) {
-          const int b = b0 + u;
-          if (b >= nblk) continue;                     // warp-uniform
-          const int32_t va = ca[t][u], vc = cc[t][u];
-          const bool real = b > 0 || lane >= 1;        // slot 0 holds count(X) twice and makes no rule
-          const bool valid = real && (va | vc) >= 0;
-          if (real && !valid) atomicAdd(missing, 1);
-          const float fa = (float)va, fc = (float)vc;
-          bool k1 = fx > fa * thr_hi, k2 = fx > fc * thr_hi;
-          const bool u1 = valid && !k1 && !(fx < fa * thr_lo), u2 = valid && !k2 && !(fx < fc * thr_lo);
-          if (__any_sync(kFull, u1 || u2)) {           // within 1e-5 of the threshold: the exact doubles
-            if (u1) k1 = conf_keep_exact(c_x[t], va, n_total, min_conf);
-            if (u2) k2 = conf_keep_exact(c_x[t], vc, n_total, min_conf);
-          }
-          pa_j[b << 5] = va;
-          pc_j[b << 5] = vc;
-          kept[t] += __popc(__ballot_sync(kFull, k1 && valid)) + __popc(__ballot_sync(kFull, k2 && valid));
-        }
-      }
-    }
-#pragma unroll
-    for (int t = 0; t < IPW; ++t) {
-      if (lane == 0 && j0 + t < n_k) rule_cnt[j0 + t] = kept[t];
-      c_x[t] = n_cx[t];
-      row_p[t] = n_rp[t];
-      my_sub[t] = n_ms[t];
-    }
-  }
-}
-
 // K5 pass 2: streaming. One warp per itemset; reads the (count(A), count(C)) planes of pass 1,
 // recomputes the doubles and writes the kept rules at rule_off[x] + rank (ballot + popc
 // rank). Order inside an itemset: per block of 32 slots (the whole itemset for k <= 6),
@@ -768,6 +643,254 @@ k_rules_write(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_tot
       }
     }
     if (lane == 0 && pos != rule_off[j + 1]) atomicAdd(bad, 1);
+  }
+}
+
+// Kept rules of one split, 0..2 (the pass-1 decision of conf_keep for A -> C and C -> A).
+__device__ __forceinline__ int keep_pair(float fx, int32_t c_x, int32_t va, int32_t vc, float thr_hi, float thr_lo,
+                                         double n_total, double min_conf, int32_t* missing) {
+  if ((va | vc) < 0) {
+    atomicAdd(missing, 1);
+    return 0;
+  }
+  const float fa = (float)va, fc = (float)vc;
+  bool k1 = fx > fa * thr_hi, k2 = fx > fc * thr_hi;
+  const bool u1 = !k1 && !(fx < fa * thr_lo), u2 = !k2 && !(fx < fc * thr_lo);
+  if (u1 | u2) {                        // within 1e-5 of the threshold: the exact doubles
+    if (u1) k1 = conf_keep_exact(c_x, va, n_total, min_conf);
+    if (u2) k2 = conf_keep_exact(c_x, vc, n_total, min_conf);
+  }
+  return (int)k1 + (int)k2;
+}
+
+// Gather route, FOUR consecutive slots per lane (k >= 4): the kernel above is bound by
+// instruction issue - about 130 instructions per 32 slots, most of them 64-bit address
+// arithmetic - not by memory. Here a lane owns slots s .. s+3 (s a multiple of 4): count(A)
+// comes as two 8-byte loads (the even slots from the parent's plane A at s >> 1, the odd ones
+// from its plane C at top - 2 - (s >> 1)), count(C) as ONE 16-byte load from the X_i row (all
+// four slots share the highest set bit h when s >= 4), the results leave as two 16-byte
+// stores: a quarter of the memory instructions and address computations per slot. LPI lanes
+// serve one itemset (2^(k-1) / 4 of them, at most 32), 32 / LPI itemsets share a warp. The
+// lane with s = 0 handles slots 0..3 separately (slot 0 makes no rule; slots 1, 2, 3 have
+// h = 0, 1, 1). Same planes and counts as k_rules_gather.
+template <int LPI>
+__global__ void __launch_bounds__(256)
+k_rules_gather_v4(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* __restrict__ part_prev,
+                  double n_total, double min_conf, int32_t* __restrict__ part,
+                  int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
+  constexpr int IPW = 32 / LPI;
+  const int lane = threadIdx.x & 31;
+  const int g = lane / LPI, l = lane % LPI;
+  const int n_sub = 1 << (k - 1), top = n_sub >> 1;
+  const int n_iter = n_sub > 128 ? n_sub >> 7 : 1;
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k], n_p = a.id_off[k] - a.id_off[k - 1];
+  const float thr_hi = (float)(min_conf * 1.00001), thr_lo = (float)(min_conf * 0.99999);
+  const int32_t* __restrict__ counts_k = a.counts + a.id_off[k];
+  const int32_t* __restrict__ par_k = a.par + (a.id_off[k] - a.id_off[2]);
+  const int32_t* __restrict__ pa_prev = part_prev;
+  const int32_t* __restrict__ pc_prev = part_prev + n_p * top;
+  int32_t* __restrict__ pa = part;
+  int32_t* __restrict__ pc = part + n_k * n_sub;
+  const int64_t stride = (int64_t)gridDim.x * 8 * IPW;
+  // The warp's work is a flat stream of units (IPW itemsets, 128 slots of each); the header
+  // words of the NEXT unit (count, parent row, the X_i row its slots read) are loaded before the
+  // current unit's planes, so that consecutive units' dependent loads (header -> planes) overlap.
+  int64_t j0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * IPW;
+  int it = 0;
+  int32_t c_x = 0, row_p = 0, r_a = -1, r_b = -1;      // r_a: X_i row of the lane's slots (s == 0: of slot 1), r_b: s == 0 only, of slots 2, 3
+  auto load_rows = [&](int64_t j, int s, int32_t& ra, int32_t& rb) {
+    const int32_t* subj = sub + j * (k - 1);
+    if (s == 0) {
+      ra = __ldg(subj + (k - 2));
+      rb = __ldg(subj + (k - 3));
+    } else {
+      ra = __ldg(subj + (k - 2 - (31 - __clz(s))));
+    }
+  };
+  if (j0 + g < n_k) {
+    c_x = __ldg(counts_k + j0 + g);
+    row_p = __ldg(par_k + j0 + g);
+    load_rows(j0 + g, 4 * l, r_a, r_b);
+  }
+  int kept = 0;
+  while (j0 < n_k) {
+    const int64_t j = j0 + g;
+    const bool active = j < n_k;
+    // next unit's header
+    int64_t j1 = j0;
+    int it1 = it + 1;
+    if (it1 >= n_iter) { it1 = 0; j1 = j0 + stride; }
+    int32_t n_cx = c_x, n_rp = row_p, n_ra = -1, n_rb = -1;
+    if (j1 + g < n_k) {
+      if (it1 == 0) {
+        n_cx = __ldg(counts_k + j1 + g);
+        n_rp = __ldg(par_k + j1 + g);
+      }
+      load_rows(j1 + g, (it1 << 7) + 4 * l, n_ra, n_rb);
+    }
+    if (active) {
+      const float fx = (float)c_x;
+      const int32_t* pa_p = pa_prev + (int64_t)row_p * top;
+      const int32_t* pc_p = pc_prev + (int64_t)row_p * top;
+      const int s = (it << 7) + 4 * l;
+      const int2 e = __ldg(reinterpret_cast<const int2*>(pa_p + (s >> 1)));
+      const int2 o = __ldg(reinterpret_cast<const int2*>(pc_p + (top - 2 - (s >> 1))));
+      int4 va = make_int4(e.x, o.y, e.y, o.x), vc;
+      if (s == 0) {
+        va.x = c_x;
+        vc.x = c_x;
+        vc.y = r_a < 0 ? -1 : __ldg(pc_prev + (int64_t)r_a * top);
+        vc.z = vc.w = -1;
+        if (r_b >= 0) {
+          const int2 t2 = __ldg(reinterpret_cast<const int2*>(pc_prev + (int64_t)r_b * top));
+          vc.z = t2.x;
+          vc.w = t2.y;
+        }
+      } else {
+        const int h = 31 - __clz(s);
+        vc = make_int4(-1, -1, -1, -1);
+        if (r_a >= 0) vc = __ldg(reinterpret_cast<const int4*>(pc_prev + (int64_t)r_a * top + (s - (1 << h))));
+        kept += keep_pair(fx, c_x, va.x, vc.x, thr_hi, thr_lo, n_total, min_conf, missing);
+      }
+      kept += keep_pair(fx, c_x, va.y, vc.y, thr_hi, thr_lo, n_total, min_conf, missing);
+      kept += keep_pair(fx, c_x, va.z, vc.z, thr_hi, thr_lo, n_total, min_conf, missing);
+      kept += keep_pair(fx, c_x, va.w, vc.w, thr_hi, thr_lo, n_total, min_conf, missing);
+      *reinterpret_cast<int4*>(pa + j * n_sub + s) = va;
+      *reinterpret_cast<int4*>(pc + j * n_sub + s) = vc;
+    }
+    if (it1 == 0) {                                   // the itemsets of this unit are complete
+#pragma unroll
+      for (int d = LPI >> 1; d > 0; d >>= 1) kept += __shfl_xor_sync(0xffffffffu, kept, d);
+      if (active && l == 0) rule_cnt[j] = kept;
+      kept = 0;
+    }
+    c_x = n_cx;
+    row_p = n_rp;
+    r_a = n_ra;
+    r_b = n_rb;
+    j0 = j1;
+    it = it1;
+  }
+}
+
+// Pass 2 for k >= 6, software-pipelined like k_rules_gather_v4: the warp's work is a flat stream of units
+// (IPW itemsets x BPI blocks of 32 slots, IPW * BPI = 2) and the plane words AND header words
+// (count, rule offsets) of the NEXT unit are loaded before the current one is computed - across
+// itemset boundaries too, where k_rules_write's look-ahead stops and every itemset's first
+// loads are exposed to the full (write-loaded) memory latency. Same output, same order.
+template <int IPW>
+__global__ void __launch_bounds__(256)
+k_rules_write_mlp(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
+                  const int32_t* __restrict__ pa, const int32_t* __restrict__ pc,
+                  const int64_t* __restrict__ rule_off,
+                  int2* __restrict__ out_rule, double* __restrict__ out_confidence,
+                  double* __restrict__ out_lift, int32_t* __restrict__ bad) {
+  constexpr int BPI = 2 / IPW;
+  constexpr uint32_t kFull = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int n_sub = 1 << (k - 1), nblk = n_sub >> 5;
+  const uint32_t full = (1u << k) - 1u;
+  const uint32_t below = (1u << lane) - 1u;
+  const int64_t lvl_first = a.id_off[k];
+  const int32_t* __restrict__ counts_l = a.counts + lvl_first + lvl_begin;
+  const double rcp_n = __drcp_rn(n_total);
+  const int64_t stride = (int64_t)gridDim.x * 8 * IPW;
+  int64_t j0 = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * IPW;
+  int b0 = 0;
+  if (j0 >= lvl_count) return;
+
+  int32_t ca[2], cc[2], n_ca[2], n_cc[2];
+  int32_t cnt[IPW], n_cnt[IPW];
+  int64_t off[IPW + 1], n_off[IPW + 1];
+  // unit (jj, bb): block u belongs to itemset jj + (IPW == 2 ? u : 0), block bb + (IPW == 2 ? 0 : u)
+  auto load_unit = [&](int64_t jj, int bb, int32_t* va, int32_t* vc) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int64_t j = jj + (IPW == 2 ? u : 0);
+      const int s = ((bb + (IPW == 2 ? 0 : u)) << 5) + lane;
+      va[u] = vc[u] = -1;
+      if (j < lvl_count && s >= 1 && s < n_sub) {
+        va[u] = __ldg(pa + j * n_sub + s);
+        vc[u] = __ldg(pc + j * n_sub + s);
+      }
+    }
+  };
+  auto load_header = [&](int64_t jj, int32_t* c, int64_t* o) {
+#pragma unroll
+    for (int t = 0; t < IPW; ++t) {
+      c[t] = 0;
+      if (jj + t < lvl_count) c[t] = __ldg(counts_l + jj + t);
+    }
+#pragma unroll
+    for (int t = 0; t <= IPW; ++t) {
+      o[t] = 0;
+      if (jj + t <= lvl_count) o[t] = __ldg(rule_off + jj + t);
+    }
+  };
+  load_unit(j0, 0, ca, cc);
+  load_header(j0, cnt, off);
+  double s_x[IPW];
+  int64_t pos[IPW];
+#pragma unroll
+  for (int t = 0; t < IPW; ++t) { s_x[t] = 0.0; pos[t] = 0; }
+
+  while (j0 < lvl_count) {
+    int64_t j1 = j0;
+    int b1 = b0 + BPI;
+    if (b1 >= nblk) { b1 = 0; j1 = j0 + stride; }
+    const bool next_is_new = b1 == 0;                  // warp-uniform
+    load_unit(j1, b1, n_ca, n_cc);
+    if (next_is_new) load_header(j1, n_cnt, n_off);
+    if (b0 == 0) {
+#pragma unroll
+      for (int t = 0; t < IPW; ++t) {
+        s_x[t] = div_by_rcp((double)cnt[t], n_total, rcp_n);
+        pos[t] = off[t];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int t = IPW == 2 ? u : 0;
+      const int b = b0 + (IPW == 2 ? 0 : u);
+      if (b >= nblk || j0 + t >= lvl_count) continue;  // warp-uniform
+      const int s = (b << 5) + lane;
+      const int am = slot_mask(s, k);
+      const int32_t gid = (int32_t)(lvl_first + lvl_begin + j0 + t);
+      RuleVals r;
+      r.k1 = r.k2 = false;
+      if (ca[u] >= 0 && cc[u] >= 0) r = rule_values(s_x[t], ca[u], cc[u], n_total, rcp_n, min_conf);
+      const uint32_t m1 = __ballot_sync(kFull, r.k1), m2 = __ballot_sync(kFull, r.k2);
+      const int n1 = __popc(m1);
+      if (r.k1) {
+        const int64_t o = pos[t] + __popc(m1 & below);
+        out_rule[o] = make_int2(gid, am);
+        out_confidence[o] = r.c1;
+        out_lift[o] = r.l1;
+      }
+      if (r.k2) {
+        const int64_t o = pos[t] + n1 + __popc(m2 & below);
+        out_rule[o] = make_int2(gid, (int32_t)(full ^ (uint32_t)am));
+        out_confidence[o] = r.c2;
+        out_lift[o] = r.l2;
+      }
+      pos[t] += n1 + __popc(m2);
+    }
+    if (next_is_new) {
+#pragma unroll
+      for (int t = 0; t < IPW; ++t)
+        if (lane == 0 && j0 + t < lvl_count && pos[t] != off[t + 1]) atomicAdd(bad, 1);
+#pragma unroll
+      for (int t = 0; t < IPW; ++t) cnt[t] = n_cnt[t];
+#pragma unroll
+      for (int t = 0; t <= IPW; ++t) off[t] = n_off[t];
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      ca[u] = n_ca[u];
+      cc[u] = n_cc[u];
+    }
+    j0 = j1;
+    b0 = b1;
   }
 }
 
@@ -946,14 +1069,16 @@ extern "C" int kmls_rules_count_gather(const int32_t* d_items, const int32_t* d_
   KMLS_REQUIRE(d_items && d_counts && d_par && d_sub && d_part && d_rule_cnt && d_missing &&
                    (k == 2 || d_part_prev), "kmls_rules_count_gather: null pointer");
   static const bool old_long = [] { const char* e = getenv("KMLS_RULES_GATHER"); return e && e[0] == 'o'; }();
-  if (k >= 6 && !old_long) {
-    const int ipw = k == 6 ? 4 : k == 7 ? 2 : 1;
-    const int64_t warps = (n_k + ipw - 1) / ipw;
-    const int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 16);
-    auto kern = ipw == 4 ? k_rules_gather_mlp<4> : ipw == 2 ? k_rules_gather_mlp<2> : k_rules_gather_mlp<1>;
+  const bool aligned16 = ((uintptr_t)d_part & 15) == 0 && ((uintptr_t)d_part_prev & 15) == 0;
+  if (k >= 4 && !old_long && aligned16) {
+    const int lpi = k >= 8 ? 32 : 1 << (k - 3);          // lanes per itemset = slots / 4, at most a warp
+    const int64_t warps = (n_k * lpi + 31) / 32;
+    const int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 32);
+    auto kern = lpi == 32 ? k_rules_gather_v4<32> : lpi == 16 ? k_rules_gather_v4<16> : lpi == 8 ? k_rules_gather_v4<8>
+              : lpi == 4 ? k_rules_gather_v4<4> : k_rules_gather_v4<2>;
     kern<<<grid, 256, 0, (cudaStream_t)stream>>>(a, k, d_sub, (const int32_t*)d_part_prev, (double)n_playlists_total,
                                                  min_confidence, (int32_t*)d_part, d_rule_cnt, d_missing);
-    KMLS_LAUNCHED("k_rules_gather_mlp");
+    KMLS_LAUNCHED("k_rules_gather_v4");
     return 0;
   }
   const int per_warp = k <= 5 ? 32 >> (k - 1) : 1;
@@ -995,6 +1120,18 @@ extern "C" int kmls_rules_write_planes(const int32_t* d_counts, const int64_t* l
   if (lvl_count == 0) return 0;
   KMLS_REQUIRE(d_plane_a && d_plane_c && d_rule_off && d_out_rule && d_out_confidence && d_out_lift && d_mismatch &&
                    ((uintptr_t)d_out_rule & 7) == 0, "kmls_rules_write: null or misaligned pointer");
+  static const bool old_long = [] { const char* e = getenv("KMLS_RULES_WRITE"); return e && e[0] == 'o'; }();
+  if (k >= 6 && !old_long) {
+    const int ipw = k == 6 ? 2 : 1;
+    const int64_t warps = (lvl_count + ipw - 1) / ipw;
+    const int grid = (int)std::min<int64_t>((warps + 7) / 8, (int64_t)num_sms() * 32);
+    auto kern = ipw == 2 ? k_rules_write_mlp<2> : k_rules_write_mlp<1>;
+    kern<<<grid, 256, 0, (cudaStream_t)stream>>>(a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence,
+                                                 d_plane_a, d_plane_c, d_rule_off, (int2*)d_out_rule, d_out_confidence,
+                                                 d_out_lift, d_mismatch);
+    KMLS_LAUNCHED("k_rules_write_mlp");
+    return 0;
+  }
   int grid = (int)std::min<int64_t>((lvl_count + 7) / 8, (int64_t)num_sms() * 32);
   k_rules_write<<<grid, 256, 0, (cudaStream_t)stream>>>(
       a, k, lvl_begin, lvl_count, (double)n_playlists_total, min_confidence, d_plane_a, d_plane_c,
