@@ -502,7 +502,9 @@ def run_gpu(args):
     # per-call events would weigh on the timed region, so that path is traced in extra steps
     trace_in_loop = not by_playlists
     _lib.TRACE = [] if trace_in_loop else None
-    _lib.profile_begin()          # per-kernel CUDA events inside kmls_mine / kmls_rules
+    # per-kernel CUDA events inside kmls_mine / kmls_rules - events only: the data-dependent work
+    # figures cost extra kernels and host synchronisations, they come from one untimed step below
+    _lib.profile_begin(work=False)
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -521,6 +523,19 @@ def run_gpu(args):
         torch.cuda.synchronize()
     trace, _lib.TRACE = _lib.TRACE, None
     prof = _lib.profile_report()
+    if prof:
+        # algorithmic work per launch from one more step with the full accounting switched on; the
+        # launch sequence of a step is deterministic, so record i of a step gets record i's figure
+        _lib.profile_begin(work=True)
+        res, rules = step(d_off, d_items)
+        del res, rules
+        torch.cuda.synchronize()
+        prof_w = _lib.profile_report()
+        per_step = len(prof) // max(args.steps, 1)
+        if len(prof_w) == per_step and all(a[0] == b[0] and a[1] == b[1] for a, b in zip(prof, prof_w)):
+            prof = [(nm, lv, ms, prof_w[i % per_step][3]) for i, (nm, lv, ms, _) in enumerate(prof)]
+        else:
+            log(f"[bench] work accounting step has {len(prof_w)} records, timed steps {per_step}: work figures dropped")
     launches = launches_timed
     step_s = max_over_ranks(e0.elapsed_time(e1) / 1e3 / args.steps)
 
@@ -592,8 +607,21 @@ def run_gpu(args):
                 pk_a = json.load(open(os.path.join(ROOT, "profiles", "r2_redg_peak.json")))["peak_updates_per_s"]
                 r["atomic_peak_updates_per_s"] = pk_a
                 r["atomic_frac"] = r["atomic_updates_per_s"] / pk_a
-                r["atomic_peak_source"] = "profiles/r2_redg_peak.json (tools/redg_peak.py, uniform scatter)"
+                r["atomic_peak_source"] = ("profiles/r2_redg_peak.json (tools/redg_peak.py: the best rate of a kernel that "
+                                           "only scatters RED.ADDs - uniformly over a 4 MB matrix; this kernel's addresses are "
+                                           "skewed towards popular rows and combine in L2, so the ratio can pass 1; ncu puts "
+                                           "its busiest unit, the L1/LSU path, at 68 %)")
             except (OSError, ValueError, KeyError):
+                pass
+        if nm == "k_rules_write":
+            # 1 part plane words read to 3 parts rule columns written: what a trivial streaming kernel
+            # with that mix reaches on this GPU (tools/stream_mix_peak.py), next to the copy peak
+            try:
+                mix = json.load(open(os.path.join(ROOT, "profiles", "r2_stream_mix_peak.json")))["cases"]
+                pk_m = next(c_["gb_per_s"] for c_ in mix if (c_["reads_per_element"], c_["writes_per_element"]) == (1, 3))
+                r["mix_peak"] = {"read_write_mix": "1:3", "peak": pk_m, "unit": "GB/s", "frac": ach / pk_m,
+                                 "source": "profiles/r2_stream_mix_peak.json (tools/stream_mix_peak.py)"}
+            except (OSError, ValueError, KeyError, StopIteration):
                 pass
         t = ncu_traffic.get(nm)
         if t and name == t.get("workload", "zipf_1Mx100k_s0.001") and world == 1:

@@ -514,7 +514,15 @@ int kmls_rebuild_items(const int32_t* d_items_prev, int32_t k, const int32_t* d_
  * one text line per launch, "kernel,level,milliseconds,algorithmic_work", into buf (at most
  * capacity bytes, NUL-terminated); returns the bytes the full report needs. The work figure is
  * the algorithmic bytes of the launch as DESIGN.md section 3 defines them (operations for the
- * tensor-core GEMM). */
+ * tensor-core GEMM). Where that figure depends on the data (rows actually read and written by
+ * the counting kernels, counter updates, rules kept per level) finding it costs a few small
+ * kernels and a host synchronisation per level: kmls_profile_begin_events records the events
+ * only and leaves those figures at their static part, for the timed steps of a benchmark
+ * (bench.py takes the work figures from one extra, untimed step with kmls_profile_begin). */
+int kmls_profile_begin(void);
+int kmls_profile_begin_events(void);
+int64_t kmls_profile_report(char* buf, size_t capacity);
+
 /* Measurement plumbing: n_updates 32-bit RED.ADD updates scattered uniformly over
  * d_buf[n_words] - the micro-benchmark that gives k_pair_counts_csr's roofline its peak
  * (counter updates per second; tools/redg_peak.py times it). */
@@ -532,8 +540,7 @@ int kmls_redg_microbench_span(int32_t* d_buf, int64_t n_words, int64_t n_updates
 int kmls_stream_mix_microbench(const void* d_a, const void* d_b, const void* d_c, int64_t n,
                                int32_t reads, int32_t writes, void* d_x, void* d_y, void* d_z,
                                kmls_stream_t stream);
-int kmls_profile_begin(void);
-int64_t kmls_profile_report(char* buf, size_t capacity);
+
 
 #ifdef __cplusplus
 }

@@ -73,6 +73,7 @@ SIGNATURES = {
     "kmls_stream_mix_microbench": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _I32, _P, _P, _P, _P]),
     "kmls_redg_microbench_span": (ctypes.c_int, [_P, _I64, _I64, _I64, ctypes.c_uint64, _P]),
     "kmls_profile_begin": (ctypes.c_int, []),
+    "kmls_profile_begin_events": (ctypes.c_int, []),
     "kmls_profile_report": (_I64, [_P, _SZ]),
     "kmls_place_level_compact": (ctypes.c_int, [_P, _P, _P, _I64, _I32, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "kmls_rebuild_items": (ctypes.c_int, [_P, _I32, _P, _P, _I64, _P, _P]),
@@ -215,8 +216,14 @@ def value(name: str, *args):
     return getattr(load(), name)(*[_arg(a) for a in args])
 
 
-def profile_begin():
-    load().kmls_profile_begin()
+def profile_begin(work: bool = True):
+    """Per-kernel events inside kmls_mine / kmls_rules from now on; ``work=False``: events only,
+    without the data-dependent work figures (which cost extra small kernels and a host
+    synchronisation per level) - for timed steps."""
+    if work:
+        load().kmls_profile_begin()
+    else:
+        load().kmls_profile_begin_events()
 
 
 def profile_report():

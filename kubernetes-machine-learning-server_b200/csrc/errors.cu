@@ -48,7 +48,14 @@ extern "C" int kmls_profile_begin(void) {
   }
   p.records.clear();
   p.on = true;
+  p.work = true;
   return 0;
+}
+
+extern "C" int kmls_profile_begin_events(void) {
+  const int rc = kmls_profile_begin();
+  kmls::profiler().work = false;
+  return rc;
 }
 
 extern "C" int64_t kmls_profile_report(char* buf, size_t capacity) {

@@ -1059,6 +1059,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_TRY(kmls_pair_counts_csr_cold(d_offsets + pl_lo, d_items, pl_hi - pl_lo, row_of_item, n_rows, n_hot, pair,
                                          flags + 4, s));
     }
+    if (!profiler().work) rec = -1;
     if (rec >= 0) {   // work = counter updates made = sum of the upper triangle, 4 bytes each
       KMLS_CUDA(cudaMemsetAsync(flags + 6, 0, 8, s));
       k_sum_upper<<<grid_for((int64_t)n_rows * n_rows, 256, 8), 256, 0, s>>>(pair, n_rows, (unsigned long long*)(flags + 6));
@@ -1231,7 +1232,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     KMLS_TRY(M.take(&wnew, n_k));
     KMLS_TRY(M.take(&off2, n_k + 1));
     const bool parted = k == 2 && opt.n_parts > 1;
-    const bool prof = profiler().on;
+    const bool prof = profiler().on && profiler().work;
     KMLS_CUDA(cudaMemsetAsync(flags + 5, 0, 3 * sizeof(int32_t), s));
     {
       ProfScope ps("k_join_size", s, 20.0 * (double)n_k, k + 1);
@@ -1347,7 +1348,7 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
       KMLS_LAUNCHED("k_emit_rows");
     }
     ++M.launches;
-    if (rec_cp >= 0 || rec_and >= 0) {   // rows written = widths of the new itemsets that own a row
+    if ((rec_cp >= 0 || rec_and >= 0) && profiler().work) {   // rows written = widths of the new itemsets that own a row
       unsigned long long h[2] = {0, 0};
       KMLS_CUDA(cudaMemsetAsync(flags + 8, 0, 16, s));
       k_written_work<<<grid_for(n_next, 256, 8), 256, 0, s>>>(roww_n, par_n, roww_k, wnew, n_next,

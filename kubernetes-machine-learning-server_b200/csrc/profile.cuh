@@ -20,6 +20,8 @@ struct ProfRecord {
 
 struct Profiler {
   bool on = false;
+  bool work = true;   // also account the data-dependent work figures (extra small kernels and host
+                      // synchronisations per level): off for the timed steps of a benchmark
   std::vector<ProfRecord> records;
   std::vector<cudaEvent_t> pool;
   cudaEvent_t get() {

@@ -272,7 +272,7 @@ extern "C" int kmls_rules(const kmls_mine_result* mined, const void* d_tables_ba
                 "(nothing was truncated)", (long long)n_rules, R->workspace_needed_bytes, workspace_bytes);
   if (n_rules) {
     int64_t lvl_rules[KMLS_MAX_LEVELS + 3] = {0};
-    if (profiler().on) {   // rules per level, for the work figure of pass 2
+    if (profiler().on && profiler().work) {   // rules per level, for the work figure of pass 2
       for (int i = 0; i < n_plan; ++i)
         KMLS_CUDA(cudaMemcpyAsync(&lvl_rules[i], rule_off + plan[i].out0, 8, cudaMemcpyDeviceToHost, s));
       KMLS_CUDA(cudaStreamSynchronize(s));
