@@ -241,7 +241,7 @@ int kmls_project_rows(const uint32_t* d_arena_old, const int64_t* d_rowptr_old,
  * d_tids[d_tid_off[r] .. d_tid_off[r+1]) (d_tid_off = exclusive scan of the local row
  * counts); kmls_project_rows_gather then builds row(a, b) by sampling bitmap row b at the
  * columns of a (total_words = d_rowptr_new[n], the size of the new arena). Same output as
- * kmls_project_rows on the full bitmap. */
+ * kmls_project_rows on the full bitmap. Rows 16-byte aligned (row_words a multiple of 4). */
 int kmls_row_tidlists(const uint32_t* d_bitmap, int32_t n_rows, int64_t row_words,
                       const int64_t* d_tid_off, int32_t* d_tids, kmls_stream_t stream);
 int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_words, const int32_t* d_par_p,

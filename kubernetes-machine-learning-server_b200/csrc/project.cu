@@ -220,40 +220,50 @@ k_project_rows(const uint32_t* __restrict__ arena_old, const int64_t* __restrict
 // list of the playlists that contain it (k_row_tidlists); a new row (a, b) is then
 // row_b sampled at those positions: one gathered load + one ballot per 32 output bits.
 // ---------------------------------------------------------------------------------------
+// One CTA per row, one eighth of the row per warp: first the warp's number of set bits (128-bit
+// loads, no block barrier inside the loop), one barrier to turn the eight totals into offsets,
+// then the warp walks its part again (from L2) 128 words at a time - shuffle scan of the lanes'
+// popcounts, every lane writes the positions of its four words' bits.
 __global__ void __launch_bounds__(256)
 k_row_tidlists(const uint32_t* __restrict__ bitmap, int64_t row_words,
                const int64_t* __restrict__ tid_off, int32_t* __restrict__ tids) {
   __shared__ int warp_tot[8];
-  __shared__ int carry;
   if (tid_off[blockIdx.x + 1] == tid_off[blockIdx.x]) return;   // no list wanted for this row (block-uniform)
   const uint32_t* row = bitmap + (int64_t)blockIdx.x * row_words;
   int32_t* out = tids + tid_off[blockIdx.x];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry = 0;
+  const int64_t part = (((row_words + 7) >> 3) + 127) & ~(int64_t)127;
+  const int64_t w_lo = min(row_words, warp * part), w_hi = min(row_words, w_lo + part);
+  int cnt = 0;
+  for (int64_t w = w_lo + 4 * lane; w < w_hi; w += 128) cnt += popc4(ldg4(reinterpret_cast<const uint4*>(row + w)));
+  cnt = warp_sum(cnt);
+  if (lane == 0) warp_tot[warp] = cnt;
   __syncthreads();
-  for (int64_t w0 = 0; w0 < row_words; w0 += 256) {
-    const int64_t w = w0 + threadIdx.x;
-    uint32_t m = w < row_words ? __ldg(row + w) : 0u;
-    const int nb = __popc(m);
+  int pos = 0;
+  for (int i = 0; i < warp; ++i) pos += warp_tot[i];
+  for (int64_t w = w_lo; w < w_hi; w += 128) {
+    const int64_t ww = w + 4 * lane;
+    uint4 v = make_uint4(0u, 0u, 0u, 0u);
+    if (ww < w_hi) v = ldg4(reinterpret_cast<const uint4*>(row + ww));
+    const int nb = popc4(v);
     int incl = nb;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const int u = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += u;
     }
-    if (lane == 31) warp_tot[warp] = incl;
-    __syncthreads();
-    int pos = carry + incl - nb;
-    for (int i = 0; i < warp; ++i) pos += warp_tot[i];
-    const int32_t colbase = (int32_t)(w << 5);
-    while (m) {
-      const int b = __ffs(m) - 1;
-      out[pos++] = colbase + b;
-      m &= m - 1;
+    int p = pos + incl - nb;
+    const uint32_t m4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      uint32_t m = m4[t];
+      const int32_t colbase = (int32_t)((ww + t) << 5);
+      while (m) {
+        out[p++] = colbase + (__ffs(m) - 1);
+        m &= m - 1;
+      }
     }
-    __syncthreads();
-    if (threadIdx.x == 255) carry = pos;   // thread 255 ends at the block's total
-    __syncthreads();
+    pos += __shfl_sync(0xffffffffu, incl, 31);
   }
 }
 
@@ -400,6 +410,8 @@ extern "C" int kmls_row_tidlists(const uint32_t* d_bitmap, int32_t n_rows, int64
   KMLS_REQUIRE(n_rows >= 0 && row_words >= 0, "kmls_row_tidlists: negative size");
   if (n_rows == 0) return 0;
   KMLS_REQUIRE(d_bitmap && d_tid_off && d_tids, "kmls_row_tidlists: null pointer");
+  KMLS_REQUIRE((row_words & 3) == 0 && ((uintptr_t)d_bitmap & 15) == 0,
+               "kmls_row_tidlists: rows must be 16-byte aligned (row_words a multiple of 4, as kmls_bitmap_row_words gives)");
   k_row_tidlists<<<n_rows, 256, 0, (cudaStream_t)stream>>>(d_bitmap, row_words, d_tid_off, d_tids);
   KMLS_LAUNCHED("k_row_tidlists");
   return 0;
