@@ -50,7 +50,12 @@ __device__ __forceinline__ const int32_t* itemset_ptr(const Arena& a, int k, int
   return a.items + a.item_off[k] + (gid - a.id_off[k]) * k;
 }
 
-// node = {first child gid, number of children, last member, count}
+// node = {first child gid, number of children, last member, count}. The array is zeroed first
+// (a node without children keeps {0, 0}); every itemset then writes its own (last member,
+// count) and, if it is the first of its parent's children (the parent column is sorted, so a
+// parent's children are one run), the parent's (first child, number of children) - the run's
+// end found by galloping, not by a search per PARENT over the whole column (23 dependent probes
+// for each of 34 M itemsets at Z1M: 1.07 ms).
 __global__ void __launch_bounds__(256) k_trie_build(Arena a, int4* __restrict__ node) {
   const int64_t n = a.id_off[a.max_k + 1];
   for (int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; gid < n;
@@ -58,24 +63,23 @@ __global__ void __launch_bounds__(256) k_trie_build(Arena a, int4* __restrict__ 
     int k = 1;
     while (gid >= a.id_off[k + 1]) ++k;
     const int32_t last = __ldg(itemset_ptr(a, k, gid) + (k - 1));
-    // children: the run of level k+1 whose parent index is this itemset's index in level k;
-    // found by a binary search for the run's start in the (sorted) parent column
-    int32_t first = 0, cnt = 0;
-    if (k < a.max_k) {
-      const int64_t me = gid - a.id_off[k];
-      const int32_t* par = a.par + (a.id_off[k + 1] - a.id_off[2]);
-      const int64_t m = a.id_off[k + 2] - a.id_off[k + 1];
-      int64_t lo = 0, hi = m;
-      while (lo < hi) {
-        const int64_t mid = (lo + hi) >> 1;
-        if (__ldg(par + mid) < me) lo = mid + 1; else hi = mid;
-      }
-      int64_t e = lo;
-      while (e < m && __ldg(par + e) == me) ++e;
-      first = (int32_t)(a.id_off[k + 1] + lo);
-      cnt = (int32_t)(e - lo);
+    reinterpret_cast<int2*>(node + gid)[1] = make_int2(last, __ldg(a.counts + gid));
+    if (k < 2) continue;
+    const int64_t idx = gid - a.id_off[k], m = a.id_off[k + 1] - a.id_off[k];
+    const int32_t* par = a.par + (a.id_off[k] - a.id_off[2]);
+    const int32_t me = __ldg(par + idx);
+    if (idx > 0 && __ldg(par + idx - 1) == me) continue;      // not the first child
+    int64_t lo = idx, step = 1;                               // par[lo] == me
+    while (lo + step < m && __ldg(par + lo + step) == me) {
+      lo += step;
+      step <<= 1;
     }
-    node[gid] = make_int4(first, cnt, last, __ldg(a.counts + gid));
+    int64_t hi = min(lo + step, m);                           // par[hi] != me or hi == m
+    while (hi - lo > 1) {
+      const int64_t mid = (lo + hi) >> 1;
+      if (__ldg(par + mid) == me) lo = mid; else hi = mid;
+    }
+    reinterpret_cast<int2*>(node + a.id_off[k - 1] + me)[0] = make_int2((int32_t)gid, (int32_t)(hi - idx));
   }
 }
 
@@ -993,6 +997,7 @@ extern "C" int kmls_trie_index_build(const int32_t* d_items, const int32_t* d_co
   KMLS_REQUIRE(d_nodes && ((uintptr_t)d_nodes & 15) == 0, "kmls_trie_index_build: d_nodes must be 16-byte aligned");
   KMLS_REQUIRE(max_k < 2 || d_par, "kmls_trie_index_build: d_par is null");
   int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)num_sms() * 16);
+  KMLS_CUDA(cudaMemsetAsync(d_nodes, 0, sizeof(int4) * (size_t)n, (cudaStream_t)stream));
   k_trie_build<<<grid, 256, 0, (cudaStream_t)stream>>>(a, (int4*)d_nodes);
   KMLS_LAUNCHED("k_trie_build");
   return 0;
