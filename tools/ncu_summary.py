@@ -25,12 +25,26 @@ METRICS = [
 ]
 
 
-def launches(path):
+def launches(path, start_at=None, stop_at=None):
+    """start_at = "kernel:n": count from the n-th launch (1-based) of the first kernel whose name
+    contains `kernel` - to leave out an untimed first call of an entry point."""
     lines = [l for l in open(path) if not l.startswith("==")]
     agg, n = collections.OrderedDict(), 0
+    want, seen = (start_at.split(":")[0], int(start_at.split(":")[1])) if start_at else (None, 0)
+    stop, left = (stop_at.split(":")[0], int(stop_at.split(":")[1])) if stop_at else (None, 0)
     for row in csv.DictReader(lines):
         if row.get("Metric Name") != "gpu__time_duration.sum":
             continue
+        if stop is not None and stop in row["Kernel Name"]:
+            left -= 1
+            if left <= 0:
+                break
+        if want is not None:
+            if want in row["Kernel Name"]:
+                seen -= 1
+            if seen > 0:
+                continue
+            want = None
         v, u = float(row["Metric Value"].replace(",", "")), row["Metric Unit"]
         v = v / 1e6 if u == "ns" else v / 1e3 if u == "us" else v * 1e3 if u == "s" else v
         a = agg.setdefault(row["Kernel Name"], [0, 0.0])
@@ -62,6 +76,8 @@ def main():
     ap.add_argument("--title", required=True)
     ap.add_argument("--command", default="")
     ap.add_argument("--launches")
+    ap.add_argument("--stop-at", default=None, help="kernel:n - end the launch list before the n-th launch of that kernel")
+    ap.add_argument("--start-at", default=None, help="kernel:n - start the launch list at the n-th launch of that kernel")
     ap.add_argument("--full", nargs="*", default=[])
     ap.add_argument("--note", default="")
     ap.add_argument("--only", default="", help="comma-separated launch indices to keep from each --full report")
@@ -70,7 +86,7 @@ def main():
     if a.command:
         print(f"Command (B200, after the same command exited 0 without ncu): `{a.command}`\n")
     if a.launches:
-        agg, n = launches(a.launches)
+        agg, n = launches(a.launches, a.start_at, a.stop_at)
         tot = sum(v[1] for v in agg.values())
         print(f"## Launch list: {n} launches, {tot:.1f} ms in total (cold-cache, serialised: compare shares)\n")
         print("| share | total ms | launches | kernel |\n|---|---|---|---|")
