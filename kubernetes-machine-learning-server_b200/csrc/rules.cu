@@ -677,8 +677,13 @@ __device__ __forceinline__ int keep_pair(float fx, int32_t c_x, int32_t va, int3
 // serve one itemset (2^(k-1) / 4 of them, at most 32), 32 / LPI itemsets share a warp. The
 // lane with s = 0 handles slots 0..3 separately (slot 0 makes no rule; slots 1, 2, 3 have
 // h = 0, 1, 1). Same planes and counts as k_rules_gather.
+// resident CTAs per SM asked of ptxas (A/B builds with tools/build_variant.sh: ptxas' own choice of
+// 56 registers gives 8.46 ms over all levels at Z1M, 5 CTAs = 48 registers 7.96 ms, 6 CTAs = 40 registers 10.95 ms)
+#ifndef KMLS_GATHER_MINB
+#define KMLS_GATHER_MINB 5
+#endif
 template <int LPI>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, KMLS_GATHER_MINB)
 k_rules_gather_v4(Arena a, int k, const int32_t* __restrict__ sub, const int32_t* __restrict__ part_prev,
                   double n_total, double min_conf, int32_t* __restrict__ part,
                   int32_t* __restrict__ rule_cnt, int32_t* __restrict__ missing) {
