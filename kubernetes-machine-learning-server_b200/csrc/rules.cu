@@ -787,8 +787,11 @@ k_rules_gather_v4(Arena a, int k, const int32_t* __restrict__ sub, const int32_t
 // (count, rule offsets) of the NEXT unit are loaded before the current one is computed - across
 // itemset boundaries too, where k_rules_write's look-ahead stops and every itemset's first
 // loads are exposed to the full (write-loaded) memory latency. Same output, same order.
+#ifndef KMLS_WRITE_MINB
+#define KMLS_WRITE_MINB 4
+#endif
 template <int IPW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, KMLS_WRITE_MINB)
 k_rules_write_mlp(Arena a, int k, int64_t lvl_begin, int64_t lvl_count, double n_total, double min_conf,
                   const int32_t* __restrict__ pa, const int32_t* __restrict__ pc,
                   const int64_t* __restrict__ rule_off,
