@@ -267,9 +267,15 @@ k_row_tidlists(const uint32_t* __restrict__ bitmap, int64_t row_words,
   }
 }
 
-// Work unit = 64 consecutive words of the new arena (rows are 4-word multiples, so a group
+// Work unit = 256 consecutive words of the new arena (rows are 4-word multiples, so a group
 // of 4 words never straddles two rows): every warp does the same amount of work no matter
 // how long the rows are, and 4 independent gathers are in flight per lane.
+// 32-word halves per work unit (A/B at Z1M: 2 / 4 / 8 / 16 halves = 2.12 / 1.88 / 1.78 / 1.71 ms - a unit starts
+// with a 17-step binary search for its first row)
+#ifndef KMLS_PG_HALVES
+#define KMLS_PG_HALVES 8
+#endif
+constexpr int kPgWords = 32 * KMLS_PG_HALVES;   // words of the new arena per work unit
 __global__ void __launch_bounds__(256)
 k_project_gather(const uint32_t* __restrict__ bitmap, int64_t row_words,
                  const int32_t* __restrict__ par_p, const int32_t* __restrict__ par_q, int64_t n,
@@ -277,10 +283,10 @@ k_project_gather(const uint32_t* __restrict__ bitmap, int64_t row_words,
                  uint32_t* __restrict__ arena_new, const int64_t* __restrict__ rowptr_new,
                  int64_t total_words) {
   const int lane = threadIdx.x & 31;
-  const int64_t n_blocks = (total_words + 63) >> 6;
+  const int64_t n_blocks = (total_words + kPgWords - 1) / kPgWords;
   for (int64_t blk = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); blk < n_blocks;
        blk += (int64_t)gridDim.x * 8) {
-    const int64_t g0 = blk << 6;
+    const int64_t g0 = blk * kPgWords;
     // first row o with rowptr[o + 1] > g0 (rows without storage are skipped by construction)
     int64_t lo = 0, hi = n - 1;
     while (lo < hi) {
@@ -293,7 +299,7 @@ k_project_gather(const uint32_t* __restrict__ bitmap, int64_t row_words,
     const uint32_t* src = nullptr;
     int c = 0;
 #pragma unroll 1
-    for (int half = 0; half < 2; ++half) {
+    for (int half = 0; half < KMLS_PG_HALVES; ++half) {
       uint32_t mine = 0;
       for (int i = 0; i < 32; i += 4) {
         const int64_t g = g0 + half * 32 + i;
@@ -427,7 +433,7 @@ extern "C" int kmls_project_rows_gather(const uint32_t* d_bitmap, int64_t row_wo
   if (n == 0 || total_words == 0) return 0;
   KMLS_REQUIRE(d_bitmap && d_par_p && d_par_q && d_tids && d_tid_off && d_rowptr_new && d_arena_new,
                "kmls_project_rows_gather: null pointer");
-  const int64_t n_blocks = (total_words + 63) / 64;
+  const int64_t n_blocks = (total_words + kPgWords - 1) / kPgWords;
   int grid = (int)std::min<int64_t>((n_blocks + 7) / 8, (int64_t)num_sms() * 64);
   k_project_gather<<<grid, 256, 0, (cudaStream_t)stream>>>(d_bitmap, row_words, d_par_p, d_par_q, n,
                                                            d_tids, d_tid_off, d_arena_new,
