@@ -420,6 +420,64 @@ k_rules_subsets(Arena a, int k, const int4* __restrict__ node, const int32_t* __
   }
 }
 
+// The same, one thread per ITEMSET (k >= 3): the last member and the parent are loaded once for
+// all k-1 dropped members, and two dropped members are looked up at a time - their loads
+// (P \ {p_i}, its node, the candidate children) are independent and issued together.
+__global__ void __launch_bounds__(256)
+k_rules_subsets_row(Arena a, int k, const int4* __restrict__ node, const int32_t* __restrict__ sub_prev,
+                    int32_t* __restrict__ sub, int32_t* __restrict__ missing) {
+  const int64_t n_k = a.id_off[k + 1] - a.id_off[k];
+  const int32_t* items_k = a.items + a.item_off[k];
+  const int32_t* par_k = a.par + (a.id_off[k] - a.id_off[2]);
+  const int32_t* par_km1 = a.par + (a.id_off[k - 1] - a.id_off[2]);
+  const uint32_t base2 = (uint32_t)a.id_off[k - 2];
+  const int32_t base1 = (int32_t)a.id_off[k - 1];
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < n_k;
+       j += (int64_t)gridDim.x * blockDim.x) {
+    const int32_t x = __ldg(items_k + j * k + (k - 1));
+    const int32_t row_p = __ldg(par_k + j);
+    const int32_t* sp = sub_prev + (int64_t)row_p * (k - 2);
+    int32_t* out = sub + j * (k - 1);
+    int bad = 0;
+    for (int i0 = 0; i0 < k - 1; i0 += 2) {
+      int32_t pi[2];
+      int4 nd[2];
+      int lo[2], hi[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int i = i0 + u;
+        pi[u] = -1;
+        if (i < k - 1) pi[u] = i == k - 2 ? __ldg(par_km1 + row_p) : __ldg(sp + i);
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        nd[u] = make_int4(0, 0, 0, 0);
+        if (pi[u] >= 0) nd[u] = __ldg(node + (base2 + (uint32_t)pi[u]));
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) trie_bisect(node, nd[u].x, nd[u].y, x, lo[u], hi[u]);
+      int32_t key[2][4];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          key[u][c] = lo[u] + c < hi[u] ? __ldg(&node[(uint32_t)(nd[u].x + lo[u] + c)].z) : -1;
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int i = i0 + u;
+        if (i >= k - 1) continue;
+        int32_t res = -1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (key[u][c] == x) res = nd[u].x + lo[u] + c - base1;
+        if (res < 0) ++bad;
+        out[i] = res;
+      }
+    }
+    if (bad) atomicAdd(missing, bad);
+  }
+}
+
 // antecedent mask of slot s (and back): bit reversal over the k-1 prefix positions
 __device__ __forceinline__ int slot_mask(int s, int k) { return (int)(__brev((unsigned)s) >> (33 - k)); }
 
@@ -1059,6 +1117,13 @@ extern "C" int kmls_rules_subsets(const int32_t* d_items, const int32_t* d_par,
   if (n_k == 0) return 0;
   KMLS_REQUIRE(d_items && d_par && d_nodes && d_sub && d_missing && (k == 2 || d_sub_prev),
                "kmls_rules_subsets: null pointer");
+  static const bool old_kernel = [] { const char* e = getenv("KMLS_RULES_SUBSETS"); return e && e[0] == 'o'; }();
+  if (k >= 3 && !old_kernel) {
+    const int g = (int)std::min<int64_t>((n_k + 255) / 256, (int64_t)num_sms() * 32);
+    k_rules_subsets_row<<<g, 256, 0, (cudaStream_t)stream>>>(a, k, (const int4*)d_nodes, d_sub_prev, d_sub, d_missing);
+    KMLS_LAUNCHED("k_rules_subsets_row");
+    return 0;
+  }
   dim3 grid((unsigned)std::min<int64_t>((n_k + 255) / 256, (int64_t)num_sms() * 8), (unsigned)(k - 1));
   k_rules_subsets<<<grid, 256, 0, (cudaStream_t)stream>>>(a, k, (const int4*)d_nodes, d_sub_prev, d_sub,
                                                           d_missing);
