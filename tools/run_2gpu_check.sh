@@ -1,3 +1,2 @@
-python -m pytest tests/test_multi_rank.py -x -q -m gpu > gpurun_out/t2_multi.txt 2>&1
 T="python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1"
 $T --master-port 29511 bench.py --gpus 2 --steps 5 --warmup 3 --no-cpu > gpurun_out/bench_2gpu.json 2> gpurun_out/bench_2gpu.err
