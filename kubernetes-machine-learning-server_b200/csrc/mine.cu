@@ -400,6 +400,82 @@ k_count_and(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_
   }
 }
 
+// The same with HALF a warp per unit, for the deep levels where a unit holds one or two
+// candidates: a warp per unit then has two or three rows in flight and levels 8-10 run at
+// 3.3-4.8 TB/s where levels 4-6 reach 6-6.8. Two units per warp double the rows in flight per
+// resident warp; rows wider than 64 words take several passes of 16 lanes (their tail is formed
+// again at store time, as above).
+__global__ void __launch_bounds__(256)
+k_count_and_half(const Unit* __restrict__ units, int64_t n_units, int32_t thr, int32_t* __restrict__ cand_cnt,
+                 int32_t* __restrict__ cand_p) {
+  const int lane = threadIdx.x & 31, l = lane & 15;
+  const int64_t stride = (int64_t)gridDim.x * 16;
+  const int64_t n_iter = (n_units + stride - 1) / stride;
+  int64_t ui = ((int64_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 2 + (lane >> 4);
+  for (int64_t it = 0; it < n_iter; ++it, ui += stride) {     // warp-uniform trip count (full-mask shuffles inside)
+    const bool live = ui < n_units;
+    uint4 d0 = or4z(), d1 = or4z(), d2 = or4z(), d3 = or4z();
+    if (live) {
+      const uint4* u4 = reinterpret_cast<const uint4*>(units + ui);
+      d0 = __ldg(u4);
+      d1 = __ldg(u4 + 1);
+      d2 = __ldg(u4 + 2);
+      d3 = __ldg(u4 + 3);
+    }
+    const uint4* rowp = reinterpret_cast<const uint4*>(((uint64_t)d0.y << 32) | d0.x);
+    uint4* dst = reinterpret_cast<uint4*>(((uint64_t)d0.w << 32) | d0.z);
+    const uint4* rq[kUnitCands] = {reinterpret_cast<const uint4*>(((uint64_t)d1.y << 32) | d1.x),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d1.w << 32) | d1.z),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d2.y << 32) | d2.x),
+                                   reinterpret_cast<const uint4*>(((uint64_t)d2.w << 32) | d2.z)};
+    const int mc = (int)(d3.z >> 29), nv = (int)(d3.z & 0x1fffffffu);   // 0, 0 for a dead half
+    const bool h0 = l < nv;
+    const uint4 m0 = h0 ? ldg4(rowp + l) : or4z();
+    uint4 r0[kUnitCands];
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) r0[t] = (h0 && t < mc) ? ldg4(rq[t] + l) : or4z();
+    int cnt[kUnitCands];
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+      r0[t] = and4(r0[t], m0);
+      cnt[t] = popc4(r0[t]);
+    }
+    for (int seg = 16; seg < nv; seg += 16) {          // rows wider than 64 words (trip count differs per half: no shuffles inside)
+      if (l + seg < nv) {
+        const uint4 m1 = ldg4(rowp + l + seg);
+#pragma unroll
+        for (int t = 0; t < kUnitCands; ++t)
+          if (t < mc) cnt[t] += popc4(and4(ldg4(rq[t] + l + seg), m1));
+      }
+    }
+    uint32_t surv = 0;
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) cnt[t] += __shfl_xor_sync(0xffffffffu, cnt[t], o);   // inside the half
+      if (t < mc && cnt[t] >= thr) surv |= 1u << t;
+    }
+    if (l < mc) {
+      int c = cnt[0];
+#pragma unroll
+      for (int t = 1; t < kUnitCands; ++t)
+        if (l == t) c = cnt[t];
+      cand_cnt[d3.y + l] = c;
+      cand_p[d3.y + l] = (int32_t)d3.x;
+    }
+    if (surv == 0 || (d3.w && (surv & (surv - 1)) == 0)) continue;   // nobody, or an only child (no shuffles follow)
+#pragma unroll
+    for (int t = 0; t < kUnitCands; ++t) {
+      if ((surv >> t) & 1u) {                          // uniform inside the half
+        uint4* d = dst + (size_t)t * nv;
+        if (h0) d[l] = r0[t];
+        for (int seg = 16; seg < nv; seg += 16)
+          if (l + seg < nv) d[l + seg] = and4(ldg4(rq[t] + l + seg), ldg4(rowp + l + seg));
+      }
+    }
+  }
+}
+
 constexpr int kAndIlp = 4;   // candidates of a parent in flight per warp (AND route)
 constexpr int kChunk = 8;    // candidates of a parent handled together (bit-extract route)
 static_assert(kChunk == 8, "k_join_size and k_expand_units count chunks of 8");
@@ -1302,7 +1378,13 @@ extern "C" int kmls_mine(const int64_t* d_offsets, const int32_t* d_items, int64
     if (n_units > 0) {
       ProfScope ps("k_count_and", s, 4.0 * read_and + 32.0 * (double)n_units, k + 1);
       rec_and = ps.idx;
-      k_count_and<<<grid_for(n_units, 8, 48), 256, 0, s>>>(units, n_units, thr, cand_cnt, cand_p);
+      // half a warp per unit once the level's units are mostly single candidates (k_count_and_half)
+      static const int and_half = [] { const char* e = getenv("KMLS_AND_HALF"); return e ? atoi(e) : -1; }();
+      // (measured at Z1M: levels 5-10, where a unit holds 1-2 candidates, gain 5-8 %; levels 3-4 with their
+      // full units of four lose as much)
+      const bool half = and_half >= 0 ? and_half != 0 : (double)n_cand < 2.6 * (double)n_units;
+      if (half) k_count_and_half<<<grid_for(n_units, 16, 48), 256, 0, s>>>(units, n_units, thr, cand_cnt, cand_p);
+      else k_count_and<<<grid_for(n_units, 8, 48), 256, 0, s>>>(units, n_units, thr, cand_cnt, cand_p);
       KMLS_LAUNCHED("k_count_and");
       ++M.launches;
     }
